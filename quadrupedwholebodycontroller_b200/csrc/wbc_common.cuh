@@ -1,0 +1,85 @@
+// Shared definitions for the batched ANYmal whole-body-controller kernels (sm_100a).
+//
+// Execution model: ONE ROBOT INSTANCE PER WARP.  Per-instance matrices live in shared memory, scalars that steer
+// control flow are replicated in registers of all 32 lanes (every lane takes the same branches), vector work is
+// split as "lane i owns element i, i+32, i+64" and inner products run sequentially inside a lane so that sums are
+// accumulated in the same order as the reference's scalar loops.
+//
+// The same source also compiles as plain C++ with WBC_NL == 1 (one "lane") -- used ONLY by tools/host_emul to
+// debug control flow against the oracle on a machine without a GPU; it is never part of the shipped library.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+  #define WBC_DEV __device__ __forceinline__
+  #define WBC_FN  __device__ __noinline__
+  #define WBC_NL 32
+  #define WBC_SYNC() __syncwarp()
+  WBC_DEV unsigned wbc_ballot(bool p){ return __ballot_sync(0xffffffffu,p); }
+  WBC_DEV double wbc_max(double v){ for(int o=16;o>0;o>>=1){ double t=__shfl_xor_sync(0xffffffffu,v,o); v = t>v?t:v; } return v; }
+  WBC_DEV double wbc_bcast(double v,int src){ return __shfl_sync(0xffffffffu,v,src); }
+  WBC_DEV int    wbc_bcasti(int v,int src){ return __shfl_sync(0xffffffffu,v,src); }
+  WBC_DEV int    wbc_ffs(unsigned m){ return __ffs(m)-1; }
+#else
+  #define WBC_DEV static inline
+  #define WBC_FN  static
+  #define WBC_NL 1
+  #define WBC_SYNC() do{}while(0)
+  WBC_DEV unsigned wbc_ballot(bool p){ return p?1u:0u; }
+  WBC_DEV double wbc_max(double v){ return v; }
+  WBC_DEV double wbc_bcast(double v,int){ return v; }
+  WBC_DEV int    wbc_bcasti(int v,int){ return v; }
+  WBC_DEV int    wbc_ffs(unsigned m){ return m?0:-1; }
+#endif
+
+#define LANE_FOR(i,n) for(int i=lane;i<(n);i+=WBC_NL)
+
+namespace wbc {
+
+constexpr int NJ=12, NLEG=4, NV=42, NC=70;              // whole_body_controller.hpp:27-32
+constexpr double GRAV=9.81;
+
+// gains and limits shared by the whole batch (whole_body_controller.hpp:91-104, config/params_controller.yaml)
+struct Params {
+    double friction, loopRate, maxTorque, kpValue, kpValueZ, kdValue, kiValue, kpSwingValue, kdSwingValue, slackWeight;
+    double refPose[6];
+};
+
+// ---- compact QP handed from the assembly stage to the solver (doubles, per instance) ----
+// The dense 42x42 H and 70x42 A of whole_body_controller.cpp:479-497 have few distinct blocks:
+//   H = blkdiag(I6, I12, Hff, rho*I12),  Hff = I12 + Jst_b Jst_b^T
+//   A rows 0:6   [Mbb 0 -Jst_b^T 0]      rows 6:18  [Jst_b Jst_j 0 0]     rows 18:34 [0 0 Dfr 0]
+//     rows 34:46 [0 Mjj -Jst_j^T 0]      rows 46:58 [Jsw_b Jsw_j 0 -I]    rows 58:70 [Jsw_b Jsw_j 0 +I]
+// with Jst = c (.) Jc and Jsw = (1-c) (.) Jc row masks of ONE centroidal foot Jacobian Jc (12x18).
+struct QPData {
+    double Jc[12*18];      // centroidal foot Jacobian (all four feet, unmasked), row-major
+    double Mbb[36];        // centroidal mass matrix, base block
+    double Mjj[144];       // centroidal mass matrix, joint block
+    double Hff[144];       // H[18:30,18:30]
+    double gf[12];         // g[18:30]
+    double lbA[70], ubA[70];
+    double biasj[12];      // centroidal bias, joint part (for the torque recovery, wbc.cpp:565-568)
+    double mu, rho;
+    double cmask[4];       // 1.0 = stance, 0.0 = swing  (leg order LH, LF, RF, RH)
+};
+constexpr int QPDATA_DOUBLES = sizeof(QPData)/sizeof(double);
+
+// ---- per-instance persistent controller state (wbc.hpp:150-161) kept in HBM between ticks ----
+struct CtrlState {
+    double Told[6*18];     // top 6 rows of oldTransformationMatrix_ (rows 6..17 are constant [0 I])
+    double Jstold[12*18];  // oldCentroidStanceJacobian_
+    double Jswold[12*18];  // oldCentroidSwingJacobian_
+    double TdotInv[6*18];  // top 6 rows of transformationMatrixDotInverse_ (rows 6..17 are identically zero)
+    double integral[6];    // integralError_
+};
+constexpr int CTRLSTATE_DOUBLES = sizeof(CtrlState)/sizeof(double);
+
+// ---- small fixed-size helpers (3-vectors, 3x3 row-major) ----
+WBC_DEV void cross3(const double* a,const double* b,double* r){ double x=a[1]*b[2]-a[2]*b[1], y=a[2]*b[0]-a[0]*b[2], z=a[0]*b[1]-a[1]*b[0]; r[0]=x;r[1]=y;r[2]=z; }
+WBC_DEV void mv3(const double* R,const double* v,double* r){ double x=R[0]*v[0]+R[1]*v[1]+R[2]*v[2], y=R[3]*v[0]+R[4]*v[1]+R[5]*v[2], z=R[6]*v[0]+R[7]*v[1]+R[8]*v[2]; r[0]=x;r[1]=y;r[2]=z; }
+WBC_DEV void mtv3(const double* R,const double* v,double* r){ double x=R[0]*v[0]+R[3]*v[1]+R[6]*v[2], y=R[1]*v[0]+R[4]*v[1]+R[7]*v[2], z=R[2]*v[0]+R[5]*v[1]+R[8]*v[2]; r[0]=x;r[1]=y;r[2]=z; }
+WBC_DEV void mm3(const double* A,const double* B,double* C){ double t[9]; for(int i=0;i<3;i++)for(int j=0;j<3;j++) t[3*i+j]=A[3*i]*B[j]+A[3*i+1]*B[3+j]+A[3*i+2]*B[6+j]; for(int i=0;i<9;i++) C[i]=t[i]; }
+WBC_DEV double dot3(const double* a,const double* b){ return a[0]*b[0]+a[1]*b[1]+a[2]*b[2]; }
+
+}  // namespace wbc
