@@ -1,0 +1,794 @@
+// Batched dense active-set QP solver mirroring qpOASES 3.2.2 SQProblem::init / hotstart as configured by the
+// reference (Options::setToReliable, nWSR = 100, no simple bounds; src/whole_body_controller.cpp:517-541).
+// One QP instance per warp; Q (42x42), R, T and every vector live in shared memory.
+//
+// What is mirrored (reference lib/qpOASES/src): the online active-set homotopy of
+// QProblem::solveQP with far bounds (QProblem.cpp:446-640, 5498-5552), ramping (:5416-5492), drift correction
+// (:5559-5652), per-iteration projected Cholesky (:2036-2129), determineStepDirection with <= 2 refinement passes
+// (:4637-4975), the six sequential ratio tests (:4981-5278, QProblemB.cpp:2065-2107), add/remove of bounds and
+// constraints with Givens maintenance of the TQ factorisation (:2819-4252), full LI tests and LI exchange
+// (:2982-3300, 3487-3780), insertion-ordered index lists (Indexlist.cpp), and SQProblem::setupNewAuxiliaryQP
+// (SQProblem.cpp:340-515) for the warm start.
+//
+// What is NOT executed, with the reason it cannot change a result for this QP family (H = I + PSD, finite A):
+//  * Givens updates of R inside add/remove: enableCholeskyRefactorisation = 1 recomputes R from Q right after every
+//    working-set change and nothing reads R in between except the rho^2 test below  -> dead stores.
+//  * flipping bounds (Flipper snapshot of R,Q,T): fires only if rho^2 = z'Hz - r'r <= 1e3*EPS; z is a unit vector and
+//    H >= I, so rho^2 >= 1.
+//  * zero-curvature (NZC) test: fires only if max|dy| < 3e3*EPS*max|dx| for the removal direction; there
+//    dx'H dx = |dy_k| >= |dx|^2 and |dx|_inf >= 1/(42 max|A|), so the test never passes; the step direction it would
+//    compute has no side effect.
+//  * Hessian regularisation, HST_ZERO / HST_IDENTITY / semidefinite branches: H is always typed HST_POSDEF.
+// If one of these preconditions were ever violated the solver reports QP_RET_UNSUPPORTED_PATH instead of guessing.
+#pragma once
+#include "wbc_common.cuh"
+
+namespace wbc {
+
+// qpOASES returnValue numbering (MessageHandling.hpp) for the codes this path can produce
+enum : int { QP_OK=0, QP_RET_DIV_BY_ZERO=1, QP_RET_INIT_FAILED=33, QP_RET_INIT_FAILED_CHOLESKY=35, QP_RET_INIT_FAILED_HOTSTART=36,
+             QP_RET_INIT_FAILED_INFEASIBILITY=37, QP_RET_INIT_FAILED_UNBOUNDEDNESS=38, QP_RET_SETUP_AUXILIARYQP_FAILED=43,
+             QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED=54, QP_RET_STEPDIRECTION_DETERMINATION_FAILED=57, QP_RET_HOMOTOPY_STEP_FAILED=60,
+             QP_RET_HOTSTART_STOPPED_INFEASIBILITY=61, QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS=62, QP_RET_MAX_NWSR_REACHED=64, QP_RET_STEPDIRECTION_FAILED_TQ=68, QP_RET_STEPDIRECTION_FAILED_CHOLESKY=69,
+             QP_RET_HESSIAN_NOT_SPD=99, QP_RET_UNSUPPORTED_PATH=1001 };
+enum : int { QPS_NOTINITIALISED=0, QPS_PREPARINGAUXILIARYQP=1, QPS_AUXILIARYQPSOLVED=2, QPS_PERFORMINGHOMOTOPY=3, QPS_HOMOTOPYQPSOLVED=4, QPS_SOLVED=5 };
+enum : int { ST_LOWER=-1, ST_INACTIVE=0, ST_UPPER=1 };     // Types.hpp:272-280
+
+// Constants.hpp:48-64 and Options::setToReliable (Options.cpp:91-189)
+constexpr double QEPS=2.221e-16, QZERO=1.0e-25, QINFTY=1.0e20;
+constexpr double OPT_terminationTolerance=5.0e6*QEPS, OPT_boundTolerance=1.0e6*QEPS, OPT_boundRelaxation=1.0e4,
+                 OPT_epsNum=-1.0e3*QEPS, OPT_epsDen=1.0e3*QEPS, OPT_maxPrimalJump=1.0e8, OPT_maxDualJump=1.0e8,
+                 OPT_initialFarBounds=1.0e6, OPT_growFarBounds=1.0e3, OPT_epsFlipping=1.0e3*QEPS, OPT_epsIterRef=1.0e2*QEPS,
+                 OPT_epsLITests=1.0e5*QEPS, OPT_ramp0=0.5, OPT_ramp1=1.0;
+constexpr int OPT_numRefinementSteps=2;
+
+constexpr int LD=43;                  // leading dimension of Q, R, T (odd: conflict-free row AND column sweeps)
+#define QQ(i,j) w.Q[(i)+LD*(j)]       // Types.hpp:141-147: Q, R column-major, T row-major
+#define RR(i,j) w.R[(i)+LD*(j)]
+#define TT(i,j) w.T[(i)*LD+(j)]
+constexpr int SIZET=42;               // sizeT = min(nV,nC)
+
+// persistent solver state of one instance between ticks (HBM) -- what SQProblem keeps across hotstarts
+struct QPState {
+    double x[42], y[112], lb[42], ub[42], Ax_l[70], Ax_u[70];
+    signed char bstat[42], cstat[70];   // working set; list ORDER is re-derived afresh by setupNewAuxiliaryQP
+    int rampOffset, status, pad_;
+};
+
+// per-instance shared-memory workspace
+struct QPWork {
+    double Q[42*LD], R[42*LD], T[42*LD];
+    QPData qp;                                  // compact H, A, new g / lbA / ubA
+    double x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
+    double lbF[42], ubF[42], lbAF[70], ubAF[70];                 // far-bounded targets of the current homotopy
+    double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
+    double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
+    double tA[42], tB[42], xFRy[42], xFRz[42], Zdz[42], xTMP[42], yTMP[42];
+    double dAx[70], num[70], den[70], cs_c[42], cs_s[42], wv[42], tmpv[42], HZf[12*LD], zero[70];
+    signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70];
+};
+
+// scalar solver state, replicated in every lane
+struct QPCtx {
+    int lane;
+    int nFR,nFX,nAC,nIAC;
+    int status, infeasible, unbounded, rampOffset;
+    double tau;
+};
+
+// ---------------------------------------------------------------- structured A and H
+WBC_DEV double Ael(const QPData& q,int i,int j){
+    if(i<6){ if(j<6) return q.Mbb[6*i+j]; if(j<18||j>=30) return 0.0; int r=j-18; return -(q.cmask[r/3]*q.Jc[18*r+i]); }
+    if(i<18){ int r=i-6; return (j<18)? q.cmask[r/3]*q.Jc[18*r+j] : 0.0; }
+    if(i<34){ int r=i-18,l=r>>2,k=r&3,c=j-18-3*l; if(c<0||c>2) return 0.0;
+              double d = (c==2)? -q.mu : ((c==(k>>1))? ((k&1)?-1.0:1.0) : 0.0); return d*q.cmask[l]; }
+    if(i<46){ int r=i-34; if(j<6||j>=30) return 0.0; if(j<18) return q.Mjj[12*r+j-6]; int f=j-18; return -(q.cmask[f/3]*q.Jc[18*f+6+r]); }
+    { int r=(i<58)?i-46:i-58; if(j<18) return (1.0-q.cmask[r/3])*q.Jc[18*r+j]; if(j==30+r) return (i<58)?-1.0:1.0; return 0.0; }
+}
+WBC_DEV double Hel(const QPData& q,int i,int j){
+    if(i>=18&&i<30&&j>=18&&j<30) return q.Hff[12*(i-18)+(j-18)];
+    if(i!=j) return 0.0; return (i>=30)?q.rho:1.0;
+}
+// sum_j A[i][j] v[j] over columns with (sel==2: all, sel==0: free, sel==1: fixed), ascending j (Matrices.cpp:332-397 order)
+WBC_DEV double Arow_dot(const QPWork& w,int i,const double* v,int sel){
+    double s=0; for(int j=0;j<42;j++){ if(sel!=2 && ((w.bstat[j]!=0)!=(sel==1))) continue; double a=Ael(w.qp,i,j); if(a!=0.0) s+=a*v[j]; } return s; }
+WBC_DEV double Hrow_dot(const QPWork& w,int i,const double* v,int sel){
+    double s=0;
+    if(i>=18&&i<30){ for(int j=18;j<30;j++){ if(sel!=2 && ((w.bstat[j]!=0)!=(sel==1))) continue; s+=w.qp.Hff[12*(i-18)+(j-18)]*v[j]; } return s; }
+    if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return 0.0;
+    return ((i>=30)?w.qp.rho:1.0)*v[i];
+}
+
+// sum over ACTIVE constraints i (ascending number, the iSort order of Matrices.cpp transTimes) of A[i][j] yAC[pos(i)]
+WBC_DEV double AcolT_dot(const QPWork& w,int j,const double* yAC){
+    double s=0; for(int i=0;i<70;i++){ if(w.cstat[i]==0) continue; double a=Ael(w.qp,i,j); if(a!=0.0) s+=a*yAC[w.posAC[i]]; } return s; }
+
+// ---------------------------------------------------------------- index lists (Indexlist.cpp: insertion-ordered number[])
+// removal keeps the order of the remaining entries; every lane holds the same counters, one lane edits the list
+WBC_DEV void list_remove(signed char* L,int& n,int number,int lane){
+    if(lane==0){ int k=0; while(k<n&&L[k]!=number) k++; for(;k<n-1;k++) L[k]=L[k+1]; }
+    n--; WBC_SYNC();
+}
+WBC_DEV void list_append(signed char* L,int& n,int number,int lane){ if(lane==0) L[n]=(signed char)number; n++; WBC_SYNC(); }
+WBC_DEV void rebuild_posAC(QPWork& w,const QPCtx& c){ const int lane=c.lane; LANE_FOR(k,c.nAC) w.posAC[(int)w.AC[k]]=(signed char)k; WBC_SYNC(); }
+
+// Bounds::moveFreeToFixed / moveFixedToFree, Constraints::moveInactiveToActive / moveActiveToInactive (Bounds.cpp, Constraints.cpp)
+WBC_DEV void moveFreeToFixed(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.FR,c.nFR,number,c.lane); list_append(w.FX,c.nFX,number,c.lane); if(c.lane==0) w.bstat[number]=(signed char)st; WBC_SYNC(); }
+WBC_DEV void moveFixedToFree(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); list_remove(w.FX,c.nFX,number,c.lane); list_append(w.FR,c.nFR,number,c.lane); if(c.lane==0) w.bstat[number]=0; WBC_SYNC(); }
+WBC_DEV void moveInactiveToActive(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.IAC,c.nIAC,number,c.lane); list_append(w.AC,c.nAC,number,c.lane); if(c.lane==0) w.cstat[number]=(signed char)st; WBC_SYNC(); rebuild_posAC(w,c); }
+WBC_DEV void moveActiveToInactive(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); list_remove(w.AC,c.nAC,number,c.lane); list_append(w.IAC,c.nIAC,number,c.lane); if(c.lane==0) w.cstat[number]=0; WBC_SYNC(); rebuild_posAC(w,c); }
+// Indexlist::swapNumbers on the free list (Bounds::swapFree)
+WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ WBC_SYNC(); if(c.lane==0){ int a=0,b=0; while(w.FR[a]!=n1) a++; while(w.FR[b]!=n2) b++; signed char t=w.FR[a]; w.FR[a]=w.FR[b]; w.FR[b]=t; } WBC_SYNC(); }
+
+// ---------------------------------------------------------------- triangular solves
+constexpr int SLOTS=(42+WBC_NL-1)/WBC_NL;
+// generic column-oriented forward substitution for a lower-triangular system L a = b of size n:
+//   a_k = (b_k - sum_{j<k} L(k,j) a_j) / L(k,k);  each lane owns rows lane, lane+NL, ... and accumulates its rows'
+//   sums in ascending j exactly like the row-oriented reference loops.  Lget(k,j) returns L(k,j).
+// returns false on a (near-)zero pivot according to `pivot_ok(diag,sum)`.
+#define WBC_TRISOLVE(n, LGET, BSRC, ADST, PIVOT_OK, okflag)                                              \
+    {   double sum_[SLOTS]; okflag=true;                                                                  \
+        for(int s_=0;s_<SLOTS;s_++){ int r_=lane+WBC_NL*s_; sum_[s_]=(r_<(n))?(BSRC):0.0; (void)r_; }      \
+        WBC_SYNC();                                                                                       \
+        for(int k_=0;k_<(n);k_++){                                                                        \
+            double mine_=0.0; { int s_=k_/WBC_NL; if((k_%WBC_NL)==lane){ int r_=k_; double d_=LGET(k_,k_); \
+                if(!(PIVOT_OK(d_,sum_[s_]))) mine_=NAN; else mine_=sum_[s_]/d_; (void)r_; } }               \
+            double ak_=wbc_bcast(mine_,k_%WBC_NL);                                                        \
+            if(ak_!=ak_){ okflag=false; break; }                                                           \
+            if((k_%WBC_NL)==lane) ADST(k_)=ak_;                                                            \
+            for(int s_=0;s_<SLOTS;s_++){ int r_=lane+WBC_NL*s_; if(r_>k_&&r_<(n)) sum_[s_]-=LGET(r_,k_)*ak_; } \
+        }                                                                                                 \
+        WBC_SYNC(); }
+
+#define PIV_T(d,sum) (fabs(d)>QEPS)
+#define PIV_R(d,sum) (fabs(d)>=QZERO*fabs(sum))
+
+// QProblem::backsolveT (QProblem.cpp:4518-4565).  b, a indexed by AC position; a may alias b only if noted by caller (never here)
+WBC_DEV bool backsolveT(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a){
+    const int lane=c.lane, nT=c.nAC, tcol=SIZET-nT; bool ok=true;
+    if(nT<=0) return true;
+    WBC_SYNC();
+    if(!transposed){
+        // row i: sum_{j<i} TT(i,sizeT-1-j) a[nT-1-j];  unknown u_k = a[nT-1-k]
+        #define LG(i,j) TT(i,SIZET-1-(j))
+        #define BS b[r_]
+        #define AD(k) a[nT-1-(k)]
+        WBC_TRISOLVE(nT,LG,BS,AD,PIV_T,ok)
+        #undef LG
+        #undef BS
+        #undef AD
+    } else {
+        // row i: sum_{j<i} TT(nT-1-j,tcol+i) a[nT-1-j]
+        #define LG(i,j) TT(nT-1-(j),tcol+(i))
+        #define BS b[r_]
+        #define AD(k) a[nT-1-(k)]
+        WBC_TRISOLVE(nT,LG,BS,AD,PIV_T,ok)
+        #undef LG
+        #undef BS
+        #undef AD
+    }
+    return ok;
+}
+// QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b
+WBC_DEV bool backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a,int nR){
+    const int lane=c.lane; bool ok=true;
+    if(nR<=0) return true;
+    WBC_SYNC();
+    if(transposed){
+        #define LG(i,j) RR(j,i)
+        #define BS b[r_]
+        #define AD(k) a[k]
+        WBC_TRISOLVE(nR,LG,BS,AD,PIV_R,ok)
+        #undef LG
+        #undef BS
+        #undef AD
+    } else {
+        // R a = b solved from the last row up: unknown u_k = a[nR-1-k], L(i,j) = RR(nR-1-i, nR-1-j)
+        #define LG(i,j) RR(nR-1-(i),nR-1-(j))
+        #define BS b[nR-1-r_]
+        #define AD(k) a[nR-1-(k)]
+        WBC_TRISOLVE(nR,LG,BS,AD,PIV_R,ok)
+        #undef LG
+        #undef BS
+        #undef AD
+    }
+    return ok;
+}
+
+// ---------------------------------------------------------------- factorisations
+// QProblem::setupTQfactorisation (QProblem.cpp:2169-2193)
+WBC_DEV void setupTQfactorisation(QPWork& w,const QPCtx& c){
+    const int lane=c.lane; WBC_SYNC();
+    LANE_FOR(e,42*LD){ w.Q[e]=0.0; w.T[e]=0.0; }
+    WBC_SYNC();
+    LANE_FOR(i,c.nFR) QQ((int)w.FR[i],i)=1.0;
+    WBC_SYNC();
+}
+// DPOTRF "U" of LAPACKReplacement.cpp:39-77 on the leading n x n block of R; column j is owned by lane j%NL and its
+// inner products run k = i-1 .. 0 like the reference.  returns false if not SPD.
+WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
+    const int lane=c.lane;
+    for(int i=0;i<n;i++){
+        WBC_SYNC();
+        double sum=RR(i,i); for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);      // every lane, same value (broadcast reads)
+        if(!(sum>0.0)) return false;
+        const double d=sqrt(sum);
+        WBC_SYNC();
+        if(lane==(i%WBC_NL)) RR(i,i)=d;
+        for(int j=i+1+lane;j<n;j+=WBC_NL){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=s2/d; }
+    }
+    WBC_SYNC();
+    return true;
+}
+// QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
+WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
+    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    WBC_SYNC();
+    LANE_FOR(e,42*LD) w.R[e]=0.0;
+    WBC_SYNC();
+    if(c.nFX+c.nAC==0){
+        LANE_FOR(i,nFR) for(int j=0;j<nFR;j++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+        if(!potrf_R(w,c,nFR)) return QP_RET_HESSIAN_NOT_SPD;
+        return QP_OK;
+    }
+    if(nZ==0) return QP_OK;
+    if(c.nAC==0){
+        // make Z trivial
+        LANE_FOR(i,42) for(int j=0;j<nZ;j++) QQ(i,j)=0.0;
+        WBC_SYNC();
+        LANE_FOR(j,nZ) QQ((int)w.FR[j],j)=1.0;
+        LANE_FOR(i,nFR) for(int j=0;j<nFR;j++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+    } else {
+        // Z'HZ (SymDenseMat::bilinear, Matrices.cpp:630-667).  H = diag except the 12x12 force block, so
+        // (HZ)(v,k) = H_vv Z(v,k) for v outside the block; inside, the sum runs over the free force variables in list order.
+        LANE_FOR(k,nZ) for(int a=0;a<12;a++){ double s=0;
+            if(w.bstat[18+a]==0){ for(int i=0;i<nFR;i++){ int v=(int)w.FR[i]; if(v>=18&&v<30) s+=w.qp.Hff[12*a+(v-18)]*QQ(v,k); } }
+            w.HZf[a*LD+k]=s; }
+        WBC_SYNC();
+        // R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk), upper triangle only (the rest is never read)
+        LANE_FOR(kk,nZ) for(int jj=kk;jj<nZ;jj++){ double s=0;
+            for(int ii=0;ii<nFR;ii++){ int v=(int)w.FR[ii];
+                double hz = (v>=18&&v<30)? w.HZf[(v-18)*LD+kk] : ((v>=30)?w.qp.rho:1.0)*QQ(v,kk);
+                s+=QQ(v,jj)*hz; }
+            RR(kk,jj)=s; }
+    }
+    if(!potrf_R(w,c,nZ)) return QP_RET_HESSIAN_NOT_SPD;
+    return QP_OK;
+}
+
+// ---------------------------------------------------------------- step direction
+// QProblem::determineStepDirection (QProblem.cpp:4637-4975), HST_POSDEF branch.
+// delta_* point to 42- / 70-long vectors by variable / constraint number.  Results: w.dx (free and fixed parts, by
+// variable number), w.dyAC (by AC position), w.dyFX (by variable number).
+WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const double* dlbA,const double* dubA,const double* dlb,const double* dub,
+                                  bool bCzero,bool bBzero){
+    const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
+    WBC_SYNC();
+    // I) delta_xFX
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= bBzero?0.0:((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=0.0; }
+    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=0.0; w.tB[i]= bCzero?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
+    WBC_SYNC();
+    for(int r=0;r<=OPT_numRefinementSteps;r++){
+        if(nFR>0){
+            LANE_FOR(i,nFR) w.xTMP[(int)w.FR[i]]=0.0;
+            WBC_SYNC();
+            if(nAC>0){
+                if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=0.0; WBC_SYNC(); }
+                else {
+                    if(!bBzero&&r==0){ LANE_FOR(i,nAC) w.tB[i]-=Arow_dot(w,(int)w.AC[i],w.dx,1); WBC_SYNC(); }
+                    if(!backsolveT(w,c,w.tB,false,w.xFRy)) return QP_RET_STEPDIRECTION_FAILED_TQ;
+                    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=w.xTMP[ii]; for(int j=0;j<nAC;j++) s+=QQ(ii,nZ+j)*w.xFRy[j]; w.xTMP[ii]=s; }
+                    WBC_SYNC();
+                }
+            }
+            LANE_FOR(i,nZ) w.xFRz[i]=0.0;
+            // HMX*delta_xFX and HFR*delta_xFRy into tempA
+            if(!bBzero&&r==0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.dx,1); } WBC_SYNC(); }
+            if(nAC>0&&(!bCzero||!bBzero)){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.xTMP,0); } }
+            WBC_SYNC();
+            if(nZ>0){
+                LANE_FOR(i,nZ){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s-=QQ(jj,i)*w.tA[jj]; } w.xFRz[i]=s; }
+                if(!backsolveR(w,c,w.xFRz,true,w.xFRz,nZ)) return QP_RET_STEPDIRECTION_FAILED_CHOLESKY;
+                if(!backsolveR(w,c,w.xFRz,false,w.xFRz,nZ)) return QP_RET_STEPDIRECTION_FAILED_CHOLESKY;
+                LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=0; for(int j=0;j<nZ;j++) s+=QQ(ii,j)*w.xFRz[j]; w.Zdz[ii]=s; w.xTMP[ii]+=s; }
+                WBC_SYNC();
+            }
+        }
+        // III) delta_yAC
+        if(nAC>0){
+            if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.Zdz,0); } WBC_SYNC(); }
+            LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*w.tA[jj]; } w.tB[i]=s; }
+            if(!backsolveT(w,c,w.tB,true,w.yTMP)) return QP_RET_STEPDIRECTION_FAILED_TQ;
+        }
+        WBC_SYNC();
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.dx[ii]+=w.xTMP[ii]; }
+        LANE_FOR(i,nAC) w.dyAC[i]+=w.yTMP[i];
+        WBC_SYNC();
+        // residuals for the next refinement pass
+        double rnrm=0.0;
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); t-=AcolT_dot(w,ii,w.dyAC); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= bCzero?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
+            t-=Arow_dot(w,ii,w.dx,0); t-=Arow_dot(w,ii,w.dx,1); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
+        rnrm=wbc_max(rnrm);
+        WBC_SYNC();
+        if(rnrm<OPT_epsIterRef) break;
+    }
+    // IV) delta_yFX
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=AcolT_dot(w,ii,w.dyAC); t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); w.dyFX[ii]=t; }
+    WBC_SYNC();
+    return QP_OK;
+}
+
+// ---------------------------------------------------------------- ratio tests
+// QProblemB::performRatioTest + isBlocking (QProblemB.cpp:2065-2107, QProblemB.ipp:474-488).  The reference scans the
+// list sequentially, replacing the candidate whenever num_i < t*den_i with the CURRENT t.  Exactly the same chain of
+// winners is produced here: a ballot finds the first later entry that beats the current t, t is updated, repeat.
+// stat == 0: plain test (performPlainRatioTest, QProblem.cpp:4256-4275: num > epsNum, den > epsDen, t*den > num).
+WBC_DEV void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const double* num,const double* den,
+                              double& t,int& BC_idx){
+    const int lane=c.lane; BC_idx=-1; int pos=0;
+    WBC_SYNC();
+    for(;;){
+        int found=-1;
+        for(int base=(pos/WBC_NL)*WBC_NL; base<n; base+=WBC_NL){
+            int i=base+lane; bool f=false;
+            if(i>=pos&&i<n){
+                double nu=num[i], de=den[i];
+                if(stat){ if(stat[(int)idx[i]]==ST_UPPER){ nu=-nu; de=-de; }
+                          f=(de>=OPT_epsDen)&&(nu>=OPT_epsNum)&&(nu<t*de); }
+                else f=(nu>OPT_epsNum)&&(de>OPT_epsDen)&&(t*de>nu);
+            }
+            unsigned m=wbc_ballot(f);
+            if(m){ found=base+wbc_ffs(m); break; }
+        }
+        if(found<0) break;
+        t=num[found]/den[found]; BC_idx=(int)idx[found]; pos=found+1;
+    }
+}
+
+// ---------------------------------------------------------------- data shift, step, termination
+// QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are w.qp.gf (g_new), lbF/ubF/lbAF/ubAF
+WBC_DEV void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
+    const int lane=c.lane; WBC_SYNC();
+    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; w.dg[i]=gn-w.g[i]; w.dlb[i]=w.lbF[i]-w.lb[i]; w.dub[i]=w.ubF[i]-w.ub[i]; }
+    LANE_FOR(i,70){ w.dlbA[i]=w.lbAF[i]-w.lbA[i]; w.dubA[i]=w.ubAF[i]-w.ubA[i]; }
+    WBC_SYNC();
+    bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(w.dlb[ii])>QEPS||fabs(w.dub[ii])>QEPS) nz=true; }
+    bBzero=(wbc_ballot(nz)==0u);
+    nz=false; LANE_FOR(i,c.nAC){ int ii=(int)w.AC[i]; if(fabs(w.dlbA[ii])>QEPS||fabs(w.dubA[ii])>QEPS) nz=true; }
+    bCzero=(wbc_ballot(nz)==0u);
+}
+// QProblem::getRelativeHomotopyLength (QProblem.cpp:5372-5410, QProblemB.cpp:2113-2157)
+WBC_DEV double relativeHomotopyLength(const QPWork& w,const QPCtx& c){
+    const int lane=c.lane; double len=0.0;
+    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; double s=fmax(fabs(gn),1.0); len=fmax(len,fabs(gn-w.g[i])/s);
+                    s=fmax(fabs(w.lbF[i]),1.0); len=fmax(len,fabs(w.lbF[i]-w.lb[i])/s); s=fmax(fabs(w.ubF[i]),1.0); len=fmax(len,fabs(w.ubF[i]-w.ub[i])/s); }
+    LANE_FOR(i,70){ double s=fmax(fabs(w.lbAF[i]),1.0); len=fmax(len,fabs(w.lbAF[i]-w.lbA[i])/s); s=fmax(fabs(w.ubAF[i]),1.0); len=fmax(len,fabs(w.ubAF[i]-w.ubA[i])/s); }
+    return wbc_max(len);
+}
+// QProblem::setupAuxiliaryQPgradient (QProblem.cpp:2602-2641): g = y_B - H x + A' y_C
+WBC_DEV void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
+    const int lane=c.lane; WBC_SYNC();
+    LANE_FOR(i,42){ double t=w.y[i]; t-=Hrow_dot(w,i,w.x,2);
+        double s=0; for(int k=0;k<70;k++){ double a=Ael(w.qp,k,i); if(a!=0.0) s+=a*w.y[42+k]; } w.g[i]=t+s; }
+    WBC_SYNC();
+}
+// QProblem::performStep (QProblem.cpp:4981-5278)
+WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_isBound){
+    const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nIAC=c.nIAC;
+    c.tau=1.0; BC_idx=-1; BC_status=2 /*ST_UNDEFINED*/; BC_isBound=false; int tmp;
+    WBC_SYNC();
+    // I.1 active constraints' duals
+    LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=-w.dyAC[i]; }
+    performRatioTest(c,nAC,w.AC,w.cstat,w.num,w.den,c.tau,tmp);
+    if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=false; }
+    WBC_SYNC();
+    // I.2 fixed variables' duals
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.num[i]=w.y[ii]; w.den[i]=-w.dyFX[ii]; }
+    performRatioTest(c,nFX,w.FX,w.bstat,w.num,w.den,c.tau,tmp);
+    if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
+    WBC_SYNC();
+    // II.1 inactive constraints
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_dot(w,ii,w.dx,2); }
+    WBC_SYNC();
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],0.0); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
+    performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
+    if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=false; }
+    WBC_SYNC();
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_u[ii],0.0); w.den[i]=w.dAx[ii]-w.dubA[ii]; }
+    performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
+    if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=false; }
+    WBC_SYNC();
+    // II.2 free variables
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.x[ii]-w.lb[ii],0.0); w.den[i]=w.dlb[ii]-w.dx[ii]; }
+    performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
+    if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=true; }
+    WBC_SYNC();
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.ub[ii]-w.x[ii],0.0); w.den[i]=w.dx[ii]-w.dub[ii]; }
+    performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
+    if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=true; }
+    WBC_SYNC();
+    // III) step
+    if(c.tau>QZERO){
+        const double tau=c.tau;
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.x[ii]+=tau*w.dx[ii]; }
+        LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.x[ii]+=tau*w.dx[ii]; w.y[ii]+=tau*w.dyFX[ii]; }
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]+=tau*w.dyAC[i]; }
+        LANE_FOR(i,42){ w.g[i]+=tau*w.dg[i]; w.lb[i]+=tau*w.dlb[i]; w.ub[i]+=tau*w.dub[i]; }
+        LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
+        WBC_SYNC();
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_dot(w,ii,w.x,2); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
+        LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; double da=w.dAx[ii];
+            w.Ax[ii]+=tau*da; w.Ax_l[ii]+=tau*(da-w.dlbA[ii]); w.Ax_u[ii]+=tau*(w.dubA[ii]-da); }
+        WBC_SYNC();
+    }
+}
+// QProblem::performRamping (QProblem.cpp:5416-5492); all bounds and constraints are typed ST_BOUNDED on this path
+WBC_FN void performRamping(QPWork& w,QPCtx& c){
+    const int lane=c.lane, nRamp=42+70+70+42; WBC_SYNC();
+    LANE_FOR(i,42){
+        double tP=(double)((i+c.rampOffset)%nRamp)/(double)(nRamp-1), rP=(1.0-tP)*OPT_ramp0+tP*OPT_ramp1;
+        double tD=(double)((42+70+70+i+c.rampOffset)%nRamp)/(double)(nRamp-1), rD=(1.0-tD)*OPT_ramp0+tD*OPT_ramp1;
+        int bs=w.bstat[i]; double xi=w.x[i], sca=fmax(fabs(xi),1.0);
+        if(bs!=ST_LOWER) w.lb[i]=xi-sca*rP;
+        if(bs!=ST_UPPER) w.ub[i]=xi+sca*rP;
+        if(bs==ST_LOWER){ w.lb[i]=xi; w.y[i]=+rD; }
+        if(bs==ST_UPPER){ w.ub[i]=xi; w.y[i]=-rD; }
+        if(bs==ST_INACTIVE) w.y[i]=0.0;
+    }
+    LANE_FOR(i,70){
+        double tP=(double)((42+i+c.rampOffset)%nRamp)/(double)(nRamp-1), rP=(1.0-tP)*OPT_ramp0+tP*OPT_ramp1;
+        double tD=(double)((42+70+i+c.rampOffset)%nRamp)/(double)(nRamp-1), rD=(1.0-tD)*OPT_ramp0+tD*OPT_ramp1;
+        int cs=w.cstat[i]; double ax=w.Ax[i], sca=fmax(fabs(ax),1.0);
+        if(cs!=ST_LOWER) w.lbA[i]=ax-sca*rP;
+        if(cs!=ST_UPPER) w.ubA[i]=ax+sca*rP;
+        if(cs==ST_LOWER){ w.lbA[i]=ax; w.y[42+i]=+rD; }
+        if(cs==ST_UPPER){ w.ubA[i]=ax; w.y[42+i]=-rD; }
+        if(cs==ST_INACTIVE) w.y[42+i]=0.0;
+        w.Ax_l[i]=ax-w.lbA[i]; w.Ax_u[i]=w.ubA[i]-ax;
+    }
+    setupAuxiliaryQPgradient(w,c);
+    c.rampOffset++;
+}
+// QProblem::performDriftCorrection (QProblem.cpp:5559-5652)
+WBC_FN void performDriftCorrection(QPWork& w,QPCtx& c){
+    const int lane=c.lane; WBC_SYNC();
+    LANE_FOR(i,42){ int bs=w.bstat[i]; double xi=w.x[i];
+        if(bs==ST_LOWER){ w.lb[i]=xi; w.ub[i]=fmax(w.ub[i],xi); w.y[i]=fmax(w.y[i],0.0); }
+        else if(bs==ST_UPPER){ w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=xi; w.y[i]=fmin(w.y[i],0.0); }
+        else { w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=fmax(w.ub[i],xi); w.y[i]=0.0; } }
+    LANE_FOR(i,70){ int cs=w.cstat[i]; double ax=w.Ax[i];
+        if(cs==ST_LOWER){ w.lbA[i]=ax; w.Ax_l[i]=0.0; w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=fmax(w.y[42+i],0.0); }
+        else if(cs==ST_UPPER){ w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=ax; w.Ax_u[i]=0.0; w.y[42+i]=fmin(w.y[42+i],0.0); }
+        else { w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=0.0; } }
+    setupAuxiliaryQPgradient(w,c);
+}
+
+// ---------------------------------------------------------------- Givens (QProblemB.ipp:409-470, four-multiplication form)
+WBC_DEV void computeGivens(double xold,double yold,double& xnew,double& ynew,double& cc,double& ss){
+    if(fabs(yold)<QZERO){ cc=1.0; ss=0.0; xnew=xold; ynew=yold; }
+    else { double mu=fabs(xold); if(fabs(yold)>mu) mu=fabs(yold);
+           double t=mu*sqrt((xold/mu)*(xold/mu)+(yold/mu)*(yold/mu)); if(xold<0.0) t=-t;
+           cc=xold/t; ss=yold/t; xnew=t; ynew=0.0; }
+}
+// The column-wise Givens chains of addConstraint / addBound: rotation j is defined by (wv[j+1], wv[j]) where wv[j] is the
+// result of rotation j-1 -- a scalar recurrence every lane evaluates redundantly -- and then applied to the column
+// pair (j+1, j) of Q.  The rows of Q are independent, so each lane sweeps its own rows through the whole chain.
+WBC_DEV void givens_chain(QPWork& w,const QPCtx& c,int nrot){
+    WBC_SYNC();
+    double cur=w.wv[0];
+    for(int j=0;j<nrot;j++){ double xn,yn,cc,ss; computeGivens(w.wv[j+1],cur,xn,yn,cc,ss); cur=xn; if(c.lane==0){ w.cs_c[j]=cc; w.cs_s[j]=ss; } }
+    WBC_SYNC();
+    if(c.lane==0&&nrot>0) w.wv[nrot]=cur;
+    WBC_SYNC();
+}
+WBC_DEV void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
+    const int lane=c.lane;
+    LANE_FOR(i,nrows){ int ii=(int)w.FR[i]; double qa=QQ(ii,0);
+        for(int j=0;j<nrot;j++){ double qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
+        QQ(ii,nrot)=qa; }
+    WBC_SYNC();
+}
+
+WBC_FN int removeBound(QPWork& w,QPCtx& c,int number);
+WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number);
+
+// QProblem::addConstraint_checkLI (QProblem.cpp:2982-3106): returns true if linearly independent
+WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
+    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    WBC_SYNC();
+    if(fullTest){
+        LANE_FOR(j,42) w.tmpv[j]=Ael(w.qp,number,j);
+        WBC_SYNC();
+        int rv=determineStepDirection(w,c,w.tmpv,w.zero,w.zero,w.zero,w.zero,false,false);
+        if(rv!=QP_OK) return false;
+        double weight=0.0, zero=0.0;
+        LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
+        LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; weight=fmax(weight,fabs(w.dyFX[ii])); zero=fmax(zero,fabs(w.dx[ii])); }
+        LANE_FOR(i,nFR) zero=fmax(zero,fabs(w.dx[(int)w.FR[i]]));
+        weight=wbc_max(weight); zero=wbc_max(zero);
+        return zero>OPT_epsLITests*weight;
+    }
+    double l2=0.0; for(int i=0;i<nFR;i++){ double a=Ael(w.qp,number,(int)w.FR[i]); l2+=a*a; }
+    bool li=false;
+    LANE_FOR(j,nZ){ double sum=0.0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=Ael(w.qp,number,ii)*QQ(ii,j); } if(fabs(sum)>OPT_epsLITests*l2) li=true; }
+    return wbc_ballot(li)!=0u;
+}
+// QProblem::addBound_checkLI (QProblem.cpp:3487-3590)
+WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
+    const int lane=c.lane, nZ=c.nFR-c.nAC;
+    WBC_SYNC();
+    if(fullTest){
+        LANE_FOR(j,42) w.tmpv[j]=(j==number)?1.0:0.0;
+        WBC_SYNC();
+        int rv=determineStepDirection(w,c,w.tmpv,w.zero,w.zero,w.zero,w.zero,false,false);
+        if(rv!=QP_OK) return false;
+        double weight=0.0, zero=0.0;
+        LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
+        LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; weight=fmax(weight,fabs(w.dyFX[ii])); zero=fmax(zero,fabs(w.dx[ii])); }
+        LANE_FOR(i,c.nFR) zero=fmax(zero,fabs(w.dx[(int)w.FR[i]]));
+        weight=wbc_max(weight); zero=wbc_max(zero);
+        return zero>OPT_epsLITests*weight;
+    }
+    bool li=false; LANE_FOR(i,nZ) if(fabs(QQ(number,i))>OPT_epsLITests) li=true;
+    return wbc_ballot(li)!=0u;
+}
+
+// common tail of addConstraint_ensureLI / addBound_ensureLI (QProblem.cpp:3178-3300, 3658-3775): xiC in w.xFRy (AC position),
+// xiB in w.Zdz (variable number).  returns QP_OK, or QP_RET_HOTSTART_STOPPED_INFEASIBILITY if no index can leave.
+WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBound){
+    const int lane=c.lane, nAC=c.nAC, nFX=c.nFX;
+    double y_min=OPT_maxDualJump; int ymn=-1, ymnb=-1;
+    WBC_SYNC();
+    LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=w.xFRy[i]; }
+    performRatioTest(c,nAC,w.AC,w.cstat,w.num,w.den,y_min,ymn);
+    WBC_SYNC();
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.num[i]=w.y[ii]; w.den[i]=w.Zdz[ii]; }
+    performRatioTest(c,nFX,w.FX,w.bstat,w.num,w.den,y_min,ymnb);
+    bool ymIsBound=false; if(ymnb>=0){ ymn=ymnb; ymIsBound=true; }
+    if(ymn<0){ c.infeasible=1; return QP_RET_HOTSTART_STOPPED_INFEASIBILITY; }
+    WBC_SYNC();
+    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]-=y_min*w.xFRy[i]; }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.y[ii]-=y_min*w.Zdz[ii]; }
+    WBC_SYNC();
+    if(lane==0){ double v=(status==ST_LOWER)?y_min:-y_min; if(isBound) w.y[number]=v; else w.y[42+number]=v; }
+    WBC_SYNC();
+    int rv;
+    if(ymIsBound){ rv=removeBound(w,c,ymn); if(rv!=QP_OK) return rv; if(lane==0) w.y[ymn]=0.0; }
+    else { rv=removeConstraint(w,c,ymn); if(rv!=QP_OK) return rv; if(lane==0) w.y[42+ymn]=0.0; }
+    WBC_SYNC();
+    return QP_OK;
+}
+// QProblem::addConstraint_ensureLI (QProblem.cpp:3117-3300)
+WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
+    const int lane=c.lane;
+    if(addConstraint_checkLI(w,c,number,true)) return QP_OK;
+    const int nFR=c.nFR, nAC=c.nAC, nFX=c.nFX, nZ=nFR-nAC; const double sg=(C_status==ST_LOWER)?1.0:-1.0;
+    WBC_SYNC();
+    if(nAC>0){
+        LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*(sg*Ael(w.qp,number,jj)); } w.tB[i]=s; }
+        if(!backsolveT(w,c,w.tB,true,w.xFRy)) return QP_RET_UNSUPPORTED_PATH;
+    }
+    WBC_SYNC();
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=sg*Ael(w.qp,number,ii)-AcolT_dot(w,ii,w.xFRy); }
+    return ensureLI_exchange(w,c,number,C_status,false);
+}
+// QProblem::addBound_ensureLI (QProblem.cpp:3596-3780)
+WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
+    const int lane=c.lane;
+    if(addBound_checkLI(w,c,number,true)) return QP_OK;
+    const int nAC=c.nAC, nFX=c.nFX, nZ=c.nFR-nAC; const double sg=(B_status==ST_LOWER)?1.0:-1.0;
+    WBC_SYNC();
+    if(nAC>0){
+        LANE_FOR(i,nAC) w.tB[i]=sg*QQ(number,nZ+i);
+        if(!backsolveT(w,c,w.tB,true,w.xFRy)) return QP_RET_UNSUPPORTED_PATH;
+    }
+    WBC_SYNC();
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=0.0-AcolT_dot(w,ii,w.xFRy); }
+    return ensureLI_exchange(w,c,number,B_status,true);
+}
+
+// QProblem::addConstraint (QProblem.cpp:2819-2975)
+WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateCholesky,bool ensureLI){
+    const int lane=c.lane;
+    if(updateCholesky&&ensureLI){ int rv=addConstraint_ensureLI(w,c,number,C_status); if(rv!=QP_OK) return rv; }
+    const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    WBC_SYNC();
+    // row [wZ wY] = aFR' [Z Y]
+    LANE_FOR(j,nFR){ double s=0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; s+=Ael(w.qp,number,ii)*QQ(ii,j); }
+        if(j<nZ) w.wv[j]=s; else TT(nAC,tcol+(j-nZ))=s; }
+    if(nZ>0){
+        givens_chain(w,c,nZ-1);
+        apply_chain_Q(w,c,nZ-1,nFR);
+        if(lane==0) TT(nAC,tcol-1)=(nZ>1)?w.wv[nZ-1]:w.wv[0];
+    }
+    moveInactiveToActive(w,c,number,C_status);
+    return QP_OK;
+}
+// QProblem::addBound (QProblem.cpp:3307-3480)
+WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholesky,bool ensureLI){
+    const int lane=c.lane;
+    if(updateCholesky&&ensureLI){ int rv=addBound_ensureLI(w,c,number,B_status); if(rv!=QP_OK) return rv; }
+    const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    WBC_SYNC();
+    const int lastfree=(int)w.FR[nFR-1];
+    if(lastfree!=number) swapFree(w,c,number,lastfree);
+    LANE_FOR(i,nFR) w.wv[i]=QQ(number,i);
+    const int nrot=nFR-1;                          // j = 0 .. nFR-2 (the three loops of the reference are contiguous)
+    givens_chain(w,c,(nAC>0)?nrot:(nZ-1));
+    apply_chain_Q(w,c,(nAC>0)?nrot:(nZ-1),nFR);
+    if(nAC>0){
+        // T rows: rotation j >= nZ-1 touches rows i >= nFR-2-j at column 1+tcol-nZ+j, paired with the temporary column tmp
+        LANE_FOR(i,nAC){ double tmp=0.0; int j0=nFR-2-i; if(j0<nZ-1) j0=nZ-1;
+            for(int j=j0;j<=nFR-2;j++){ int col=1+tcol-nZ+j; double xo=TT(i,col), cc=w.cs_c[j], ss=w.cs_s[j];
+                double xn=cc*xo+ss*tmp, yn=-ss*xo+cc*tmp; tmp=xn; TT(i,col)=yn; } }
+    }
+    moveFreeToFixed(w,c,number,B_status);
+    return QP_OK;
+}
+// QProblem::removeConstraint (QProblem.cpp:3782-4012) without NZC test / flipper / R update (see file header)
+WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
+    const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    WBC_SYNC();
+    const int number_idx=(int)w.posAC[number];
+    if(number_idx<nAC-1){
+        // shift rows up; lane per column so that the upward copy is ordered inside one lane
+        LANE_FOR(j,nAC){ for(int i=number_idx+1;i<nAC;i++) if(j>=nAC-i-1) TT(i-1,tcol+j)=TT(i,tcol+j); TT(nAC-1,tcol+j)=0.0; }
+        for(int j=nAC-2-number_idx;j>=0;j--){
+            WBC_SYNC();
+            const int pr=nAC-2-j; double xn,yn,cc,ss; computeGivens(TT(pr,tcol+1+j),TT(pr,tcol+j),xn,yn,cc,ss);
+            WBC_SYNC();
+            if(lane==0){ TT(pr,tcol+1+j)=xn; TT(pr,tcol+j)=yn; }
+            for(int i=nAC-j-1+lane;i<nAC-1;i+=WBC_NL){ double xo=TT(i,tcol+1+j), yo=TT(i,tcol+j); TT(i,tcol+1+j)=cc*xo+ss*yo; TT(i,tcol+j)=-ss*xo+cc*yo; }
+            LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
+        }
+    } else { LANE_FOR(j,nAC) TT(nAC-1,tcol+j)=0.0; }
+    moveActiveToInactive(w,c,number);
+    return QP_OK;
+}
+// QProblem::removeBound (QProblem.cpp:4018-4252) without NZC test / flipper / R update (see file header)
+WBC_FN int removeBound(QPWork& w,QPCtx& c,int number){
+    const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    moveFixedToFree(w,c,number);
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; QQ(ii,nFR)=0.0; QQ(number,i)=0.0; }
+    WBC_SYNC();
+    if(lane==0) QQ(number,nFR)=1.0;
+    if(nAC>0){
+        LANE_FOR(i,nAC) w.tmpv[i]=Ael(w.qp,(int)w.AC[i],number);
+        for(int j=nAC-1;j>=0;j--){
+            WBC_SYNC();
+            const int pr=nAC-1-j; double xn,yn,cc,ss; computeGivens(w.tmpv[pr],TT(pr,tcol+j),xn,yn,cc,ss);
+            WBC_SYNC();
+            if(lane==0){ TT(pr,tcol+j)=xn; w.tmpv[pr]=yn; }
+            for(int i=nAC-j+lane;i<nAC;i+=WBC_NL){ double xo=w.tmpv[i], yo=TT(i,tcol+j); TT(i,tcol+j)=cc*xo+ss*yo; w.tmpv[i]=-ss*xo+cc*yo; }
+            LANE_FOR(i,nFR+1){ int ii=(int)w.FR[i]; double xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
+        }
+    }
+    WBC_SYNC();
+    return QP_OK;
+}
+
+// ---------------------------------------------------------------- homotopy
+// QProblem::changeActiveSet (QProblem.cpp:5284-5365)
+WBC_FN int changeActiveSet(QPWork& w,QPCtx& c,int BC_idx,int BC_status,bool BC_isBound){
+    int rv=QP_OK;
+    if(BC_status==2) return QP_OK;
+    if(BC_status==ST_INACTIVE){
+        if(BC_isBound){ rv=removeBound(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[BC_idx]=0.0; }
+        else { rv=removeConstraint(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[42+BC_idx]=0.0; }
+        WBC_SYNC();
+    } else {
+        if(BC_isBound) rv=addBound(w,c,BC_idx,BC_status,true,true);
+        else rv=addConstraint(w,c,BC_idx,BC_status,true,true);
+    }
+    return rv;
+}
+// QProblem::updateFarBounds (QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246); user bounds: none on x, w.qp.lbA/ubA on Ax
+WBC_DEV void updateFarBounds(QPWork& w,const QPCtx& c,double curFarBound){
+    const int lane=c.lane, nRamp=42+70; WBC_SYNC();
+    LANE_FOR(i,42){ double t=(double)((i+c.rampOffset)%nRamp)/(double)(nRamp-1); double rv=curFarBound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1); w.lbF[i]=-rv; w.ubF[i]=rv; }
+    LANE_FOR(i,70){ double t=(double)((42+i+c.rampOffset)%nRamp)/(double)(nRamp-1); double rv=curFarBound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1);
+        w.lbAF[i]=fmax(-rv,w.qp.lbA[i]); w.ubAF[i]=fmin(rv,w.qp.ubA[i]); }
+    WBC_SYNC();
+}
+// QProblem::solveQP (QProblem.cpp:1477-1747); nWSR in/out like the reference
+WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
+    if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
+    c.status=QPS_PERFORMINGHOMOTOPY;                 // updateActivitiesForHotstart: nothing to do, every far bound is finite
+    c.infeasible=0; c.unbounded=0;
+    for(int iter=nWSRperformed;iter<nWSR;iter++){
+        c.status=QPS_PERFORMINGHOMOTOPY;
+        bool bCzero,bBzero; determineDataShift(w,c,bCzero,bBzero);
+        int rv=determineStepDirection(w,c,w.dg,w.dlbA,w.dubA,w.dlb,w.dub,bCzero,bBzero);
+        if(rv!=QP_OK){ nWSR=iter; return rv; }
+        int BC_idx,BC_status; bool BC_isBound;
+        performStep(w,c,BC_idx,BC_status,BC_isBound);
+        const double hl=relativeHomotopyLength(w,c);
+        if(hl<=OPT_terminationTolerance){ c.status=QPS_SOLVED; nWSR=iter; return QP_OK; }
+        rv=changeActiveSet(w,c,BC_idx,BC_status,BC_isBound);
+        if(rv!=QP_OK){ nWSR=iter; if(c.infeasible){ c.status=QPS_HOMOTOPYQPSOLVED; return QP_RET_HOTSTART_STOPPED_INFEASIBILITY; } return rv; }
+        rv=computeProjectedCholesky(w,c);
+        if(rv!=QP_OK) return rv;
+        c.status=QPS_HOMOTOPYQPSOLVED;
+        if(BC_status!=2&&c.tau<=QEPS) performRamping(w,c); else performDriftCorrection(w,c);
+    }
+    return QP_RET_MAX_NWSR_REACHED;
+}
+// QProblem::hotstart (QProblem.cpp:446-640): far-bound outer loop
+WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
+    const int lane=c.lane; const int nWSR_max=nWSR; int nWSR_performed=0;
+    double farbound=OPT_initialFarBounds;
+    { double m=0.0; LANE_FOR(i,70){ double u=w.qp.ubA[i], l=w.qp.lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
+    updateFarBounds(w,c,farbound);
+    int rv;
+    for(;;){
+        nWSR=nWSR_max;
+        rv=solveQP(w,c,nWSR,nWSR_performed);
+        nWSR_performed=nWSR;
+        farbound*=OPT_growFarBounds;
+        if(c.infeasible){
+            if(farbound>=QINFTY){ rv=QP_RET_HOTSTART_STOPPED_INFEASIBILITY; break; }
+            updateFarBounds(w,c,farbound);
+        } else if(c.status==QPS_SOLVED){
+            const double tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
+            LANE_FOR(i,42){ if(fabs(w.lbF[i]-w.x[i])<tol) na++; if(fabs(w.ubF[i]-w.x[i])<tol) na++; }
+            LANE_FOR(i,70){ if(w.lbAF[i]>w.qp.lbA[i]&&fabs(w.lbAF[i]-w.Ax[i])<tol) na++; if(w.ubAF[i]<w.qp.ubA[i]&&fabs(w.ubAF[i]-w.Ax[i])<tol) na++; }
+            if(wbc_ballot(na>0)==0u) break;
+            c.status=QPS_HOMOTOPYQPSOLVED;
+            if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
+            updateFarBounds(w,c,farbound);
+        } else break;
+        c.rampOffset++;
+    }
+    return rv;
+}
+// SQProblem/QProblem::init -> solveInitialQP (QProblem.cpp:316-368, 1301-1471): cold start from x = y = 0 with every variable
+// fixed at its (far) lower bound (initialStatusBounds = ST_LOWER) and no active constraint.
+WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
+    const int lane=c.lane; WBC_SYNC();
+    LANE_FOR(i,42){ w.x[i]=0.0; w.y[i]=0.0; w.g[i]=0.0; w.lb[i]=0.0; w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; w.zero[i]=0.0; }
+    LANE_FOR(i,70){ w.y[42+i]=0.0; w.Ax[i]=0.0; w.lbA[i]=-OPT_boundRelaxation; w.ubA[i]=OPT_boundRelaxation; w.Ax_l[i]=OPT_boundRelaxation; w.Ax_u[i]=OPT_boundRelaxation;
+                    w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; w.zero[i]=0.0; }
+    c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=0.0;
+    setupTQfactorisation(w,c);
+    c.status=QPS_AUXILIARYQPSOLVED;
+    performRamping(w,c);
+    int rv=computeProjectedCholesky(w,c);                    // setupInitialCholesky
+    if(rv!=QP_OK) return QP_RET_INIT_FAILED_CHOLESKY;
+    rv=hotstartFar(w,c,nWSR);
+    if(c.infeasible) return QP_RET_INIT_FAILED_INFEASIBILITY;
+    if(c.unbounded) return QP_RET_INIT_FAILED_UNBOUNDEDNESS;
+    if(rv!=QP_OK&&rv!=QP_RET_MAX_NWSR_REACHED) return QP_RET_INIT_FAILED_HOTSTART;
+    return rv;
+}
+// SQProblem::hotstart -> setupNewAuxiliaryQP (SQProblem.cpp:153-197, 340-515) then QProblem::hotstart.
+// On entry w.x, w.y, w.lb, w.ub, w.Ax_l, w.Ax_u, w.bstat, w.cstat hold the previous tick's solver state.
+WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
+    const int lane=c.lane;
+    if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
+    c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
+    LANE_FOR(i,70){ w.zero[i]=0.0; double ax=Arow_dot(w,i,w.x,2); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    setupAuxiliaryQPgradient(w,c);
+    // old working set (statuses), then everything free / inactive again
+    bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;
+    if(wbc_ballot(anyFixed)!=0u) return QP_RET_SETUP_AUXILIARYQP_FAILED;     // addBound on an ST_UNBOUNDED-typed variable: RET_ALL_BOUNDS_ACTIVE
+    LANE_FOR(i,42){ w.FR[i]=(signed char)i; }
+    LANE_FOR(i,70){ w.IAC[i]=(signed char)i; w.num[i]=(double)w.cstat[i]; }      // park the old statuses in w.num
+    WBC_SYNC();
+    LANE_FOR(i,70) w.cstat[i]=ST_INACTIVE;
+    c.nFR=42; c.nFX=0; c.nAC=0; c.nIAC=70;
+    setupTQfactorisation(w,c);
+    // setupAuxiliaryWorkingSet(old, setupAfresh): re-add the old active constraints in ascending order, cheap LI test, no LI exchange
+    for(int i=0;i<70;i++){
+        const int os=(int)w.num[i];
+        if(os==ST_INACTIVE) continue;
+        if(addConstraint_checkLI(w,c,i,false)){ int rv=addConstraint(w,c,i,os,false,false); if(rv!=QP_OK) return QP_RET_SETUP_AUXILIARYQP_FAILED; }
+    }
+    int rv=computeProjectedCholesky(w,c);
+    if(rv!=QP_OK) return QP_RET_UNSUPPORTED_PATH;
+    c.status=QPS_AUXILIARYQPSOLVED;
+    return hotstartFar(w,c,nWSR);
+}
+
+}  // namespace wbc

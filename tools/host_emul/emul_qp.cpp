@@ -1,0 +1,18 @@
+// DEVELOPMENT AID ONLY -- not part of the shipped library (see emul_rbd.cpp).  One emulated lane.
+#include "../../quadrupedwholebodycontroller_b200/csrc/wbc_qp.cuh"
+#include <cstring>
+#include <cstdio>
+using namespace wbc;
+
+struct EmulQP { QPWork w; QPCtx c; };
+extern "C" void* emulqp_create(){ EmulQP* e=new EmulQP; memset(e,0,sizeof(*e)); e->c.lane=0; e->c.status=QPS_NOTINITIALISED; return e; }
+extern "C" void emulqp_destroy(void* h){ delete (EmulQP*)h; }
+// first != 0: init (cold), else hotstart.  outputs: x[42], y[112], ws[112], returns rc; *nwsr in/out
+extern "C" int emulqp_solve(void* h,const double* qpdata,int first,int* nwsr,double* x,double* y,signed char* ws){
+    EmulQP* e=(EmulQP*)h; memcpy(&e->w.qp,qpdata,sizeof(QPData));
+    int n=*nwsr; int rc= first? qp_init(e->w,e->c,n) : qp_hotstart(e->w,e->c,n);
+    *nwsr=n;
+    memcpy(x,e->w.x,42*8); memcpy(y,e->w.y,112*8);
+    for(int i=0;i<42;i++) ws[i]=e->w.bstat[i]; for(int i=0;i<70;i++) ws[42+i]=e->w.cstat[i];
+    return rc;
+}
