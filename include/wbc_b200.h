@@ -1,0 +1,103 @@
+/* wbc_b200.h -- C ABI of the batched ANYmal whole-body controller for NVIDIA B200 (sm_100a).
+ *
+ * Drop-in boundary for ONE hot path of Mavagnale/QuadrupedWholeBodyController: the body of the 400 Hz control loop
+ *     updateState(); solveQP(); computeJointTorques();          (reference src/whole_body_controller.cpp:650-652)
+ * evaluated for a batch of N independent robots on one GPU.  Every entry point below names the reference interface it
+ * replaces (paths relative to the reference repository).  There is no CPU fallback: every call fails with
+ * WBC_ERR_CUDA if no sm_100-class device is usable.
+ *
+ * Array convention: structure-of-arrays, instance index fastest -- element k of robot i is a[k*N + i]; fp64; flags are
+ * bytes.  Pointers may be HOST or DEVICE pointers (detected with cudaPointerGetAttributes); host buffers are copied
+ * with cudaMemcpyAsync on the handle's stream.  The caller owns its buffers, the library owns all per-robot
+ * persistent state (finite-difference history, integral error, QP warm-start state) in device memory.
+ * Threading: one handle = one host thread at a time; handles are independent.
+ *
+ * Orders fixed by the reference: joints/DOFs LH_HAA,LH_HFE,LH_KFE, LF_*, RF_*, RH_* (whole_body_controller.cpp:81,234;
+ * config/controllers.yaml:8-19); legs / contacts / ground-reaction forces LH, LF, RF, RH (:327-341);
+ * QP variables x[42] = [CoM acc(6) | joint acc(12) | contact forces(12) | slacks(12)] (whole_body_controller.hpp:31).
+ */
+#ifndef WBC_B200_H
+#define WBC_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WBC_NUM_JOINTS 12          /* whole_body_controller.hpp:27 numberOfJoints          */
+#define WBC_NUM_LEGS 4             /* whole_body_controller.hpp:28 numberOfLegs            */
+#define WBC_QP_NV 42               /* whole_body_controller.hpp:31 qpNumberOfVariables     */
+#define WBC_QP_NC 70               /* whole_body_controller.hpp:32 qpNumberOfConstraints   */
+
+#define WBC_OK 0
+#define WBC_ERR_ARG (-1)
+#define WBC_ERR_CUDA (-2)
+#define WBC_ERR_NOMEM (-3)
+
+/* per-robot solver status values are qpOASES returnValue numbers (lib/qpOASES/include/qpOASES/MessageHandling.hpp):
+ * 0 SUCCESSFUL_RETURN, 64 RET_MAX_NWSR_REACHED, 37 RET_INIT_FAILED_INFEASIBILITY, 61 RET_HOTSTART_STOPPED_INFEASIBILITY ... */
+
+typedef struct wbc_handle wbc_handle;
+
+/* Replaces WholeBodyController::params / loadParameters (whole_body_controller.hpp:91-104, whole_body_controller.cpp:122-148,
+ * config/params_controller.yaml).  Shared by the whole batch. */
+typedef struct wbc_params {
+    double friction, loopRate, maxTorque, kpValue, kpValueZ, kdValue, kiValue, kpSwingValue, kdSwingValue, slackWeight;
+    double initialReferencePose[6];
+} wbc_params;
+
+/* config/params_controller.yaml:1-11 */
+void wbc_default_params(wbc_params* p);
+
+/* Replaces WholeBodyController::WholeBodyController() (whole_body_controller.cpp:22-59): model "load" (the 13-body ANYmal
+ * table compiled from urdf/anymal.urdf is baked into the library), SQProblem(42,70) construction, loadParameters,
+ * setInitialState.  device = CUDA ordinal.  stream = a cudaStream_t (as void*) to run on, or NULL for a private stream. */
+int wbc_create(int n_robots, int device, const wbc_params* params, void* stream, wbc_handle** out);
+int wbc_destroy(wbc_handle* h);                                   /* ~WholeBodyController (whole_body_controller.cpp:61-63) */
+
+/* Replaces setInitialState() (whole_body_controller.cpp:65-120) for robots [first, first+count): contacts 1111, nominal joint
+ * configuration, base at z = 0.60, references = initialReferencePose, old T = I, old Jacobians = 0, integral error = 0,
+ * firstControllerIteration_ = true (next solve is SQProblem::init).  Tdot^-1 (uninitialised upstream) is defined as 0. */
+int wbc_reset(wbc_handle* h, int first, int count);
+
+/* Replaces jointStateCallback (whole_body_controller.cpp:232-254; q, qd already in model DOF order) and
+ * floatingBaseStateCallback (:187-230): base position[3], orientation quaternion (w,x,y,z)[4] (Eigen toRotationMatrix, not
+ * normalised), base twist[6] = [linear world; angular world]. */
+int wbc_set_state(wbc_handle* h, const double* q, const double* qd, const double* base_pos, const double* base_quat_wxyz,
+                  const double* base_twist);
+
+/* Replaces referenceCallback (whole_body_controller.cpp:150-185; msg/WbcReferenceMsg.msg): desired CoM pose[6] = [xyz; rpy],
+ * velocity[6], acceleration[6], swing-leg position/velocity/acceleration[12], footContacts[4] (bytes, leg-major: c[l*N+i]).
+ * switching[N] (bytes) = isSwitchingFootState_; NULL derives it from the previous contacts exactly like :176-184. */
+int wbc_set_reference(wbc_handle* h, const double* pose, const double* vel, const double* acc, const double* sw_pos,
+                      const double* sw_vel, const double* sw_acc, const unsigned char* contacts, const unsigned char* switching);
+
+/* The three hot methods, batched (whole_body_controller.hpp:47,54,52; whole_body_controller.cpp:256-294, 466-542, 553-577).
+ * Robots whose previous solve did not return 0 are halted like the reference's control loop (:654-659): they keep their
+ * status, output zero torques (terminate(), :626-635) and are skipped until wbc_reset. */
+int wbc_update_state(wbc_handle* h);
+int wbc_solve_qp(wbc_handle* h);
+int wbc_compute_joint_torques(wbc_handle* h);
+int wbc_step(wbc_handle* h);                                     /* the three calls above, asynchronous on the stream */
+int wbc_synchronize(wbc_handle* h);
+
+/* Replaces the publishers (whole_body_controller.cpp:558-576, 666-670) and quadraticProblem_ getters: joint torques tau[12],
+ * desired ground reaction forces grf[12], x[42], qpReturnValue_ rc[N], working-set recalculations nwsr[N], working set
+ * ws[112] in {-1,0,+1} (QProblem::getWorkingSet: 42 bounds then 70 constraints), CoM position com[3].  Any pointer may be NULL.
+ * Synchronises the stream when a HOST pointer is given. */
+int wbc_get_outputs(wbc_handle* h, double* tau, double* grf, double* x, int* rc, int* nwsr, signed char* ws, double* com);
+
+/* Test / inspection hook: the dense QP of robot i as the reference would hand it to qpOASES (row-major H[42*42], g[42],
+ * A[70*42], lbA[70], ubA[70]; whole_body_controller.cpp:479-515), expanded on the host from the compact device form. */
+int wbc_get_dense_qp(wbc_handle* h, int robot, double* H, double* g, double* A, double* lbA, double* ubA);
+
+int wbc_num_robots(const wbc_handle* h);
+/* number of kernel launches issued by this handle so far (bench.py reports it as gpu_launches) */
+long long wbc_launch_count(const wbc_handle* h);
+/* duration [ms] of the most recent wbc_solve_qp kernel measured with CUDA events on the handle's stream (synchronises) */
+int wbc_last_kernel_ms(wbc_handle* h, float* rbd_ms, float* qp_ms, float* torque_ms);
+const char* wbc_last_error(const wbc_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WBC_B200_H */

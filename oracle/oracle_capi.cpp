@@ -7,6 +7,7 @@
 #include <thread>
 #include <atomic>
 #include <chrono>
+#include <cstdlib>
 
 using namespace oracle;
 
@@ -122,7 +123,7 @@ void orc_qp_sequence(int T,const double* H,const double* g,const double* A,const
                      double* x,double* y,signed char* ws,int* rc,int* nwsr){
     qpOASES::SQProblem qp(42,70);
     for(int t=0;t<T;t++){
-        qpOASES::int_t nWSR=nWSRmax; qpOASES::Options o; o.setToReliable(); o.printLevel=qpOASES::PL_LOW; qp.setOptions(o);
+        qpOASES::int_t nWSR=nWSRmax; qpOASES::Options o; o.setToReliable(); o.printLevel=getenv("ORC_PRINT")?qpOASES::PL_MEDIUM:qpOASES::PL_LOW; qp.setOptions(o);
         int r = (t==0) ? qp.init(H+t*1764,g+t*42,A+t*2940,nullptr,nullptr,lbA+t*70,ubA+t*70,nWSR,0)
                        : qp.hotstart(H+t*1764,g+t*42,A+t*2940,nullptr,nullptr,lbA+t*70,ubA+t*70,nWSR,0);
         rc[t]=r; nwsr[t]=(int)nWSR;

@@ -1,0 +1,147 @@
+"""Batched ANYmal whole-body controller for NVIDIA B200 (sm_100a) -- Python binding of the C ABI (include/wbc_b200.h).
+
+The product is the CUDA shared library `libwbc_b200.so` (csrc/wbc_kernels.cu); this module is a thin ctypes front-end used by
+the tests and bench.py.  The host-language mirror of the reference's C++ class lives in csrc/whole_body_controller.hpp.
+There is no CPU fallback: constructing a controller without the library or without a CUDA device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .build import build_library, LIB_PATH
+
+NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC = 12, 4, 42, 70          # whole_body_controller.hpp:27-32 of the reference
+_lib = None
+
+EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
+           "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
+           "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_last_error"]
+
+
+class WbcParams(C.Structure):
+    """wbc_params == WholeBodyController::params (reference whole_body_controller.hpp:91-104)."""
+    _fields_ = [(k, C.c_double) for k in ("friction", "loopRate", "maxTorque", "kpValue", "kpValueZ", "kdValue", "kiValue",
+                                          "kpSwingValue", "kdSwingValue", "slackWeight")] + [("initialReferencePose", C.c_double * 6)]
+
+
+def load_library():
+    """dlopen the CUDA library; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
+                               "The controller has no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        lib.wbc_create.argtypes = [C.c_int, C.c_int, C.POINTER(WbcParams), C.c_void_p, C.POINTER(C.c_void_p)]
+        for name in ("wbc_destroy", "wbc_update_state", "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize"):
+            getattr(lib, name).argtypes = [C.c_void_p]
+        lib.wbc_reset.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        lib.wbc_set_state.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        lib.wbc_set_reference.argtypes = [C.c_void_p] + [C.c_void_p] * 8
+        lib.wbc_get_outputs.argtypes = [C.c_void_p] + [C.c_void_p] * 7
+        lib.wbc_get_dense_qp.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5
+        lib.wbc_num_robots.argtypes = [C.c_void_p]
+        lib.wbc_launch_count.argtypes = [C.c_void_p]; lib.wbc_launch_count.restype = C.c_longlong
+        lib.wbc_last_kernel_ms.argtypes = [C.c_void_p] + [C.POINTER(C.c_float)] * 3
+        lib.wbc_last_error.argtypes = [C.c_void_p]; lib.wbc_last_error.restype = C.c_char_p
+        lib.wbc_default_params.argtypes = [C.POINTER(WbcParams)]
+        _lib = lib
+    return _lib
+
+
+def default_params():
+    p = WbcParams(); load_library().wbc_default_params(C.byref(p)); return p
+
+
+def _ptr(a):
+    """numpy array -> host pointer; torch CUDA tensor -> device pointer; int -> raw pointer; None -> NULL."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data_as(C.c_void_p)
+    if hasattr(a, "data_ptr"):
+        assert a.is_contiguous()
+        return C.c_void_p(a.data_ptr())
+    raise TypeError(type(a))
+
+
+class WholeBodyController:
+    """Batch of N independent reference-equivalent controllers on one GPU.
+
+    Method names follow the reference class (updateState / solveQP / computeJointTorques); the three ROS callbacks become
+    setJointAndBaseState / setReference.  Arrays are (K, N) C-contiguous float64 (uint8 for flags): numpy (host) or torch CUDA.
+    """
+
+    numberOfJoints, numberOfLegs, qpNumberOfVariables, qpNumberOfConstraints = NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC
+
+    def __init__(self, n_robots, device=0, params=None, stream=None):
+        lib = load_library()
+        self.N = int(n_robots)
+        self._h = C.c_void_p()
+        p = params if params is not None else default_params()
+        rc = lib.wbc_create(self.N, int(device), C.byref(p), C.c_void_p(stream) if stream else None, C.byref(self._h))
+        if rc != 0:
+            self._h = C.c_void_p()
+            raise RuntimeError(f"wbc_create failed with {rc} (CUDA device {device} unusable? there is no CPU fallback)")
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError(f"wbc error {rc}: {load_library().wbc_last_error(self._h).decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            load_library().wbc_destroy(self._h); self._h = C.c_void_p()
+
+    __del__ = close
+
+    def setInitialState(self, first=0, count=None):
+        self._ck(load_library().wbc_reset(self._h, first, self.N - first if count is None else count))
+
+    def setJointAndBaseState(self, q, qd, base_pos, base_quat, base_twist):
+        self._ck(load_library().wbc_set_state(self._h, _ptr(q), _ptr(qd), _ptr(base_pos), _ptr(base_quat), _ptr(base_twist)))
+
+    def setReference(self, pose, vel, acc, sw_pos, sw_vel, sw_acc, contacts, switching=None):
+        self._ck(load_library().wbc_set_reference(self._h, _ptr(pose), _ptr(vel), _ptr(acc), _ptr(sw_pos), _ptr(sw_vel), _ptr(sw_acc),
+                                                  _ptr(contacts), _ptr(switching)))
+
+    def updateState(self):
+        self._ck(load_library().wbc_update_state(self._h))
+
+    def solveQP(self):
+        self._ck(load_library().wbc_solve_qp(self._h))
+
+    def computeJointTorques(self):
+        self._ck(load_library().wbc_compute_joint_torques(self._h))
+
+    def step(self):
+        self._ck(load_library().wbc_step(self._h))
+
+    def synchronize(self):
+        self._ck(load_library().wbc_synchronize(self._h))
+
+    def getOutputs(self, tau=None, grf=None, x=None, rc=None, nwsr=None, ws=None, com=None):
+        """copies into the given buffers (host or device); with no argument returns fresh numpy arrays of everything."""
+        if all(v is None for v in (tau, grf, x, rc, nwsr, ws, com)):
+            N = self.N
+            o = dict(tau=np.zeros((12, N)), grf=np.zeros((12, N)), x=np.zeros((42, N)), rc=np.zeros(N, np.int32), nwsr=np.zeros(N, np.int32),
+                     ws=np.zeros((112, N), np.int8), com=np.zeros((3, N)))
+            self._ck(load_library().wbc_get_outputs(self._h, *[_ptr(o[k]) for k in ("tau", "grf", "x", "rc", "nwsr", "ws", "com")]))
+            return o
+        self._ck(load_library().wbc_get_outputs(self._h, _ptr(tau), _ptr(grf), _ptr(x), _ptr(rc), _ptr(nwsr), _ptr(ws), _ptr(com)))
+
+    def denseQP(self, robot):
+        o = dict(H=np.zeros((42, 42)), g=np.zeros(42), A=np.zeros((70, 42)), lbA=np.zeros(70), ubA=np.zeros(70))
+        self._ck(load_library().wbc_get_dense_qp(self._h, robot, *[_ptr(o[k]) for k in ("H", "g", "A", "lbA", "ubA")]))
+        return o
+
+    def launchCount(self):
+        return int(load_library().wbc_launch_count(self._h))
+
+    def lastKernelMs(self):
+        a, b, c = C.c_float(), C.c_float(), C.c_float()
+        self._ck(load_library().wbc_last_kernel_ms(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(update_state=a.value, solve_qp=b.value, compute_joint_torques=c.value)

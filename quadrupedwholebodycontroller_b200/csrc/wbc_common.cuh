@@ -13,6 +13,7 @@
 
 #if defined(__CUDACC__)
   #define WBC_DEV __device__ __forceinline__
+  #define WBC_HD  __host__ __device__ __forceinline__
   #define WBC_FN  __device__ __noinline__
   #define WBC_NL 32
   #define WBC_SYNC() __syncwarp()
@@ -23,6 +24,7 @@
   WBC_DEV int    wbc_ffs(unsigned m){ return __ffs(m)-1; }
 #else
   #define WBC_DEV static inline
+  #define WBC_HD  static inline
   #define WBC_FN  static
   #define WBC_NL 1
   #define WBC_SYNC() do{}while(0)

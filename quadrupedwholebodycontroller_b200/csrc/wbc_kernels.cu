@@ -1,0 +1,321 @@
+// CUDA kernels (sm_100a) + C ABI of the batched ANYmal whole-body controller.  See include/wbc_b200.h.
+// One robot instance per warp, one warp per CTA (shared-memory bound: the solver keeps Q, R, T and all vectors of its
+// instance in ~57 KB of shared memory), persistent CTAs pulling instances from an atomic work counter so that robots
+// that need 100 working-set changes do not hold up robots that need none.
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/wbc_b200.h"
+#include "wbc_assembly.cuh"
+#include "wbc_qp.cuh"
+#include "anymal_model.h"
+
+using namespace wbc;
+
+// ---------------------------------------------------------------- device-side batch views
+struct BatchIn {      // SoA, instance index fastest
+    const double *q,*qd,*pos,*quat,*twist,*pose,*vel,*acc,*swp,*swv,*swa;
+    const unsigned char *contacts,*switching;
+};
+struct BatchOut { double *tau,*grf,*x,*com; int *rc,*nwsr; signed char* ws; };
+
+__constant__ ModelConst c_model;
+
+// ---------------------------------------------------------------- kernel 1: RBD + centroidal transform + QP assembly
+// grid-stride over instances; the RBD stage is ~40 kFLOP per robot, far below the solver's cost
+__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,const int* rc,double* com){
+    __shared__ ModelConst mc;
+    __shared__ RbdScratch s;
+    __shared__ QPData qp;
+    const int lane=threadIdx.x;
+    { const double* src=(const double*)&c_model; double* dst=(double*)&mc; LANE_FOR(i,MODEL_DOUBLES) dst[i]=src[i]; }
+    WBC_SYNC();
+    for(int r=blockIdx.x;r<N;r+=gridDim.x){
+        if(rc[r]!=0&&!first[r]) continue;                          // halted robot (wbc.cpp:654-659)
+        LANE_FOR(k,12){ s.q[k]=in.q[k*N+r]; s.qd[k]=in.qd[k*N+r]; s.swp[k]=in.swp[k*N+r]; s.swv[k]=in.swv[k*N+r]; s.swa[k]=in.swa[k*N+r]; }
+        LANE_FOR(k,6){ s.twist[k]=in.twist[k*N+r]; s.pose_d[k]=in.pose[k*N+r]; s.vel_d[k]=in.vel[k*N+r]; s.acc_d[k]=in.acc[k*N+r]; }
+        LANE_FOR(k,3) s.pb[k]=in.pos[k*N+r];
+        LANE_FOR(k,4) s.cmask[k]=in.contacts[k*N+r]?1.0:0.0;
+        if(lane==0){ double qu[4]={in.quat[r],in.quat[N+r],in.quat[2*N+r],in.quat[3*N+r]}; quat_to_R(qu,s.Rwb); }
+        WBC_SYNC();
+        if(lane==0){ mtv3(s.Rwb,s.twist,s.vbody); mtv3(s.Rwb,s.twist+3,s.vbody+3); }   // MIXED -> body-fixed (KDC.cpp:822-825)
+        WBC_SYNC();
+        if(lane<4) rbd_leg(mc,s,lane);
+        WBC_SYNC();
+        wbc_assemble(mc,prm,s,st[r],qp,lane,(int)in.switching[r],(int)first[r]);
+        { const double* src=(const double*)&qp; double* dst=(double*)&qpd[r]; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
+        LANE_FOR(k,3) com[k*N+r]=s.com[k];
+        WBC_SYNC();
+    }
+}
+
+// ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart)
+__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax){
+    extern __shared__ double smem[];
+    QPWork& w=*reinterpret_cast<QPWork*>(smem);
+    const int lane=threadIdx.x;
+    for(;;){
+        int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
+        if(r>=N) break;
+        const bool isFirst=first[r]!=0;
+        if(!isFirst&&out.rc[r]!=0) continue;                       // halted robot
+        { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
+        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+        QPState& S=qs[r];
+        if(!isFirst){
+            LANE_FOR(i,42){ w.x[i]=S.x[i]; w.lb[i]=S.lb[i]; w.ub[i]=S.ub[i]; w.bstat[i]=S.bstat[i]; }
+            LANE_FOR(i,112) w.y[i]=S.y[i];
+            LANE_FOR(i,70){ w.Ax_l[i]=S.Ax_l[i]; w.Ax_u[i]=S.Ax_u[i]; w.cstat[i]=S.cstat[i]; }
+            c.rampOffset=S.rampOffset; c.status=S.status;
+        }
+        WBC_SYNC();
+        int nWSR=nWSRmax;
+        const int rcv= isFirst? qp_init(w,c,nWSR) : qp_hotstart(w,c,nWSR);
+        WBC_SYNC();
+        LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; out.x[i*N+r]=w.x[i]; out.ws[i*N+r]=w.bstat[i]; }
+        LANE_FOR(i,112) S.y[i]=w.y[i];
+        LANE_FOR(i,70){ S.Ax_l[i]=w.Ax_l[i]; S.Ax_u[i]=w.Ax_u[i]; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; }
+        if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0; }
+        WBC_SYNC();
+    }
+}
+
+// ---------------------------------------------------------------- kernel 3: torque recovery (wbc.cpp:553-577)
+// tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*;  a robot whose QP failed publishes zero torques (terminate(), :626-635)
+__global__ void wbc_compute_torques_kernel(int N,const QPData* qpd,BatchOut out){
+    const int r=blockIdx.x*blockDim.x+threadIdx.x;
+    if(r>=N) return;
+    const QPData& q=qpd[r];
+    const bool ok=out.rc[r]==0;
+    double xs[24]; for(int k=0;k<24;k++) xs[k]=out.x[(6+k)*N+r];
+    for(int i=0;i<12;i++){
+        double s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*xs[j];
+        double t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*xs[12+j];
+        out.tau[i*N+r]= ok? (s+q.biasj[i]-t) : 0.0;
+        out.grf[i*N+r]= xs[12+i];
+    }
+}
+
+// wbc.cpp:176-184: isSwitchingFootState_ = (contacts != previous message's contacts); also rolls prev <- current
+__global__ void wbc_derive_switching_kernel(int N,const unsigned char* contacts,unsigned char* prev,unsigned char* switching,int derive){
+    const int r=blockIdx.x*blockDim.x+threadIdx.x;
+    if(r>=N) return;
+    bool sw=false; for(int l=0;l<4;l++){ unsigned char c=contacts[l*N+r]?1:0; if(prev[l*N+r]!=c) sw=true; prev[l*N+r]=c; }
+    if(derive) switching[r]=sw?1:0;
+}
+// setInitialState (wbc.cpp:65-120) for robots [first, first+count)
+__global__ void wbc_reset_kernel(int N,Params prm,int first,int count,double* q,double* qd,double* pos,double* quat,double* twist,double* pose,double* vel,double* acc,
+                                 double* swp,double* swv,double* swa,unsigned char* contacts,unsigned char* prevc,unsigned char* switching,
+                                 unsigned char* firstflag,int* rc,int* nwsr,double* tau,double* grf,double* x){
+    const int r=first+blockIdx.x*blockDim.x+threadIdx.x;
+    if(r>=first+count||r>=N) return;
+    const double q0[12]={0.0,-0.4,0.8, 0.0,0.4,-0.8, 0.0,0.4,-0.8, 0.0,-0.4,0.8};
+    for(int k=0;k<12;k++){ q[k*N+r]=q0[k]; qd[k*N+r]=0; swp[k*N+r]=0; swv[k*N+r]=0; swa[k*N+r]=0; tau[k*N+r]=0; grf[k*N+r]=0; }
+    for(int k=0;k<6;k++){ twist[k*N+r]=0; pose[k*N+r]=prm.refPose[k]; vel[k*N+r]=0; acc[k*N+r]=0; }
+    pos[r]=0; pos[N+r]=0; pos[2*N+r]=0.60; quat[r]=1; quat[N+r]=0; quat[2*N+r]=0; quat[3*N+r]=0;
+    for(int l=0;l<4;l++){ contacts[l*N+r]=1; prevc[l*N+r]=1; }
+    for(int k=0;k<42;k++) x[k*N+r]=0;                               // qpSolution_.setZero() (wbc.cpp:58)
+    switching[r]=0; firstflag[r]=1; rc[r]=0; nwsr[r]=0;
+}
+
+// ================================================================= host side: C ABI (include/wbc_b200.h)
+struct wbc_handle {
+    int N=0, device=0; cudaStream_t stream=nullptr; bool ownStream=false;
+    wbc_params params; Params devParams;
+    // inputs (device, SoA)
+    double *q=nullptr,*qd=nullptr,*pos=nullptr,*quat=nullptr,*twist=nullptr,*pose=nullptr,*vel=nullptr,*acc=nullptr,*swp=nullptr,*swv=nullptr,*swa=nullptr;
+    unsigned char *contacts=nullptr,*prevc=nullptr,*switching=nullptr,*first=nullptr;
+    // persistent per-robot state and intermediates
+    CtrlState* ctrl=nullptr; QPData* qpd=nullptr; QPState* qps=nullptr; int* counter=nullptr;
+    // outputs
+    double *tau=nullptr,*grf=nullptr,*x=nullptr,*com=nullptr; int *rc=nullptr,*nwsr=nullptr; signed char* ws=nullptr;
+    cudaEvent_t ev[4]={nullptr,nullptr,nullptr,nullptr};
+    int smCount=0, qpBlocksPerSM=1; size_t qpSmem=0;
+    long long launches=0;
+    std::string err;
+};
+
+#define CK(call) do{ cudaError_t e_=(call); if(e_!=cudaSuccess){ h->err=std::string(#call)+": "+cudaGetErrorString(e_); return WBC_ERR_CUDA; } }while(0)
+
+static bool is_device_ptr(const void* p){
+    cudaPointerAttributes a; if(cudaPointerGetAttributes(&a,p)!=cudaSuccess){ cudaGetLastError(); return false; }
+    return a.type==cudaMemoryTypeDevice||a.type==cudaMemoryTypeManaged;
+}
+static int copy_in(wbc_handle* h,void* dst,const void* src,size_t bytes){
+    if(!src) return WBC_OK;
+    CK(cudaMemcpyAsync(dst,src,bytes,is_device_ptr(src)?cudaMemcpyDeviceToDevice:cudaMemcpyHostToDevice,h->stream));
+    return WBC_OK;
+}
+static int copy_out(wbc_handle* h,void* dst,const void* src,size_t bytes,bool& hostSeen){
+    if(!dst) return WBC_OK;
+    const bool dev=is_device_ptr(dst); if(!dev) hostSeen=true;
+    CK(cudaMemcpyAsync(dst,src,bytes,dev?cudaMemcpyDeviceToDevice:cudaMemcpyDeviceToHost,h->stream));
+    return WBC_OK;
+}
+
+extern "C" void wbc_default_params(wbc_params* p){
+    if(!p) return;
+    p->friction=1.0; p->loopRate=400.0; p->maxTorque=80.0; p->kpValue=6000.0; p->kpValueZ=10000.0; p->kdValue=1800.0; p->kiValue=0.0;
+    p->kpSwingValue=250.0; p->kdSwingValue=20.0; p->slackWeight=1000.0;
+    const double r[6]={0.0,0.0,0.5,0.0,0.0,0.0}; for(int i=0;i<6;i++) p->initialReferencePose[i]=r[i];
+}
+
+template<class T> static cudaError_t dalloc(T*& p,size_t n){ return cudaMalloc((void**)&p,n*sizeof(T)); }
+
+extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream,wbc_handle** out){
+    if(!out||n<=0) return WBC_ERR_ARG;
+    *out=nullptr;
+    wbc_handle* h=new wbc_handle; h->N=n; h->device=device;
+    if(params) h->params=*params; else wbc_default_params(&h->params);
+    auto fail=[&](int code){ fprintf(stderr,"wbc_create failed: %s\n",h->err.c_str()); wbc_destroy(h); return code; };
+    cudaError_t e=cudaSetDevice(device);
+    if(e!=cudaSuccess){ h->err=std::string("cudaSetDevice: ")+cudaGetErrorString(e)+" (no CPU fallback exists)"; int c=WBC_ERR_CUDA; fprintf(stderr,"wbc_create failed: %s\n",h->err.c_str()); delete h; return c; }
+    cudaDeviceProp prop; if(cudaGetDeviceProperties(&prop,device)!=cudaSuccess){ h->err="cudaGetDeviceProperties failed"; return fail(WBC_ERR_CUDA); }
+    h->smCount=prop.multiProcessorCount;
+    if(stream){ h->stream=(cudaStream_t)stream; h->ownStream=false; }
+    else { if(cudaStreamCreateWithFlags(&h->stream,cudaStreamNonBlocking)!=cudaSuccess){ h->err="cudaStreamCreate failed"; return fail(WBC_ERR_CUDA); } h->ownStream=true; }
+    const size_t N=(size_t)n; bool ok=true;
+    ok=ok&&dalloc(h->q,12*N)==cudaSuccess&&dalloc(h->qd,12*N)==cudaSuccess&&dalloc(h->pos,3*N)==cudaSuccess&&dalloc(h->quat,4*N)==cudaSuccess&&dalloc(h->twist,6*N)==cudaSuccess;
+    ok=ok&&dalloc(h->pose,6*N)==cudaSuccess&&dalloc(h->vel,6*N)==cudaSuccess&&dalloc(h->acc,6*N)==cudaSuccess&&dalloc(h->swp,12*N)==cudaSuccess&&dalloc(h->swv,12*N)==cudaSuccess&&dalloc(h->swa,12*N)==cudaSuccess;
+    ok=ok&&dalloc(h->contacts,4*N)==cudaSuccess&&dalloc(h->prevc,4*N)==cudaSuccess&&dalloc(h->switching,N)==cudaSuccess&&dalloc(h->first,N)==cudaSuccess;
+    ok=ok&&dalloc(h->ctrl,N)==cudaSuccess&&dalloc(h->qpd,N)==cudaSuccess&&dalloc(h->qps,N)==cudaSuccess&&dalloc(h->counter,1)==cudaSuccess;
+    ok=ok&&dalloc(h->tau,12*N)==cudaSuccess&&dalloc(h->grf,12*N)==cudaSuccess&&dalloc(h->x,42*N)==cudaSuccess&&dalloc(h->com,3*N)==cudaSuccess;
+    ok=ok&&dalloc(h->rc,N)==cudaSuccess&&dalloc(h->nwsr,N)==cudaSuccess&&dalloc(h->ws,112*N)==cudaSuccess;
+    if(!ok){ h->err=std::string("cudaMalloc: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_NOMEM); }
+    cudaMemsetAsync(h->ctrl,0,N*sizeof(CtrlState),h->stream); cudaMemsetAsync(h->qpd,0,N*sizeof(QPData),h->stream); cudaMemsetAsync(h->qps,0,N*sizeof(QPState),h->stream);
+    cudaMemsetAsync(h->ws,0,112*N,h->stream); cudaMemsetAsync(h->com,0,3*N*sizeof(double),h->stream);
+    // constants: 13-body model table and gains
+    ModelConst mc; memcpy(mc.restR,ANYMAL_restR,sizeof(mc.restR)); memcpy(mc.restP,ANYMAL_restP,sizeof(mc.restP)); memcpy(mc.axis,ANYMAL_axis,sizeof(mc.axis));
+    memcpy(mc.mass,ANYMAL_mass,sizeof(mc.mass)); memcpy(mc.mcom,ANYMAL_mcom,sizeof(mc.mcom)); memcpy(mc.inertia,ANYMAL_inertia,sizeof(mc.inertia));
+    memcpy(mc.footR,ANYMAL_footR,sizeof(mc.footR)); memcpy(mc.footP,ANYMAL_footP,sizeof(mc.footP));
+    mc.total_mass=0; for(int i=0;i<13;i++) mc.total_mass+=mc.mass[i];                 // Model::getTotalMass (wbc.cpp:72)
+    Params P; P.friction=h->params.friction; P.loopRate=h->params.loopRate; P.maxTorque=h->params.maxTorque; P.kpValue=h->params.kpValue; P.kpValueZ=h->params.kpValueZ;
+    P.kdValue=h->params.kdValue; P.kiValue=h->params.kiValue; P.kpSwingValue=h->params.kpSwingValue; P.kdSwingValue=h->params.kdSwingValue; P.slackWeight=h->params.slackWeight;
+    for(int i=0;i<6;i++) P.refPose[i]=h->params.initialReferencePose[i];
+    h->devParams=P;
+    if(cudaMemcpyToSymbol(c_model,&mc,sizeof(mc))!=cudaSuccess){
+        h->err=std::string("cudaMemcpyToSymbol: ")+cudaGetErrorString(cudaGetLastError())+" (library built for sm_100a only)"; return fail(WBC_ERR_CUDA); }
+    // solver launch geometry: one warp per CTA, as many CTAs per SM as shared memory allows
+    h->qpSmem=sizeof(QPWork);
+    if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
+        h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
+    int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,32,h->qpSmem)!=cudaSuccess||nb<1){
+        h->err=std::string("occupancy query: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
+    h->qpBlocksPerSM=nb;
+    for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
+    *out=h;
+    int rcode=wbc_reset(h,0,n);
+    if(rcode!=WBC_OK){ *out=nullptr; return fail(rcode); }
+    return WBC_OK;
+}
+
+extern "C" int wbc_destroy(wbc_handle* h){
+    if(!h) return WBC_ERR_ARG;
+    cudaSetDevice(h->device);
+    if(h->stream) cudaStreamSynchronize(h->stream);
+    void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws};
+    for(void* p:ptrs) if(p) cudaFree(p);
+    for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
+    delete h; return WBC_OK;
+}
+
+static BatchIn batch_in(const wbc_handle* h){ BatchIn b; b.q=h->q; b.qd=h->qd; b.pos=h->pos; b.quat=h->quat; b.twist=h->twist; b.pose=h->pose; b.vel=h->vel; b.acc=h->acc;
+    b.swp=h->swp; b.swv=h->swv; b.swa=h->swa; b.contacts=h->contacts; b.switching=h->switching; return b; }
+static BatchOut batch_out(const wbc_handle* h){ BatchOut o; o.tau=h->tau; o.grf=h->grf; o.x=h->x; o.com=h->com; o.rc=h->rc; o.nwsr=h->nwsr; o.ws=h->ws; return o; }
+
+extern "C" int wbc_reset(wbc_handle* h,int first,int count){
+    if(!h||first<0||count<0||first+count>h->N) return WBC_ERR_ARG;
+    if(count==0) return WBC_OK;
+    CK(cudaSetDevice(h->device));
+    wbc_reset_kernel<<<(count+127)/128,128,0,h->stream>>>(h->N,h->devParams,first,count,h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,
+                                                         h->contacts,h->prevc,h->switching,h->first,h->rc,h->nwsr,h->tau,h->grf,h->x);
+    h->launches++; CK(cudaGetLastError());
+    return WBC_OK;
+}
+extern "C" int wbc_set_state(wbc_handle* h,const double* q,const double* qd,const double* pos,const double* quat,const double* twist){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N, D=sizeof(double); int r;
+    if((r=copy_in(h,h->q,q,12*N*D))||(r=copy_in(h,h->qd,qd,12*N*D))||(r=copy_in(h,h->pos,pos,3*N*D))||(r=copy_in(h,h->quat,quat,4*N*D))||(r=copy_in(h,h->twist,twist,6*N*D))) return r;
+    return WBC_OK;
+}
+extern "C" int wbc_set_reference(wbc_handle* h,const double* pose,const double* vel,const double* acc,const double* swp,const double* swv,const double* swa,
+                                 const unsigned char* contacts,const unsigned char* switching){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N, D=sizeof(double); int r;
+    if((r=copy_in(h,h->pose,pose,6*N*D))||(r=copy_in(h,h->vel,vel,6*N*D))||(r=copy_in(h,h->acc,acc,6*N*D))||(r=copy_in(h,h->swp,swp,12*N*D))||(r=copy_in(h,h->swv,swv,12*N*D))
+       ||(r=copy_in(h,h->swa,swa,12*N*D))||(r=copy_in(h,h->contacts,contacts,4*N))||(r=copy_in(h,h->switching,switching,N))) return r;
+    if(contacts){
+        wbc_derive_switching_kernel<<<(h->N+127)/128,128,0,h->stream>>>(h->N,h->contacts,h->prevc,h->switching,switching?0:1);
+        h->launches++; CK(cudaGetLastError());
+    }
+    return WBC_OK;
+}
+extern "C" int wbc_update_state(wbc_handle* h){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    int grid=h->smCount*16; if(grid>h->N) grid=h->N;
+    CK(cudaEventRecord(h->ev[0],h->stream));
+    wbc_update_state_kernel<<<grid,32,0,h->stream>>>(h->N,h->devParams,batch_in(h),h->ctrl,h->qpd,h->first,h->rc,h->com);
+    h->launches++; CK(cudaGetLastError());
+    CK(cudaEventRecord(h->ev[1],h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_solve_qp(wbc_handle* h){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    int grid=h->smCount*h->qpBlocksPerSM; if(grid>h->N) grid=h->N;
+    CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
+    CK(cudaEventRecord(h->ev[1],h->stream));
+    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */);
+    h->launches++; CK(cudaGetLastError());
+    CK(cudaEventRecord(h->ev[2],h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_compute_joint_torques(wbc_handle* h){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    wbc_compute_torques_kernel<<<(h->N+63)/64,64,0,h->stream>>>(h->N,h->qpd,batch_out(h));
+    h->launches++; CK(cudaGetLastError());
+    CK(cudaEventRecord(h->ev[3],h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_step(wbc_handle* h){ int r; if((r=wbc_update_state(h))||(r=wbc_solve_qp(h))||(r=wbc_compute_joint_torques(h))) return r; return WBC_OK; }
+extern "C" int wbc_synchronize(wbc_handle* h){ if(!h) return WBC_ERR_ARG; CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream)); return WBC_OK; }
+
+extern "C" int wbc_get_outputs(wbc_handle* h,double* tau,double* grf,double* x,int* rc,int* nwsr,signed char* ws,double* com){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N, D=sizeof(double); bool host=false; int r;
+    if((r=copy_out(h,tau,h->tau,12*N*D,host))||(r=copy_out(h,grf,h->grf,12*N*D,host))||(r=copy_out(h,x,h->x,42*N*D,host))||(r=copy_out(h,rc,h->rc,N*sizeof(int),host))
+       ||(r=copy_out(h,nwsr,h->nwsr,N*sizeof(int),host))||(r=copy_out(h,ws,h->ws,112*N,host))||(r=copy_out(h,com,h->com,3*N*D,host))) return r;
+    if(host) CK(cudaStreamSynchronize(h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_get_dense_qp(wbc_handle* h,int robot,double* H,double* g,double* A,double* lbA,double* ubA){
+    if(!h||robot<0||robot>=h->N) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    QPData q; CK(cudaMemcpyAsync(&q,h->qpd+robot,sizeof(QPData),cudaMemcpyDeviceToHost,h->stream)); CK(cudaStreamSynchronize(h->stream));
+    if(H) for(int i=0;i<42;i++) for(int j=0;j<42;j++) H[i*42+j]=Hel(q,i,j);
+    if(g) for(int i=0;i<42;i++) g[i]=(i>=18&&i<30)?q.gf[i-18]:0.0;
+    if(A) for(int i=0;i<70;i++) for(int j=0;j<42;j++) A[i*42+j]=Ael(q,i,j);
+    if(lbA) memcpy(lbA,q.lbA,sizeof(q.lbA)); if(ubA) memcpy(ubA,q.ubA,sizeof(q.ubA));
+    return WBC_OK;
+}
+extern "C" int wbc_num_robots(const wbc_handle* h){ return h?h->N:0; }
+extern "C" long long wbc_launch_count(const wbc_handle* h){ return h?h->launches:0; }
+extern "C" int wbc_last_kernel_ms(wbc_handle* h,float* rbd_ms,float* qp_ms,float* torque_ms){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream));
+    float a=0,b=0,c=0;
+    if(cudaEventElapsedTime(&a,h->ev[0],h->ev[1])!=cudaSuccess) a=-1; if(cudaEventElapsedTime(&b,h->ev[1],h->ev[2])!=cudaSuccess) b=-1;
+    if(cudaEventElapsedTime(&c,h->ev[2],h->ev[3])!=cudaSuccess) c=-1; cudaGetLastError();
+    if(rbd_ms) *rbd_ms=a; if(qp_ms) *qp_ms=b; if(torque_ms) *torque_ms=c;
+    return WBC_OK;
+}
+extern "C" const char* wbc_last_error(const wbc_handle* h){ return h?h->err.c_str():"null handle"; }

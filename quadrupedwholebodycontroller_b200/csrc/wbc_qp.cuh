@@ -22,6 +22,9 @@
 // If one of these preconditions were ever violated the solver reports QP_RET_UNSUPPORTED_PATH instead of guessing.
 #pragma once
 #include "wbc_common.cuh"
+#if !defined(__CUDACC__) && defined(WBC_QP_TRACE)
+#include <cstdio>
+#endif
 
 namespace wbc {
 
@@ -77,7 +80,7 @@ struct QPCtx {
 };
 
 // ---------------------------------------------------------------- structured A and H
-WBC_DEV double Ael(const QPData& q,int i,int j){
+WBC_HD double Ael(const QPData& q,int i,int j){
     if(i<6){ if(j<6) return q.Mbb[6*i+j]; if(j<18||j>=30) return 0.0; int r=j-18; return -(q.cmask[r/3]*q.Jc[18*r+i]); }
     if(i<18){ int r=i-6; return (j<18)? q.cmask[r/3]*q.Jc[18*r+j] : 0.0; }
     if(i<34){ int r=i-18,l=r>>2,k=r&3,c=j-18-3*l; if(c<0||c>2) return 0.0;
@@ -85,7 +88,7 @@ WBC_DEV double Ael(const QPData& q,int i,int j){
     if(i<46){ int r=i-34; if(j<6||j>=30) return 0.0; if(j<18) return q.Mjj[12*r+j-6]; int f=j-18; return -(q.cmask[f/3]*q.Jc[18*f+6+r]); }
     { int r=(i<58)?i-46:i-58; if(j<18) return (1.0-q.cmask[r/3])*q.Jc[18*r+j]; if(j==30+r) return (i<58)?-1.0:1.0; return 0.0; }
 }
-WBC_DEV double Hel(const QPData& q,int i,int j){
+WBC_HD double Hel(const QPData& q,int i,int j){
     if(i>=18&&i<30&&j>=18&&j<30) return q.Hff[12*(i-18)+(j-18)];
     if(i!=j) return 0.0; return (i>=30)?q.rho:1.0;
 }
@@ -706,6 +709,9 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
         performStep(w,c,BC_idx,BC_status,BC_isBound);
         const double hl=relativeHomotopyLength(w,c);
         if(hl<=OPT_terminationTolerance){ c.status=QPS_SOLVED; nWSR=iter; return QP_OK; }
+#if !defined(__CUDACC__) && defined(WBC_QP_TRACE)
+        printf("  it %3d tau %.6e  %s %s %3d  nFX %2d nAC %2d\n",iter,c.tau,BC_status==2?"---":(BC_status==0?"REM":(BC_status<0?"ADL":"ADU")),BC_isBound?"B":"C",BC_idx,c.nFX,c.nAC);
+#endif
         rv=changeActiveSet(w,c,BC_idx,BC_status,BC_isBound);
         if(rv!=QP_OK){ nWSR=iter; if(c.infeasible){ c.status=QPS_HOMOTOPYQPSOLVED; return QP_RET_HOTSTART_STOPPED_INFEASIBILITY; } return rv; }
         rv=computeProjectedCholesky(w,c);
