@@ -72,8 +72,8 @@ int wbc_set_reference(wbc_handle* h, const double* pose, const double* vel, cons
                       const double* sw_vel, const double* sw_acc, const unsigned char* contacts, const unsigned char* switching);
 
 /* The three hot methods, batched (whole_body_controller.hpp:47,54,52; whole_body_controller.cpp:256-294, 466-542, 553-577).
- * Robots whose previous solve did not return 0 are halted like the reference's control loop (:654-659): they keep their
- * status, output zero torques (terminate(), :626-635) and are skipped until wbc_reset. */
+ * A robot whose solve did not return 0 gets zero torques for that tick (what terminate() publishes, :626-635); the next call
+ * hot-starts it again exactly like the SQProblem object would -- halting the loop (:654-659) is the caller's decision. */
 int wbc_update_state(wbc_handle* h);
 int wbc_solve_qp(wbc_handle* h);
 int wbc_compute_joint_torques(wbc_handle* h);
@@ -95,6 +95,9 @@ int wbc_num_robots(const wbc_handle* h);
 long long wbc_launch_count(const wbc_handle* h);
 /* duration [ms] of the most recent wbc_solve_qp kernel measured with CUDA events on the handle's stream (synchronises) */
 int wbc_last_kernel_ms(wbc_handle* h, float* rbd_ms, float* qp_ms, float* torque_ms);
+/* development hook: per-robot clock64 breakdown of the last solve (8 int64 per robot: data shift, step direction, step,
+ * active-set change, projected Cholesky, ramp/drift, whole solve, iterations); enable != 0 allocates the device buffer */
+int wbc_profile(wbc_handle* h, int enable, long long* host_out);
 const char* wbc_last_error(const wbc_handle* h);
 
 #ifdef __cplusplus

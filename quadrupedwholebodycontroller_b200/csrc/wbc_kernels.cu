@@ -25,7 +25,7 @@ __constant__ ModelConst c_model;
 
 // ---------------------------------------------------------------- kernel 1: RBD + centroidal transform + QP assembly
 // grid-stride over instances; the RBD stage is ~40 kFLOP per robot, far below the solver's cost
-__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,const int* rc,double* com){
+__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,double* com){
     __shared__ ModelConst mc;
     __shared__ RbdScratch s;
     __shared__ QPData qp;
@@ -33,7 +33,6 @@ __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,B
     { const double* src=(const double*)&c_model; double* dst=(double*)&mc; LANE_FOR(i,MODEL_DOUBLES) dst[i]=src[i]; }
     WBC_SYNC();
     for(int r=blockIdx.x;r<N;r+=gridDim.x){
-        if(rc[r]!=0&&!first[r]) continue;                          // halted robot (wbc.cpp:654-659)
         LANE_FOR(k,12){ s.q[k]=in.q[k*N+r]; s.qd[k]=in.qd[k*N+r]; s.swp[k]=in.swp[k*N+r]; s.swv[k]=in.swv[k*N+r]; s.swa[k]=in.swa[k*N+r]; }
         LANE_FOR(k,6){ s.twist[k]=in.twist[k*N+r]; s.pose_d[k]=in.pose[k*N+r]; s.vel_d[k]=in.vel[k*N+r]; s.acc_d[k]=in.acc[k*N+r]; }
         LANE_FOR(k,3) s.pb[k]=in.pos[k*N+r];
@@ -52,7 +51,7 @@ __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,B
 }
 
 // ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart)
-__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax){
+__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof){
     extern __shared__ double smem[];
     QPWork& w=*reinterpret_cast<QPWork*>(smem);
     const int lane=threadIdx.x;
@@ -60,9 +59,10 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
         if(r>=N) break;
         const bool isFirst=first[r]!=0;
-        if(!isFirst&&out.rc[r]!=0) continue;                       // halted robot
         { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+        for(int k=0;k<8;k++) c.prof[k]=0;
+        const long long tstart=clock64();
         QPState& S=qs[r];
         if(!isFirst){
             LANE_FOR(i,42){ w.x[i]=S.x[i]; w.lb[i]=S.lb[i]; w.ub[i]=S.ub[i]; w.bstat[i]=S.bstat[i]; }
@@ -77,7 +77,8 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; out.x[i*N+r]=w.x[i]; out.ws[i*N+r]=w.bstat[i]; }
         LANE_FOR(i,112) S.y[i]=w.y[i];
         LANE_FOR(i,70){ S.Ax_l[i]=w.Ax_l[i]; S.Ax_u[i]=w.Ax_u[i]; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; }
-        if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0; }
+        if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
+                     if(prof){ c.prof[6]=clock64()-tstart; for(int k=0;k<8;k++) prof[8*(size_t)r+k]=c.prof[k]; } }
         WBC_SYNC();
     }
 }
@@ -128,7 +129,7 @@ struct wbc_handle {
     double *q=nullptr,*qd=nullptr,*pos=nullptr,*quat=nullptr,*twist=nullptr,*pose=nullptr,*vel=nullptr,*acc=nullptr,*swp=nullptr,*swv=nullptr,*swa=nullptr;
     unsigned char *contacts=nullptr,*prevc=nullptr,*switching=nullptr,*first=nullptr;
     // persistent per-robot state and intermediates
-    CtrlState* ctrl=nullptr; QPData* qpd=nullptr; QPState* qps=nullptr; int* counter=nullptr;
+    CtrlState* ctrl=nullptr; QPData* qpd=nullptr; QPState* qps=nullptr; int* counter=nullptr; long long* prof=nullptr;
     // outputs
     double *tau=nullptr,*grf=nullptr,*x=nullptr,*com=nullptr; int *rc=nullptr,*nwsr=nullptr; signed char* ws=nullptr;
     cudaEvent_t ev[4]={nullptr,nullptr,nullptr,nullptr};
@@ -216,7 +217,7 @@ extern "C" int wbc_destroy(wbc_handle* h){
     cudaSetDevice(h->device);
     if(h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
-                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws};
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof};
     for(void* p:ptrs) if(p) cudaFree(p);
     for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
     if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
@@ -261,7 +262,7 @@ extern "C" int wbc_update_state(wbc_handle* h){
     CK(cudaSetDevice(h->device));
     int grid=h->smCount*16; if(grid>h->N) grid=h->N;
     CK(cudaEventRecord(h->ev[0],h->stream));
-    wbc_update_state_kernel<<<grid,32,0,h->stream>>>(h->N,h->devParams,batch_in(h),h->ctrl,h->qpd,h->first,h->rc,h->com);
+    wbc_update_state_kernel<<<grid,32,0,h->stream>>>(h->N,h->devParams,batch_in(h),h->ctrl,h->qpd,h->first,h->com);
     h->launches++; CK(cudaGetLastError());
     CK(cudaEventRecord(h->ev[1],h->stream));
     return WBC_OK;
@@ -272,7 +273,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     int grid=h->smCount*h->qpBlocksPerSM; if(grid>h->N) grid=h->N;
     CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
     CK(cudaEventRecord(h->ev[1],h->stream));
-    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */);
+    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof);
     h->launches++; CK(cudaGetLastError());
     CK(cudaEventRecord(h->ev[2],h->stream));
     return WBC_OK;
@@ -316,6 +317,14 @@ extern "C" int wbc_last_kernel_ms(wbc_handle* h,float* rbd_ms,float* qp_ms,float
     if(cudaEventElapsedTime(&a,h->ev[0],h->ev[1])!=cudaSuccess) a=-1; if(cudaEventElapsedTime(&b,h->ev[1],h->ev[2])!=cudaSuccess) b=-1;
     if(cudaEventElapsedTime(&c,h->ev[2],h->ev[3])!=cudaSuccess) c=-1; cudaGetLastError();
     if(rbd_ms) *rbd_ms=a; if(qp_ms) *qp_ms=b; if(torque_ms) *torque_ms=c;
+    return WBC_OK;
+}
+// per-robot clock64 breakdown of the last solve (8 x int64 per robot, see QPCtx::prof); enable!=0 allocates the buffer
+extern "C" int wbc_profile(wbc_handle* h,int enable,long long* host_out){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    if(enable&&!h->prof){ CK(cudaMalloc((void**)&h->prof,8*(size_t)h->N*sizeof(long long))); CK(cudaMemsetAsync(h->prof,0,8*(size_t)h->N*sizeof(long long),h->stream)); }
+    if(host_out&&h->prof){ CK(cudaMemcpyAsync(host_out,h->prof,8*(size_t)h->N*sizeof(long long),cudaMemcpyDeviceToHost,h->stream)); CK(cudaStreamSynchronize(h->stream)); }
     return WBC_OK;
 }
 extern "C" const char* wbc_last_error(const wbc_handle* h){ return h?h->err.c_str():"null handle"; }

@@ -49,7 +49,14 @@ constexpr int LD=43;                  // leading dimension of Q, R, T (odd: conf
 #define QQ(i,j) w.Q[(i)+LD*(j)]       // Types.hpp:141-147: Q, R column-major, T row-major
 #define RR(i,j) w.R[(i)+LD*(j)]
 #define TT(i,j) w.T[(i)*LD+(j)]
-constexpr int SIZET=42;               // sizeT = min(nV,nC)
+constexpr int SIZET=42;
+#if defined(__CUDACC__)
+  #define WBC_TIC(t) long long t=clock64()
+  #define WBC_TOC(t,k) { long long n_=clock64(); c.prof[k]+=n_-t; t=n_; }
+#else
+  #define WBC_TIC(t) long long t=0
+  #define WBC_TOC(t,k) { (void)t; }
+#endif               // sizeT = min(nV,nC)
 
 // persistent solver state of one instance between ticks (HBM) -- what SQProblem keeps across hotstarts
 struct QPState {
@@ -67,7 +74,7 @@ struct QPWork {
     double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
     double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
     double tA[42], tB[42], xFRy[42], xFRz[42], Zdz[42], xTMP[42], yTMP[42];
-    double dAx[70], num[70], den[70], cs_c[42], cs_s[42], wv[42], tmpv[42], HZf[12*LD], zero[70];
+    double dAx[70], num[70], den[70], cs_c[42], cs_s[42], wv[42], tmpv[42], HZf[12*LD], zero[70], vm[42], ym[70], arow[42];
     signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70];
 };
 
@@ -77,6 +84,7 @@ struct QPCtx {
     int nFR,nFX,nAC,nIAC;
     int status, infeasible, unbounded, rampOffset;
     double tau;
+    long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 setup, 7 iterations
 };
 
 // ---------------------------------------------------------------- structured A and H
@@ -92,19 +100,45 @@ WBC_HD double Hel(const QPData& q,int i,int j){
     if(i>=18&&i<30&&j>=18&&j<30) return q.Hff[12*(i-18)+(j-18)];
     if(i!=j) return 0.0; return (i>=30)?q.rho:1.0;
 }
-// sum_j A[i][j] v[j] over columns with (sel==2: all, sel==0: free, sel==1: fixed), ascending j (Matrices.cpp:332-397 order)
-WBC_DEV double Arow_dot(const QPWork& w,int i,const double* v,int sel){
-    double s=0; for(int j=0;j<42;j++){ if(sel!=2 && ((w.bstat[j]!=0)!=(sel==1))) continue; double a=Ael(w.qp,i,j); if(a!=0.0) s+=a*v[j]; } return s; }
+// Structured products with A (whole_body_controller.cpp:492-497): no per-element decoding, only the non-zero blocks.
+// Arow_times: (A v)_i for a 42-vector v (callers mask v to the free / fixed columns beforehand, 0-entries add exactly 0).
+WBC_DEV double Arow_times(const QPData& q,int i,const double* v){
+    double s=0;
+    if(i<6){ for(int j=0;j<6;j++) s+=q.Mbb[6*i+j]*v[j]; for(int f=0;f<12;f++) s-=(q.cmask[f/3]*q.Jc[18*f+i])*v[18+f]; return s; }
+    if(i<18){ const int r=i-6; const double c=q.cmask[r/3]; if(c==0.0) return 0.0; for(int j=0;j<18;j++) s+=q.Jc[18*r+j]*v[j]; return s; }
+    if(i<34){ const int r=i-18,l=r>>2,k=r&3; const double c=q.cmask[l]; if(c==0.0) return 0.0; const double* f=v+18+3*l;
+              return ((k&1)?-f[k>>1]:f[k>>1])-q.mu*f[2]; }
+    if(i<46){ const int r=i-34; for(int j=0;j<12;j++) s+=q.Mjj[12*r+j]*v[6+j]; for(int f=0;f<12;f++) s-=(q.cmask[f/3]*q.Jc[18*f+6+r])*v[18+f]; return s; }
+    { const int r=(i<58)?i-46:i-58; const double c=1.0-q.cmask[r/3]; if(c!=0.0) for(int j=0;j<18;j++) s+=q.Jc[18*r+j]*v[j]; return (i<58)? s-v[30+r] : s+v[30+r]; }
+}
+// Acol_times: (A' y)_j for a 70-vector y by constraint number (0 for inactive constraints), rows visited in ascending order
+WBC_DEV double Acol_times(const QPData& q,int j,const double* y){
+    double s=0;
+    if(j<18){
+        if(j<6) for(int i=0;i<6;i++) s+=q.Mbb[6*i+j]*y[i];
+        for(int r=0;r<12;r++) s+=(q.cmask[r/3]*q.Jc[18*r+j])*y[6+r];
+        if(j>=6) for(int r=0;r<12;r++) s+=q.Mjj[12*r+(j-6)]*y[34+r];
+        for(int r=0;r<12;r++) s+=((1.0-q.cmask[r/3])*q.Jc[18*r+j])*y[46+r];
+        for(int r=0;r<12;r++) s+=((1.0-q.cmask[r/3])*q.Jc[18*r+j])*y[58+r];
+        return s;
+    }
+    if(j<30){ const int f=j-18,l=f/3,c=f-3*l; const double cf=q.cmask[l];
+        for(int i=0;i<6;i++) s-=(cf*q.Jc[18*f+i])*y[i];
+        const double* yf=y+18+4*l;
+        if(c==2) s+=cf*(-q.mu)*(yf[0]+yf[1]+yf[2]+yf[3]); else s+=cf*(yf[2*c]-yf[2*c+1]);
+        for(int r=0;r<12;r++) s-=(cf*q.Jc[18*f+6+r])*y[34+r];
+        return s; }
+    return y[58+(j-30)]-y[46+(j-30)];
+}
 WBC_DEV double Hrow_dot(const QPWork& w,int i,const double* v,int sel){
     double s=0;
     if(i>=18&&i<30){ for(int j=18;j<30;j++){ if(sel!=2 && ((w.bstat[j]!=0)!=(sel==1))) continue; s+=w.qp.Hff[12*(i-18)+(j-18)]*v[j]; } return s; }
     if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return 0.0;
     return ((i>=30)?w.qp.rho:1.0)*v[i];
 }
-
-// sum over ACTIVE constraints i (ascending number, the iSort order of Matrices.cpp transTimes) of A[i][j] yAC[pos(i)]
-WBC_DEV double AcolT_dot(const QPWork& w,int j,const double* yAC){
-    double s=0; for(int i=0;i<70;i++){ if(w.cstat[i]==0) continue; double a=Ael(w.qp,i,j); if(a!=0.0) s+=a*yAC[w.posAC[i]]; } return s; }
+// masked copies: vm = v restricted to free (sel 0) / fixed (sel 1) variables; ym = yAC scattered to constraint numbers
+WBC_DEV void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
+WBC_DEV void scatter_yAC(QPWork& w,const QPCtx& c,const double* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:0.0; WBC_SYNC(); }
 
 // ---------------------------------------------------------------- index lists (Indexlist.cpp: insertion-ordered number[])
 // removal keeps the order of the remaining entries; every lane holds the same counters, one lane edits the list
@@ -279,7 +313,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
             if(nAC>0){
                 if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=0.0; WBC_SYNC(); }
                 else {
-                    if(!bBzero&&r==0){ LANE_FOR(i,nAC) w.tB[i]-=Arow_dot(w,(int)w.AC[i],w.dx,1); WBC_SYNC(); }
+                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]-=Arow_times(w.qp,(int)w.AC[i],w.vm); WBC_SYNC(); }
                     if(!backsolveT(w,c,w.tB,false,w.xFRy)) return QP_RET_STEPDIRECTION_FAILED_TQ;
                     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=w.xTMP[ii]; for(int j=0;j<nAC;j++) s+=QQ(ii,nZ+j)*w.xFRy[j]; w.xTMP[ii]=s; }
                     WBC_SYNC();
@@ -310,15 +344,17 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         WBC_SYNC();
         // residuals for the next refinement pass
         double rnrm=0.0;
-        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); t-=AcolT_dot(w,ii,w.dyAC); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        scatter_yAC(w,c,w.dyAC);
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); t-=Acol_times(w.qp,ii,w.ym); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= bCzero?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
-            t-=Arow_dot(w,ii,w.dx,0); t-=Arow_dot(w,ii,w.dx,1); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
+            t-=Arow_times(w.qp,ii,w.dx); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
         rnrm=wbc_max(rnrm);
         WBC_SYNC();
         if(rnrm<OPT_epsIterRef) break;
     }
     // IV) delta_yFX
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=AcolT_dot(w,ii,w.dyAC); t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); w.dyFX[ii]=t; }
+    scatter_yAC(w,c,w.dyAC);
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=Acol_times(w.qp,ii,w.ym); t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); w.dyFX[ii]=t; }
     WBC_SYNC();
     return QP_OK;
 }
@@ -374,7 +410,7 @@ WBC_DEV double relativeHomotopyLength(const QPWork& w,const QPCtx& c){
 WBC_DEV void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
     LANE_FOR(i,42){ double t=w.y[i]; t-=Hrow_dot(w,i,w.x,2);
-        double s=0; for(int k=0;k<70;k++){ double a=Ael(w.qp,k,i); if(a!=0.0) s+=a*w.y[42+k]; } w.g[i]=t+s; }
+        w.g[i]=t+Acol_times(w.qp,i,w.y+42); }
     WBC_SYNC();
 }
 // QProblem::performStep (QProblem.cpp:4981-5278)
@@ -393,7 +429,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
     WBC_SYNC();
     // II.1 inactive constraints
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_dot(w,ii,w.dx,2); }
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_times(w.qp,ii,w.dx); }
     WBC_SYNC();
     LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],0.0); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
@@ -421,7 +457,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
         LANE_FOR(i,42){ w.g[i]+=tau*w.dg[i]; w.lb[i]+=tau*w.dlb[i]; w.ub[i]+=tau*w.dub[i]; }
         LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
         WBC_SYNC();
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_dot(w,ii,w.x,2); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_times(w.qp,ii,w.x); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
         LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; double da=w.dAx[ii];
             w.Ax[ii]+=tau*da; w.Ax_l[ii]+=tau*(da-w.dlbA[ii]); w.Ax_u[ii]+=tau*(w.dubA[ii]-da); }
         WBC_SYNC();
@@ -513,9 +549,11 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         weight=wbc_max(weight); zero=wbc_max(zero);
         return zero>OPT_epsLITests*weight;
     }
-    double l2=0.0; for(int i=0;i<nFR;i++){ double a=Ael(w.qp,number,(int)w.FR[i]); l2+=a*a; }
+    LANE_FOR(j,42) w.arow[j]=Ael(w.qp,number,j);
+    WBC_SYNC();
+    double l2=0.0; for(int i=0;i<nFR;i++){ double a=w.arow[(int)w.FR[i]]; l2+=a*a; }
     bool li=false;
-    LANE_FOR(j,nZ){ double sum=0.0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=Ael(w.qp,number,ii)*QQ(ii,j); } if(fabs(sum)>OPT_epsLITests*l2) li=true; }
+    LANE_FOR(j,nZ){ double sum=0.0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=w.arow[ii]*QQ(ii,j); } if(fabs(sum)>OPT_epsLITests*l2) li=true; }
     return wbc_ballot(li)!=0u;
 }
 // QProblem::addBound_checkLI (QProblem.cpp:3487-3590)
@@ -570,11 +608,14 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
     const int nFR=c.nFR, nAC=c.nAC, nFX=c.nFX, nZ=nFR-nAC; const double sg=(C_status==ST_LOWER)?1.0:-1.0;
     WBC_SYNC();
     if(nAC>0){
-        LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*(sg*Ael(w.qp,number,jj)); } w.tB[i]=s; }
+        LANE_FOR(j,42) w.arow[j]=sg*Ael(w.qp,number,j);
+        WBC_SYNC();
+        LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*w.arow[jj]; } w.tB[i]=s; }
         if(!backsolveT(w,c,w.tB,true,w.xFRy)) return QP_RET_UNSUPPORTED_PATH;
     }
     WBC_SYNC();
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=sg*Ael(w.qp,number,ii)-AcolT_dot(w,ii,w.xFRy); }
+    scatter_yAC(w,c,w.xFRy);
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=sg*Ael(w.qp,number,ii)-Acol_times(w.qp,ii,w.ym); }
     return ensureLI_exchange(w,c,number,C_status,false);
 }
 // QProblem::addBound_ensureLI (QProblem.cpp:3596-3780)
@@ -588,7 +629,8 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
         if(!backsolveT(w,c,w.tB,true,w.xFRy)) return QP_RET_UNSUPPORTED_PATH;
     }
     WBC_SYNC();
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=0.0-AcolT_dot(w,ii,w.xFRy); }
+    scatter_yAC(w,c,w.xFRy);
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=0.0-Acol_times(w.qp,ii,w.ym); }
     return ensureLI_exchange(w,c,number,B_status,true);
 }
 
@@ -599,7 +641,9 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
     const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     WBC_SYNC();
     // row [wZ wY] = aFR' [Z Y]
-    LANE_FOR(j,nFR){ double s=0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; s+=Ael(w.qp,number,ii)*QQ(ii,j); }
+    LANE_FOR(j,42) w.arow[j]=Ael(w.qp,number,j);
+    WBC_SYNC();
+    LANE_FOR(j,nFR){ double s=0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; s+=w.arow[ii]*QQ(ii,j); }
         if(j<nZ) w.wv[j]=s; else TT(nAC,tcol+(j-nZ))=s; }
     if(nZ>0){
         givens_chain(w,c,nZ-1);
@@ -702,22 +746,29 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
     c.infeasible=0; c.unbounded=0;
     for(int iter=nWSRperformed;iter<nWSR;iter++){
         c.status=QPS_PERFORMINGHOMOTOPY;
+        WBC_TIC(t0);
         bool bCzero,bBzero; determineDataShift(w,c,bCzero,bBzero);
+        WBC_TOC(t0,0);
         int rv=determineStepDirection(w,c,w.dg,w.dlbA,w.dubA,w.dlb,w.dub,bCzero,bBzero);
+        WBC_TOC(t0,1);
         if(rv!=QP_OK){ nWSR=iter; return rv; }
         int BC_idx,BC_status; bool BC_isBound;
         performStep(w,c,BC_idx,BC_status,BC_isBound);
         const double hl=relativeHomotopyLength(w,c);
+        WBC_TOC(t0,2); c.prof[7]++;
         if(hl<=OPT_terminationTolerance){ c.status=QPS_SOLVED; nWSR=iter; return QP_OK; }
 #if !defined(__CUDACC__) && defined(WBC_QP_TRACE)
         printf("  it %3d tau %.6e  %s %s %3d  nFX %2d nAC %2d\n",iter,c.tau,BC_status==2?"---":(BC_status==0?"REM":(BC_status<0?"ADL":"ADU")),BC_isBound?"B":"C",BC_idx,c.nFX,c.nAC);
 #endif
         rv=changeActiveSet(w,c,BC_idx,BC_status,BC_isBound);
+        WBC_TOC(t0,3);
         if(rv!=QP_OK){ nWSR=iter; if(c.infeasible){ c.status=QPS_HOMOTOPYQPSOLVED; return QP_RET_HOTSTART_STOPPED_INFEASIBILITY; } return rv; }
         rv=computeProjectedCholesky(w,c);
+        WBC_TOC(t0,4);
         if(rv!=QP_OK) return rv;
         c.status=QPS_HOMOTOPYQPSOLVED;
         if(BC_status!=2&&c.tau<=QEPS) performRamping(w,c); else performDriftCorrection(w,c);
+        WBC_TOC(t0,5);
     }
     return QP_RET_MAX_NWSR_REACHED;
 }
@@ -774,7 +825,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane;
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
-    LANE_FOR(i,70){ w.zero[i]=0.0; double ax=Arow_dot(w,i,w.x,2); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    LANE_FOR(i,70){ w.zero[i]=0.0; double ax=Arow_times(w.qp,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;
