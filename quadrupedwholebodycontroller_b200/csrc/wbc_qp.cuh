@@ -74,7 +74,7 @@ struct QPWork {
     double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
     double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
     double tA[42], tB[42], xFRy[42], xFRz[42], Zdz[42], xTMP[42], yTMP[42];
-    double dAx[70], num[70], den[70], cs_c[42], cs_s[42], wv[42], tmpv[42], HZf[12*LD], zero[70], vm[42], ym[70], arow[42];
+    double dAx[70], num[70], den[70], cs_c[42], cs_s[42], wv[42], tmpv[42], HZf[12*LD], zero[70], vm[42], ym[70], arow[42], rdR[42], rdT[42];
     signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70];
 };
 
@@ -159,77 +159,54 @@ WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ WBC_SYNC(); if(c.lane==
 
 // ---------------------------------------------------------------- triangular solves
 constexpr int SLOTS=(42+WBC_NL-1)/WBC_NL;
-// generic column-oriented forward substitution for a lower-triangular system L a = b of size n:
-//   a_k = (b_k - sum_{j<k} L(k,j) a_j) / L(k,k);  each lane owns rows lane, lane+NL, ... and accumulates its rows'
-//   sums in ascending j exactly like the row-oriented reference loops.  Lget(k,j) returns L(k,j).
-// returns false on a (near-)zero pivot according to `pivot_ok(diag,sum)`.
-#define WBC_TRISOLVE(n, LGET, BSRC, ADST, PIVOT_OK, okflag)                                              \
-    {   double sum_[SLOTS]; okflag=true;                                                                  \
-        for(int s_=0;s_<SLOTS;s_++){ int r_=lane+WBC_NL*s_; sum_[s_]=(r_<(n))?(BSRC):0.0; (void)r_; }      \
-        WBC_SYNC();                                                                                       \
-        for(int k_=0;k_<(n);k_++){                                                                        \
-            double mine_=0.0; { int s_=k_/WBC_NL; if((k_%WBC_NL)==lane){ int r_=k_; double d_=LGET(k_,k_); \
-                if(!(PIVOT_OK(d_,sum_[s_]))) mine_=NAN; else mine_=sum_[s_]/d_; (void)r_; } }               \
-            double ak_=wbc_bcast(mine_,k_%WBC_NL);                                                        \
-            if(ak_!=ak_){ okflag=false; break; }                                                           \
-            if((k_%WBC_NL)==lane) ADST(k_)=ak_;                                                            \
-            for(int s_=0;s_<SLOTS;s_++){ int r_=lane+WBC_NL*s_; if(r_>k_&&r_<(n)) sum_[s_]-=LGET(r_,k_)*ak_; } \
-        }                                                                                                 \
-        WBC_SYNC(); }
-
-#define PIV_T(d,sum) (fabs(d)>QEPS)
-#define PIV_R(d,sum) (fabs(d)>=QZERO*fabs(sum))
-
-// QProblem::backsolveT (QProblem.cpp:4518-4565).  b, a indexed by AC position; a may alias b only if noted by caller (never here)
-WBC_DEV bool backsolveT(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a){
-    const int lane=c.lane, nT=c.nAC, tcol=SIZET-nT; bool ok=true;
-    if(nT<=0) return true;
+// Column-oriented forward substitution for a lower-triangular system L u = b of size n:
+//   u_k = (b_k - sum_{j<k} L(k,j) u_j) * rdiag(k).  Each lane owns rows lane, lane+NL, ..., keeps their running sums in
+//   registers and subtracts the terms in ascending j, the order of the reference's row loops; u_k travels by one shuffle.
+//   Diagonals enter as precomputed reciprocals (fp64 division is ~20x the latency of a multiply and sat on the critical
+//   path of every one of the 42 steps); pivots are validated where the reciprocals are formed.
+template<class LGet,class BGet,class ASet,class RGet>
+WBC_DEV void trisolve(int lane,int n,LGet L,BGet B,ASet A,RGet RD){
+    double sum_[SLOTS], rd_[SLOTS], l_[SLOTS];
+    #pragma unroll
+    for(int s_=0;s_<SLOTS;s_++){ const int r_=lane+WBC_NL*s_; const bool in=r_<n; sum_[s_]=in?B(r_):0.0; rd_[s_]=in?RD(r_):0.0; l_[s_]=(in&&r_>0)?L(r_,0):0.0; }
     WBC_SYNC();
-    if(!transposed){
-        // row i: sum_{j<i} TT(i,sizeT-1-j) a[nT-1-j];  unknown u_k = a[nT-1-k]
-        #define LG(i,j) TT(i,SIZET-1-(j))
-        #define BS b[r_]
-        #define AD(k) a[nT-1-(k)]
-        WBC_TRISOLVE(nT,LG,BS,AD,PIV_T,ok)
-        #undef LG
-        #undef BS
-        #undef AD
-    } else {
-        // row i: sum_{j<i} TT(nT-1-j,tcol+i) a[nT-1-j]
-        #define LG(i,j) TT(nT-1-(j),tcol+(i))
-        #define BS b[r_]
-        #define AD(k) a[nT-1-(k)]
-        WBC_TRISOLVE(nT,LG,BS,AD,PIV_T,ok)
-        #undef LG
-        #undef BS
-        #undef AD
+    for(int k_=0;k_<n;k_++){
+        double mine_=0.0;
+        #pragma unroll
+        for(int s_=0;s_<SLOTS;s_++) if(lane+WBC_NL*s_==k_) mine_=sum_[s_]*rd_[s_];
+        const double ak_=wbc_bcast(mine_,k_%WBC_NL);
+        if((k_%WBC_NL)==lane) A(k_,ak_);
+        #pragma unroll
+        for(int s_=0;s_<SLOTS;s_++){ const int r_=lane+WBC_NL*s_; const bool act=(r_>k_&&r_<n);
+            const double nl=(r_>k_+1&&r_<n)?L(r_,k_+1):0.0;         // next column's entry, independent of the chain
+            if(act) sum_[s_]-=l_[s_]*ak_;
+            l_[s_]=nl; }
     }
-    return ok;
+    WBC_SYNC();
 }
-// QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b
-WBC_DEV bool backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a,int nR){
-    const int lane=c.lane; bool ok=true;
-    if(nR<=0) return true;
+// reciprocals of T's diagonal TT(k, sizeT-1-k); false if a pivot fails the |.| > EPS test of QProblem::backsolveT
+WBC_DEV bool prepare_T(QPWork& w,const QPCtx& c){
+    const int lane=c.lane; bool bad=false; WBC_SYNC();
+    LANE_FOR(k,c.nAC){ const double d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=1.0/d; }
     WBC_SYNC();
-    if(transposed){
-        #define LG(i,j) RR(j,i)
-        #define BS b[r_]
-        #define AD(k) a[k]
-        WBC_TRISOLVE(nR,LG,BS,AD,PIV_R,ok)
-        #undef LG
-        #undef BS
-        #undef AD
-    } else {
-        // R a = b solved from the last row up: unknown u_k = a[nR-1-k], L(i,j) = RR(nR-1-i, nR-1-j)
-        #define LG(i,j) RR(nR-1-(i),nR-1-(j))
-        #define BS b[nR-1-r_]
-        #define AD(k) a[nR-1-(k)]
-        WBC_TRISOLVE(nR,LG,BS,AD,PIV_R,ok)
-        #undef LG
-        #undef BS
-        #undef AD
-    }
-    return ok;
+    return wbc_ballot(bad)==0u;
+}
+// QProblem::backsolveT (QProblem.cpp:4518-4565).  b, a indexed by AC position.  prepare_T must have run since T last changed.
+WBC_DEV void backsolveT(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a){
+    const int lane=c.lane, nT=c.nAC, tcol=SIZET-nT;
+    if(nT<=0) return;
+    WBC_SYNC();
+    // unknown u_k = a[nT-1-k]; row i, column j<i:  TT(i,sizeT-1-j)  resp.  TT(nT-1-j,tcol+i) for the transposed system
+    if(!transposed) trisolve(lane,nT,[&](int i,int j){ return TT(i,SIZET-1-j); },[&](int r){ return b[r]; },[&](int k,double v){ a[nT-1-k]=v; },[&](int k){ return w.rdT[k]; });
+    else trisolve(lane,nT,[&](int i,int j){ return TT(nT-1-j,tcol+i); },[&](int r){ return b[r]; },[&](int k,double v){ a[nT-1-k]=v; },[&](int k){ return w.rdT[nT-1-k]; });
+}
+// QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b.  w.rdR = 1/diag(R).
+WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a,int nR){
+    const int lane=c.lane;
+    if(nR<=0) return;
+    WBC_SYNC();
+    if(transposed) trisolve(lane,nR,[&](int i,int j){ return RR(j,i); },[&](int r){ return b[r]; },[&](int k,double v){ a[k]=v; },[&](int k){ return w.rdR[k]; });
+    else trisolve(lane,nR,[&](int i,int j){ return RR(nR-1-i,nR-1-j); },[&](int r){ return b[nR-1-r]; },[&](int k,double v){ a[nR-1-k]=v; },[&](int k){ return w.rdR[nR-1-k]; });
 }
 
 // ---------------------------------------------------------------- factorisations
@@ -247,12 +224,17 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
     const int lane=c.lane;
     for(int i=0;i<n;i++){
         WBC_SYNC();
-        double sum=RR(i,i); for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);      // every lane, same value (broadcast reads)
+        double sum=RR(i,i);
+        #pragma unroll 4
+        for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);      // every lane, same value (broadcast reads)
         if(!(sum>0.0)) return false;
-        const double d=sqrt(sum);
+        const double d=sqrt(sum), rd=1.0/d;
         WBC_SYNC();
-        if(lane==(i%WBC_NL)) RR(i,i)=d;
-        for(int j=i+1+lane;j<n;j+=WBC_NL){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=s2/d; }
+        if(lane==(i%WBC_NL)){ RR(i,i)=d; w.rdR[i]=rd; }
+        for(int j=i+1+lane;j<n;j+=WBC_NL){ double s2=RR(i,j);
+            #pragma unroll 4
+            for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j);
+            RR(i,j)=s2*rd; }
     }
     WBC_SYNC();
     return true;
@@ -282,12 +264,38 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
             if(w.bstat[18+a]==0){ for(int i=0;i<nFR;i++){ int v=(int)w.FR[i]; if(v>=18&&v<30) s+=w.qp.Hff[12*a+(v-18)]*QQ(v,k); } }
             w.HZf[a*LD+k]=s; }
         WBC_SYNC();
-        // R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk), upper triangle only (the rest is never read)
-        LANE_FOR(kk,nZ) for(int jj=kk;jj<nZ;jj++){ double s=0;
-            for(int ii=0;ii<nFR;ii++){ int v=(int)w.FR[ii];
-                double hz = (v>=18&&v<30)? w.HZf[(v-18)*LD+kk] : ((v>=30)?w.qp.rho:1.0)*QQ(v,kk);
-                s+=QQ(v,jj)*hz; }
-            RR(kk,jj)=s; }
+        // R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk), upper triangle only (the rest is never read).
+        // Register-tiled: each lane accumulates one 6x6 tile (28 upper tiles of the 7x7 tile grid) over the free
+        // variables in list order -- same products, same summation order as the scalar loops, ~36 FMAs per 12 loads.
+        LANE_FOR(t,28){
+            int ti=0, rem=t; while(rem>=7-ti){ rem-=7-ti; ti++; } const int tj=ti+rem;
+            if(6*tj>=nZ&&6*ti>=nZ) continue;
+            if(6*ti>=nZ) continue;
+            double acc[6][6];
+            #pragma unroll
+            for(int a=0;a<6;a++){
+                #pragma unroll
+                for(int b=0;b<6;b++) acc[a][b]=0.0; }
+            for(int ii=0;ii<nFR;ii++){
+                const int v=(int)w.FR[ii]; double zj[6],wk[6];
+                #pragma unroll
+                for(int b=0;b<6;b++) zj[b]=QQ(v,6*tj+b);
+                if(v>=18&&v<30){
+                    #pragma unroll
+                    for(int a=0;a<6;a++) wk[a]=w.HZf[(v-18)*LD+6*ti+a];
+                } else { const double dv=(v>=30)?w.qp.rho:1.0;
+                    #pragma unroll
+                    for(int a=0;a<6;a++) wk[a]=dv*QQ(v,6*ti+a); }
+                #pragma unroll
+                for(int a=0;a<6;a++){
+                    #pragma unroll
+                    for(int b=0;b<6;b++) acc[a][b]+=zj[b]*wk[a]; }
+            }
+            #pragma unroll
+            for(int a=0;a<6;a++){
+                #pragma unroll
+                for(int b=0;b<6;b++){ const int kk=6*ti+a, jj=6*tj+b; if(kk<=jj&&jj<nZ) RR(kk,jj)=acc[a][b]; } }
+        }
     }
     if(!potrf_R(w,c,nZ)) return QP_RET_HESSIAN_NOT_SPD;
     return QP_OK;
@@ -300,7 +308,7 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
 WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const double* dlbA,const double* dubA,const double* dlb,const double* dub,
                                   bool bCzero,bool bBzero){
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
-    WBC_SYNC();
+    if(!prepare_T(w,c)) return QP_RET_STEPDIRECTION_FAILED_TQ;
     // I) delta_xFX
     LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= bBzero?0.0:((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=0.0; }
@@ -314,7 +322,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
                 if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=0.0; WBC_SYNC(); }
                 else {
                     if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]-=Arow_times(w.qp,(int)w.AC[i],w.vm); WBC_SYNC(); }
-                    if(!backsolveT(w,c,w.tB,false,w.xFRy)) return QP_RET_STEPDIRECTION_FAILED_TQ;
+                    backsolveT(w,c,w.tB,false,w.xFRy);
                     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=w.xTMP[ii]; for(int j=0;j<nAC;j++) s+=QQ(ii,nZ+j)*w.xFRy[j]; w.xTMP[ii]=s; }
                     WBC_SYNC();
                 }
@@ -326,8 +334,8 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
             WBC_SYNC();
             if(nZ>0){
                 LANE_FOR(i,nZ){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s-=QQ(jj,i)*w.tA[jj]; } w.xFRz[i]=s; }
-                if(!backsolveR(w,c,w.xFRz,true,w.xFRz,nZ)) return QP_RET_STEPDIRECTION_FAILED_CHOLESKY;
-                if(!backsolveR(w,c,w.xFRz,false,w.xFRz,nZ)) return QP_RET_STEPDIRECTION_FAILED_CHOLESKY;
+                backsolveR(w,c,w.xFRz,true,w.xFRz,nZ);
+                backsolveR(w,c,w.xFRz,false,w.xFRz,nZ);
                 LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=0; for(int j=0;j<nZ;j++) s+=QQ(ii,j)*w.xFRz[j]; w.Zdz[ii]=s; w.xTMP[ii]+=s; }
                 WBC_SYNC();
             }
@@ -336,7 +344,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         if(nAC>0){
             if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.Zdz,0); } WBC_SYNC(); }
             LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*w.tA[jj]; } w.tB[i]=s; }
-            if(!backsolveT(w,c,w.tB,true,w.yTMP)) return QP_RET_STEPDIRECTION_FAILED_TQ;
+            backsolveT(w,c,w.tB,true,w.yTMP);
         }
         WBC_SYNC();
         LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.dx[ii]+=w.xTMP[ii]; }
@@ -515,11 +523,21 @@ WBC_DEV void computeGivens(double xold,double yold,double& xnew,double& ynew,dou
 // result of rotation j-1 -- a scalar recurrence every lane evaluates redundantly -- and then applied to the column
 // pair (j+1, j) of Q.  The rows of Q are independent, so each lane sweeps its own rows through the whole chain.
 WBC_DEV void givens_chain(QPWork& w,const QPCtx& c,int nrot){
+    // The recurrence t_j = hypot(w[j+1], t_{j-1}) of the reference's loop is t_j = sgn(w[j+1]) |w[0..j+1]|_2, so every
+    // rotation follows from prefix sums of squares: one lane per rotation, no serial sqrt/divide chain.
+    const int lane=c.lane; WBC_SYNC();
+    double tlast=w.wv[0];
+    LANE_FOR(j,nrot){
+        double P=0.0; for(int k=0;k<=j;k++) P+=w.wv[k]*w.wv[k];
+        const double xold=w.wv[j+1];
+        const double yold=(j==0)?w.wv[0]:((w.wv[j]<0.0)?-sqrt(P):sqrt(P));
+        double cc,ss,t;
+        if(fabs(yold)<QZERO){ cc=1.0; ss=0.0; t=xold; }
+        else { t=sqrt(P+xold*xold); if(xold<0.0) t=-t; const double rt=1.0/t; cc=xold*rt; ss=yold*rt; }
+        w.cs_c[j]=cc; w.cs_s[j]=ss; if(j==nrot-1) tlast=t;
+    }
     WBC_SYNC();
-    double cur=w.wv[0];
-    for(int j=0;j<nrot;j++){ double xn,yn,cc,ss; computeGivens(w.wv[j+1],cur,xn,yn,cc,ss); cur=xn; if(c.lane==0){ w.cs_c[j]=cc; w.cs_s[j]=ss; } }
-    WBC_SYNC();
-    if(c.lane==0&&nrot>0) w.wv[nrot]=cur;
+    if(nrot>0){ const int owner=(nrot-1)%WBC_NL; tlast=wbc_bcast(tlast,owner); if(lane==0) w.wv[nrot]=tlast; }
     WBC_SYNC();
 }
 WBC_DEV void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
@@ -611,7 +629,8 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
         LANE_FOR(j,42) w.arow[j]=sg*Ael(w.qp,number,j);
         WBC_SYNC();
         LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*w.arow[jj]; } w.tB[i]=s; }
-        if(!backsolveT(w,c,w.tB,true,w.xFRy)) return QP_RET_UNSUPPORTED_PATH;
+        if(!prepare_T(w,c)) return QP_RET_UNSUPPORTED_PATH;
+        backsolveT(w,c,w.tB,true,w.xFRy);
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
@@ -626,7 +645,8 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
     WBC_SYNC();
     if(nAC>0){
         LANE_FOR(i,nAC) w.tB[i]=sg*QQ(number,nZ+i);
-        if(!backsolveT(w,c,w.tB,true,w.xFRy)) return QP_RET_UNSUPPORTED_PATH;
+        if(!prepare_T(w,c)) return QP_RET_UNSUPPORTED_PATH;
+        backsolveT(w,c,w.tB,true,w.xFRy);
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
