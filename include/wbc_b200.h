@@ -95,9 +95,12 @@ int wbc_num_robots(const wbc_handle* h);
 long long wbc_launch_count(const wbc_handle* h);
 /* duration [ms] of the most recent wbc_solve_qp kernel measured with CUDA events on the handle's stream (synchronises) */
 int wbc_last_kernel_ms(wbc_handle* h, float* rbd_ms, float* qp_ms, float* torque_ms);
-/* development hook: per-robot clock64 breakdown of the last solve (8 int64 per robot: data shift, step direction, step,
- * active-set change, projected Cholesky, ramp/drift, whole solve, iterations); enable != 0 allocates the device buffer */
+/* measurement hook: per-robot record of the last solve, 10 int64 per robot: clock64 ticks in data shift, step direction, step,
+ * active-set change, projected Cholesky, ramp/drift, whole solve; iterations; ALGORITHMIC flops of the qpOASES method on dense
+ * data (formulas of SURVEY.md section 8d, the numerator of the FP64 roofline); cold-start flag.  enable != 0 allocates the buffer */
 int wbc_profile(wbc_handle* h, int enable, long long* host_out);
+/* measured FP64 FMA peak of the device in GFLOP/s (8 independent DFMA chains per thread, all SMs) -- the FP64 roofline denominator */
+int wbc_measure_fp64_peak(wbc_handle* h, double* gflops);
 const char* wbc_last_error(const wbc_handle* h);
 
 #ifdef __cplusplus

@@ -16,7 +16,7 @@ _lib = None
 
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
            "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
-           "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_last_error"]
+           "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error"]
 
 
 class WbcParams(C.Structure):
@@ -47,6 +47,7 @@ def load_library():
         lib.wbc_last_error.argtypes = [C.c_void_p]; lib.wbc_last_error.restype = C.c_char_p
         lib.wbc_default_params.argtypes = [C.POINTER(WbcParams)]
         lib.wbc_profile.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        lib.wbc_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         _lib = lib
     return _lib
 
@@ -143,10 +144,13 @@ class WholeBodyController:
         return int(load_library().wbc_launch_count(self._h))
 
     def profile(self, enable=True, fetch=False):
-        """per-robot clock64 breakdown of the last solve, shape (N, 8) int64 (development hook)"""
-        out = np.zeros((self.N, 8), np.int64) if fetch else None
+        """per-robot clock64 breakdown of the last solve, shape (N, 10) int64: 7 clock64 phase counters, iterations, algorithmic flops, cold flag"""
+        out = np.zeros((self.N, 10), np.int64) if fetch else None
         self._ck(load_library().wbc_profile(self._h, int(enable), _ptr(out)))
         return out
+
+    def measureFp64Peak(self):
+        g = C.c_double(); self._ck(load_library().wbc_measure_fp64_peak(self._h, C.byref(g))); return g.value
 
     def lastKernelMs(self):
         a, b, c = C.c_float(), C.c_float(), C.c_float()

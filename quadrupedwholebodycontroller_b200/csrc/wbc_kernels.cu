@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
         for(int k=0;k<8;k++) c.prof[k]=0;
+        c.flops=0.0;
         const long long tstart=clock64();
         QPState& S=qs[r];
         if(!isFirst){
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         LANE_FOR(i,112) S.y[i]=w.y[i];
         LANE_FOR(i,70){ S.Ax_l[i]=w.Ax_l[i]; S.Ax_u[i]=w.Ax_u[i]; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; }
         if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
-                     if(prof){ c.prof[6]=clock64()-tstart; for(int k=0;k<8;k++) prof[8*(size_t)r+k]=c.prof[k]; } }
+                     if(prof){ c.prof[6]=clock64()-tstart; for(int k=0;k<8;k++) prof[10*(size_t)r+k]=c.prof[k]; prof[10*(size_t)r+8]=(long long)c.flops; prof[10*(size_t)r+9]=isFirst?1:0; } }
         WBC_SYNC();
     }
 }
@@ -319,12 +320,30 @@ extern "C" int wbc_last_kernel_ms(wbc_handle* h,float* rbd_ms,float* qp_ms,float
     if(rbd_ms) *rbd_ms=a; if(qp_ms) *qp_ms=b; if(torque_ms) *torque_ms=c;
     return WBC_OK;
 }
-// per-robot clock64 breakdown of the last solve (8 x int64 per robot, see QPCtx::prof); enable!=0 allocates the buffer
+// per-robot breakdown of the last solve (10 x int64 per robot: QPCtx::prof[0..7], algorithmic flops, cold flag); enable!=0 allocates the buffer
 extern "C" int wbc_profile(wbc_handle* h,int enable,long long* host_out){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
-    if(enable&&!h->prof){ CK(cudaMalloc((void**)&h->prof,8*(size_t)h->N*sizeof(long long))); CK(cudaMemsetAsync(h->prof,0,8*(size_t)h->N*sizeof(long long),h->stream)); }
-    if(host_out&&h->prof){ CK(cudaMemcpyAsync(host_out,h->prof,8*(size_t)h->N*sizeof(long long),cudaMemcpyDeviceToHost,h->stream)); CK(cudaStreamSynchronize(h->stream)); }
+    if(enable&&!h->prof){ CK(cudaMalloc((void**)&h->prof,10*(size_t)h->N*sizeof(long long))); CK(cudaMemsetAsync(h->prof,0,10*(size_t)h->N*sizeof(long long),h->stream)); }
+    if(host_out&&h->prof){ CK(cudaMemcpyAsync(host_out,h->prof,10*(size_t)h->N*sizeof(long long),cudaMemcpyDeviceToHost,h->stream)); CK(cudaStreamSynchronize(h->stream)); }
     return WBC_OK;
+}
+// FP64 FMA peak of the device, measured: 8 independent DFMA chains per thread, 1024 threads x 2 CTAs per SM
+__global__ void wbc_fp64_peak_kernel(double* out,int iters){
+    double a0=1.0+threadIdx.x*1e-9,a1=a0+1,a2=a0+2,a3=a0+3,a4=a0+4,a5=a0+5,a6=a0+6,a7=a0+7; const double m=1.0000001,b=1e-9;
+    for(int i=0;i<iters;i++){ a0=fma(a0,m,b);a1=fma(a1,m,b);a2=fma(a2,m,b);a3=fma(a3,m,b);a4=fma(a4,m,b);a5=fma(a5,m,b);a6=fma(a6,m,b);a7=fma(a7,m,b); }
+    if(a0+a1+a2+a3+a4+a5+a6+a7==12345.678) out[0]=a0;
+}
+extern "C" int wbc_measure_fp64_peak(wbc_handle* h,double* gflops){
+    if(!h||!gflops) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const int iters=1<<16, grid=h->smCount*2, block=1024; cudaEvent_t e0,e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    wbc_fp64_peak_kernel<<<grid,block,0,h->stream>>>(h->com,256); h->launches++;
+    double best=0;
+    for(int rep=0;rep<3;rep++){
+        CK(cudaEventRecord(e0,h->stream)); wbc_fp64_peak_kernel<<<grid,block,0,h->stream>>>(h->com,iters); h->launches++; CK(cudaEventRecord(e1,h->stream));
+        CK(cudaEventSynchronize(e1)); float ms=0; CK(cudaEventElapsedTime(&ms,e0,e1));
+        const double gf=2.0*8.0*iters*(double)grid*block/(ms*1e-3)/1e9; if(gf>best) best=gf; }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); *gflops=best; return WBC_OK;
 }
 extern "C" const char* wbc_last_error(const wbc_handle* h){ return h?h->err.c_str():"null handle"; }

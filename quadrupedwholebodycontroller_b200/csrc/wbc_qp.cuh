@@ -84,7 +84,8 @@ struct QPCtx {
     int nFR,nFX,nAC,nIAC;
     int status, infeasible, unbounded, rampOffset;
     double tau;
-    long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 setup, 7 iterations
+    long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
+    double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
 };
 
 // ---------------------------------------------------------------- structured A and H
@@ -242,6 +243,7 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
 // QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
 WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    { const double f=nFR,z=nZ; c.flops+=2*f*f*z+2*f*z*z+z*z*z/3.0; }
     WBC_SYNC();
     LANE_FOR(e,42*LD) w.R[e]=0.0;
     WBC_SYNC();
@@ -314,6 +316,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=0.0; }
     LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=0.0; w.tB[i]= bCzero?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
     WBC_SYNC();
+    int nref=0;
     for(int r=0;r<=OPT_numRefinementSteps;r++){
         if(nFR>0){
             LANE_FOR(i,nFR) w.xTMP[(int)w.FR[i]]=0.0;
@@ -358,8 +361,10 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
             t-=Arow_times(w.qp,ii,w.dx); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
         rnrm=wbc_max(rnrm);
         WBC_SYNC();
+        nref=r;
         if(rnrm<OPT_epsIterRef) break;
     }
+    { const double a=nAC,f=nFR,z=nZ; c.flops+=(1.0+nref)*(2*a*a+4*f*a+4*f*z+4*f*f+4*z*z)+nref*(2*f*f+4*a*42.0); }
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
     LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=Acol_times(w.qp,ii,w.ym); t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); w.dyFX[ii]=t; }
@@ -425,6 +430,7 @@ WBC_DEV void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
 WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_isBound){
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nIAC=c.nIAC;
     c.tau=1.0; BC_idx=-1; BC_status=2 /*ST_UNDEFINED*/; BC_isBound=false; int tmp;
+    c.flops+=2.0*nIAC*42.0+10.0*(42+70);
     WBC_SYNC();
     // I.1 active constraints' duals
     LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=-w.dyAC[i]; }
@@ -659,6 +665,7 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
     const int lane=c.lane;
     if(updateCholesky&&ensureLI){ int rv=addConstraint_ensureLI(w,c,number,C_status); if(rv!=QP_OK) return rv; }
     const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
     WBC_SYNC();
     // row [wZ wY] = aFR' [Z Y]
     LANE_FOR(j,42) w.arow[j]=Ael(w.qp,number,j);
@@ -678,6 +685,7 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
     const int lane=c.lane;
     if(updateCholesky&&ensureLI){ int rv=addBound_ensureLI(w,c,number,B_status); if(rv!=QP_OK) return rv; }
     const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
     WBC_SYNC();
     const int lastfree=(int)w.FR[nFR-1];
     if(lastfree!=number) swapFree(w,c,number,lastfree);
@@ -697,6 +705,7 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
 // QProblem::removeConstraint (QProblem.cpp:3782-4012) without NZC test / flipper / R update (see file header)
 WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
     const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
     WBC_SYNC();
     const int number_idx=(int)w.posAC[number];
     if(number_idx<nAC-1){
@@ -717,6 +726,7 @@ WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
 // QProblem::removeBound (QProblem.cpp:4018-4252) without NZC test / flipper / R update (see file header)
 WBC_FN int removeBound(QPWork& w,QPCtx& c,int number){
     const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
     moveFixedToFree(w,c,number);
     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; QQ(ii,nFR)=0.0; QQ(number,i)=0.0; }
     WBC_SYNC();
@@ -845,6 +855,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane;
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
+    c.flops+=4.0*42*42+4.0*70*42;
     LANE_FOR(i,70){ w.zero[i]=0.0; double ax=Arow_times(w.qp,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again

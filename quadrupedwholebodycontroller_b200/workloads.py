@@ -101,3 +101,12 @@ def advance_state(state, dt=1.0 / 400.0):
     qn = np.stack([qw + dt * dqw, qx + dt * dqx, qy + dt * dqy, qz + dt * dqz])
     s["base_quat"] = np.ascontiguousarray(qn / np.linalg.norm(qn, axis=0, keepdims=True))
     return s
+
+
+def shard_range(n_total, rank, world_size):
+    """contiguous instance range [first, first+count) owned by `rank`: robots never migrate, no collective
+    on the hot path; the remainder goes to the lowest ranks."""
+    base, rem = divmod(int(n_total), int(world_size))
+    count = base + (1 if rank < rem else 0)
+    first = rank * base + min(rank, rem)
+    return first, count

@@ -1,0 +1,30 @@
+"""CPU: the synthetic workload generator (BASELINE.json configs) is counter based: sharding never changes a robot's data."""
+import numpy as np
+
+
+def test_shards_reproduce_the_full_batch(wl):
+    st, ref = wl.randomised(64, seed=1234, contacts="mixed", switching_frac=0.1)
+    for first, count in ((0, 16), (16, 16), (40, 24)):
+        s2, r2 = wl.randomised(count, seed=1234, first=first, contacts="mixed", switching_frac=0.1)
+        for k in st:
+            assert np.array_equal(st[k][:, first:first + count], s2[k]), k
+        assert np.array_equal(ref["contacts"][:, first:first + count], r2["contacts"])
+        assert np.array_equal(ref["switching"][first:first + count], r2["switching"])
+
+
+def test_contact_patterns(wl):
+    _, ref = wl.randomised(4000, seed=1, contacts="mixed")
+    n = ref["contacts"].sum(axis=0)
+    assert 0.45 < (n == 4).mean() < 0.55 and 0.35 < (n == 3).mean() < 0.45 and 0.07 < (n == 2).mean() < 0.13
+    _, ref = wl.randomised(256, seed=1, contacts="diagonal")
+    c = ref["contacts"]
+    assert ((c[0] == c[2]) & (c[1] == c[3]) & (c[0] != c[1])).all()
+
+
+def test_layout_is_structure_of_arrays(wl):
+    st, ref = wl.randomised(8)
+    assert st["q"].shape == (12, 8) and st["base_quat"].shape == (4, 8) and ref["contacts"].shape == (4, 8) and ref["contacts"].dtype == np.uint8
+    assert all(v.flags["C_CONTIGUOUS"] for v in list(st.values()) + list(ref.values()))
+    assert np.allclose(np.linalg.norm(st["base_quat"], axis=0), 1.0)
+    s2 = wl.advance_state(st)
+    assert np.allclose(s2["q"], st["q"] + st["qd"] / 400.0) and np.allclose(np.linalg.norm(s2["base_quat"], axis=0), 1.0)
