@@ -133,7 +133,8 @@ def main():
     n = args.robots or spec["n"]
     first = rank * n                                                   # weak scaling: contiguous shard [rank*n, (rank+1)*n) of the global batch
     st, ref = wl.randomised(n, seed=1234, first=first, contacts=spec["contacts"])
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)                          # a real (non-NULL) stream shared by torch's events and the library
+    torch.cuda.set_stream(stream)
     ctl = wbc.WholeBodyController(n, device=local, stream=stream.cuda_stream)
     ctl.profile(True)
     dst = {k: torch.from_numpy(v).to(dev) for k, v in st.items()}; dref = {k: torch.from_numpy(v).to(dev) for k, v in ref.items()}
