@@ -1,0 +1,102 @@
+// whole_body_controller_b200.hpp -- ROS-free C++ mirror of the reference's WholeBodyController for a BATCH of robots.
+//
+// Same class name, constants and hot-method names as include/anymal_wbc/whole_body_controller.hpp:27-63 of the
+// reference, so code written against the reference class reads the same; everything numerical is delegated to the CUDA
+// library through the C ABI (wbc_b200.h).  Header-only: link with -lwbc_b200.  No CPU fallback: the constructor throws
+// std::runtime_error if the library cannot use the requested CUDA device.
+//
+//   reference member / method                               here
+//   ------------------------------------------------------  ---------------------------------------------------------
+//   WholeBodyController()            (wbc.cpp:22-59)        WholeBodyController(nRobots, device, Params, stream)
+//   loadParameters()                 (wbc.cpp:122-148)      Params (same field names as the `params` struct, wbc.hpp:91-104)
+//   setInitialState()                (wbc.cpp:65-120)       setInitialState(first, count)
+//   jointStateCallback(msg)          (wbc.cpp:232-254)      jointStateCallback(q, qd)             [DOF order LH,LF,RF,RH x HAA,HFE,KFE]
+//   floatingBaseStateCallback(msg)   (wbc.cpp:187-230)      floatingBaseStateCallback(pos, quat_wxyz, twist)
+//   referenceCallback(msg)           (wbc.cpp:150-185)      referenceCallback(pose, vel, acc, swPos, swVel, swAcc, contacts[, switching])
+//   updateState/solveQP/computeJointTorques (wbc.cpp:256-577)   same names, whole batch, asynchronous on the stream
+//   jointTorquePub_ / desiredGroundReactionForcesPub_ / centerOfMassPub_ (wbc.cpp:558-576,666-670)   getJointTorques / getGroundReactionForces / getCenterOfMass
+//   qpSolution_, qpReturnValue_      (wbc.hpp:165-166)      getQpSolution, getQpReturnValues, getWorkingSetRecalculations, getWorkingSet
+//   controlLoop() body               (wbc.cpp:650-652)      step()
+//
+// Array convention of every pointer argument: structure-of-arrays, robot index fastest (a[k*N + i]), host or device memory.
+#ifndef WHOLE_BODY_CONTROLLER_B200_HPP
+#define WHOLE_BODY_CONTROLLER_B200_HPP
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "wbc_b200.h"
+
+namespace anymal_wbc_b200 {
+
+const int numberOfJoints = WBC_NUM_JOINTS;                 // wbc.hpp:28
+const int numberOfLegs = WBC_NUM_LEGS;                     // wbc.hpp:29
+const double gravityAcceleration = 9.81;                   // wbc.hpp:30
+const int qpNumberOfVariables = 6 + numberOfJoints + 3 * numberOfLegs + 3 * numberOfLegs;                                   // wbc.hpp:31
+const int qpNumberOfConstraints = 6 + 3 * numberOfLegs + 4 * numberOfLegs + numberOfJoints + 6 * numberOfLegs;              // wbc.hpp:32
+static_assert(qpNumberOfVariables == WBC_QP_NV && qpNumberOfConstraints == WBC_QP_NC, "QP dimensions of the reference");
+
+class WholeBodyController {
+public:
+    struct Params : wbc_params {                          // wbc.hpp:91-104; defaults = config/params_controller.yaml
+        Params() { wbc_default_params(this); }
+    };
+
+    explicit WholeBodyController(int nRobots = 1, int device = 0, const Params& params = Params(), void* cudaStream = nullptr)
+        : n_(nRobots) {
+        const int rc = wbc_create(nRobots, device, &params, cudaStream, &h_);
+        if (rc != WBC_OK) throw std::runtime_error("WholeBodyController: wbc_create failed with code " + std::to_string(rc) +
+                                                   " (no usable sm_100a CUDA device? there is no CPU fallback)");
+    }
+    ~WholeBodyController() { if (h_) wbc_destroy(h_); }
+    WholeBodyController(const WholeBodyController&) = delete;
+    WholeBodyController& operator=(const WholeBodyController&) = delete;
+
+    int numberOfRobots() const { return n_; }
+
+    void setInitialState() { check(wbc_reset(h_, 0, n_)); }
+    void setInitialState(int first, int count) { check(wbc_reset(h_, first, count)); }
+
+    void jointStateCallback(const double* jointPos, const double* jointVel) { check(wbc_set_state(h_, jointPos, jointVel, nullptr, nullptr, nullptr)); }
+    void floatingBaseStateCallback(const double* basePos, const double* baseQuatWXYZ, const double* baseTwist) {
+        check(wbc_set_state(h_, nullptr, nullptr, basePos, baseQuatWXYZ, baseTwist));
+    }
+    void referenceCallback(const double* desiredPose, const double* desiredCoMVelocity, const double* desiredCoMAcceleration,
+                           const double* desiredSwingLegsPosition, const double* desiredSwingLegsVelocity, const double* desiredSwingLegsAcceleration,
+                           const unsigned char* footContacts, const unsigned char* isSwitchingFootState = nullptr) {
+        check(wbc_set_reference(h_, desiredPose, desiredCoMVelocity, desiredCoMAcceleration, desiredSwingLegsPosition, desiredSwingLegsVelocity,
+                                desiredSwingLegsAcceleration, footContacts, isSwitchingFootState));
+    }
+
+    void updateState() { check(wbc_update_state(h_)); }
+    void solveQP() { check(wbc_solve_qp(h_)); }
+    void computeJointTorques() { check(wbc_compute_joint_torques(h_)); }
+    void step() { check(wbc_step(h_)); }                    // the body of controlLoop(), wbc.cpp:650-652
+    void synchronize() { check(wbc_synchronize(h_)); }
+
+    void getJointTorques(double* tau) { check(wbc_get_outputs(h_, tau, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr)); }
+    void getGroundReactionForces(double* grf) { check(wbc_get_outputs(h_, nullptr, grf, nullptr, nullptr, nullptr, nullptr, nullptr)); }
+    void getQpSolution(double* x) { check(wbc_get_outputs(h_, nullptr, nullptr, x, nullptr, nullptr, nullptr, nullptr)); }
+    void getQpReturnValues(int* rc) { check(wbc_get_outputs(h_, nullptr, nullptr, nullptr, rc, nullptr, nullptr, nullptr)); }
+    void getWorkingSetRecalculations(int* nWSR) { check(wbc_get_outputs(h_, nullptr, nullptr, nullptr, nullptr, nWSR, nullptr, nullptr)); }
+    void getWorkingSet(signed char* ws) { check(wbc_get_outputs(h_, nullptr, nullptr, nullptr, nullptr, nullptr, ws, nullptr)); }
+    void getCenterOfMass(double* com) { check(wbc_get_outputs(h_, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, com)); }
+    void getOutputs(double* tau, double* grf, double* x, int* rc, int* nWSR, signed char* ws, double* com) {
+        check(wbc_get_outputs(h_, tau, grf, x, rc, nWSR, ws, com));
+    }
+    // the dense QP of one robot exactly as the reference hands it to qpOASES (wbc.cpp:479-515), row-major
+    void getDenseQP(int robot, double* H, double* g, double* A, double* lbA, double* ubA) { check(wbc_get_dense_qp(h_, robot, H, g, A, lbA, ubA)); }
+
+    wbc_handle* handle() { return h_; }
+
+private:
+    void check(int rc) const {
+        if (rc != WBC_OK) throw std::runtime_error(std::string("WholeBodyController: ") + wbc_last_error(h_) + " (code " + std::to_string(rc) + ")");
+    }
+    wbc_handle* h_ = nullptr;
+    int n_ = 0;
+};
+
+}  // namespace anymal_wbc_b200
+#endif

@@ -1,7 +1,7 @@
 """Batched ANYmal whole-body controller for NVIDIA B200 (sm_100a) -- Python binding of the C ABI (include/wbc_b200.h).
 
 The product is the CUDA shared library `libwbc_b200.so` (csrc/wbc_kernels.cu); this module is a thin ctypes front-end used by
-the tests and bench.py.  The host-language mirror of the reference's C++ class lives in csrc/whole_body_controller.hpp.
+the tests and bench.py.  The C++ mirror of the reference class is include/whole_body_controller_b200.hpp.
 There is no CPU fallback: constructing a controller without the library or without a CUDA device raises.
 """
 import ctypes as C
