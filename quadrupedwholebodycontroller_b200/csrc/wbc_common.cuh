@@ -22,6 +22,8 @@
   WBC_DEV double wbc_bcast(double v,int src){ return __shfl_sync(0xffffffffu,v,src); }
   WBC_DEV int    wbc_bcasti(int v,int src){ return __shfl_sync(0xffffffffu,v,src); }
   WBC_DEV int    wbc_ffs(unsigned m){ return __ffs(m)-1; }
+  WBC_DEV int    wbc_popc(unsigned m){ return __popc(m); }
+  WBC_DEV int    wbc_rank(unsigned m,int lane){ return __popc(m&((1u<<lane)-1u)); }   // set bits below `lane`
 #else
   #define WBC_DEV static inline
   #define WBC_HD  static inline
@@ -33,9 +35,16 @@
   WBC_DEV double wbc_bcast(double v,int){ return v; }
   WBC_DEV int    wbc_bcasti(int v,int){ return v; }
   WBC_DEV int    wbc_ffs(unsigned m){ return m?0:-1; }
+  WBC_DEV int    wbc_popc(unsigned m){ return m?1:0; }
+  WBC_DEV int    wbc_rank(unsigned,int){ return 0; }
 #endif
 
-#define LANE_FOR(i,n) for(int i=lane;i<(n);i+=WBC_NL)
+// element loops are NOT unrolled: the solver is instruction-cache bound (453 KB of code vs a 32 KB L1.5), not issue bound
+#if defined(__CUDACC__)
+  #define LANE_FOR(i,n) _Pragma("unroll 1") for(int i=lane;i<(n);i+=WBC_NL)
+#else
+  #define LANE_FOR(i,n) for(int i=lane;i<(n);i+=WBC_NL)
+#endif
 
 namespace wbc {
 

@@ -45,18 +45,23 @@ constexpr double OPT_terminationTolerance=5.0e6*QEPS, OPT_boundTolerance=1.0e6*Q
                  OPT_epsLITests=1.0e5*QEPS, OPT_ramp0=0.5, OPT_ramp1=1.0;
 constexpr int OPT_numRefinementSteps=2;
 
-constexpr int LD=43;                  // leading dimension of Q, R, T (odd: conflict-free row AND column sweeps)
-#define QQ(i,j) w.Q[(i)+LD*(j)]       // Types.hpp:141-147: Q, R column-major, T row-major
-#define RR(i,j) w.R[(i)+LD*(j)]
-#define TT(i,j) w.T[(i)*LD+(j)]
-constexpr int SIZET=42;
+constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
+constexpr int SIZET=42;               // sizeT = min(nV,nC)
+#define QQ(i,j) w.Q[(i)+LD*(j)]       // Types.hpp:141-147: Q column-major
+// R (nZ x nZ upper triangular) and T (nAC x nAC reverse triangular) are the only parts of the reference's 42x42 R and T
+// arrays that are ever read, and nZ + nAC = nFR <= 42, so both live PACKED in one 903-entry buffer: T's row i (its i+1
+// entries TT(i,sizeT-1-i) .. TT(i,sizeT-1)) grows from the front, R's column j (RR(0,j) .. RR(j,j)) from the back.
+constexpr int TRI42=42*43/2;
+WBC_HD int tri(int i){ return (i*(i+1))>>1; }
+#define RR(i,j) w.RT[TRI42-1-(tri(j)+(i))]
+#define TT(i,j) w.RT[tri(i)+(SIZET-1-(j))]
 #if defined(__CUDACC__)
   #define WBC_TIC(t) long long t=clock64()
   #define WBC_TOC(t,k) { long long n_=clock64(); c.prof[k]+=n_-t; t=n_; }
 #else
   #define WBC_TIC(t) long long t=0
   #define WBC_TOC(t,k) { (void)t; }
-#endif               // sizeT = min(nV,nC)
+#endif
 
 // persistent solver state of one instance between ticks (HBM) -- what SQProblem keeps across hotstarts
 struct QPState {
@@ -65,16 +70,25 @@ struct QPState {
     int rampOffset, status, pad_;
 };
 
-// per-instance shared-memory workspace
+// per-instance shared-memory workspace (40.6 KB -> 5 instances per SM)
 struct QPWork {
-    double Q[42*LD], R[42*LD], T[42*LD];
+    double Q[42*LD];
+    double RT[TRI42+1];                         // packed R and T (see RR / TT)
     QPData qp;                                  // compact H, A, new g / lbA / ubA
     double x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
-    double lbF[42], ubF[42], lbAF[70], ubAF[70];                 // far-bounded targets of the current homotopy
     double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
     double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
-    double tA[42], tB[42], xFRy[42], xFRz[42], Zdz[42], xTMP[42], yTMP[42];
-    double dAx[70], num[70], den[70], cs_c[42], cs_s[42], wv[42], tmpv[42], HZf[12*LD], zero[70], vm[42], ym[70], arow[42], rdR[42], rdT[42];
+    double rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
+    // phase-local scratch, overlaid: {ratio tests | step-direction temporaries} + LI-exchange vectors + Givens / row vectors,
+    // all of it reused as the 12 x nZ block (HZ)_force by the projected Cholesky (which runs when none of them is live)
+    union {
+        struct {
+            union { struct { double num[70], den[70], dAx[70]; }; struct { double tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; };
+            double xFRy[42], xFRz[42], Zdz[42], ym[70];
+            double wv[42], cs_c[42], cs_s[42], tmpv[42], arow[42];
+        };
+        double HZf[12*LD];
+    };
     signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70];
 };
 
@@ -83,6 +97,8 @@ struct QPCtx {
     int lane;
     int nFR,nFX,nAC,nIAC;
     int status, infeasible, unbounded, rampOffset;
+    int farRampOffset;   // rampOffset at the last updateFarBounds
+    double farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
     double tau;
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
     double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
@@ -103,7 +119,7 @@ WBC_HD double Hel(const QPData& q,int i,int j){
 }
 // Structured products with A (whole_body_controller.cpp:492-497): no per-element decoding, only the non-zero blocks.
 // Arow_times: (A v)_i for a 42-vector v (callers mask v to the free / fixed columns beforehand, 0-entries add exactly 0).
-WBC_DEV double Arow_times(const QPData& q,int i,const double* v){
+WBC_FN double Arow_times(const QPData& q,int i,const double* v){
     double s=0;
     if(i<6){ for(int j=0;j<6;j++) s+=q.Mbb[6*i+j]*v[j]; for(int f=0;f<12;f++) s-=(q.cmask[f/3]*q.Jc[18*f+i])*v[18+f]; return s; }
     if(i<18){ const int r=i-6; const double c=q.cmask[r/3]; if(c==0.0) return 0.0; for(int j=0;j<18;j++) s+=q.Jc[18*r+j]*v[j]; return s; }
@@ -113,7 +129,7 @@ WBC_DEV double Arow_times(const QPData& q,int i,const double* v){
     { const int r=(i<58)?i-46:i-58; const double c=1.0-q.cmask[r/3]; if(c!=0.0) for(int j=0;j<18;j++) s+=q.Jc[18*r+j]*v[j]; return (i<58)? s-v[30+r] : s+v[30+r]; }
 }
 // Acol_times: (A' y)_j for a 70-vector y by constraint number (0 for inactive constraints), rows visited in ascending order
-WBC_DEV double Acol_times(const QPData& q,int j,const double* y){
+WBC_FN double Acol_times(const QPData& q,int j,const double* y){
     double s=0;
     if(j<18){
         if(j<6) for(int i=0;i<6;i++) s+=q.Mbb[6*i+j]*y[i];
@@ -131,15 +147,15 @@ WBC_DEV double Acol_times(const QPData& q,int j,const double* y){
         return s; }
     return y[58+(j-30)]-y[46+(j-30)];
 }
-WBC_DEV double Hrow_dot(const QPWork& w,int i,const double* v,int sel){
+WBC_FN double Hrow_dot(const QPWork& w,int i,const double* v,int sel){
     double s=0;
     if(i>=18&&i<30){ for(int j=18;j<30;j++){ if(sel!=2 && ((w.bstat[j]!=0)!=(sel==1))) continue; s+=w.qp.Hff[12*(i-18)+(j-18)]*v[j]; } return s; }
     if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return 0.0;
     return ((i>=30)?w.qp.rho:1.0)*v[i];
 }
 // masked copies: vm = v restricted to free (sel 0) / fixed (sel 1) variables; ym = yAC scattered to constraint numbers
-WBC_DEV void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
-WBC_DEV void scatter_yAC(QPWork& w,const QPCtx& c,const double* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:0.0; WBC_SYNC(); }
+WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
+WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const double* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:0.0; WBC_SYNC(); }
 
 // ---------------------------------------------------------------- index lists (Indexlist.cpp: insertion-ordered number[])
 // removal keeps the order of the remaining entries; every lane holds the same counters, one lane edits the list
@@ -159,96 +175,163 @@ WBC_DEV void moveActiveToInactive(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); li
 WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ WBC_SYNC(); if(c.lane==0){ int a=0,b=0; while(w.FR[a]!=n1) a++; while(w.FR[b]!=n2) b++; signed char t=w.FR[a]; w.FR[a]=w.FR[b]; w.FR[b]=t; } WBC_SYNC(); }
 
 // ---------------------------------------------------------------- triangular solves
-constexpr int SLOTS=(42+WBC_NL-1)/WBC_NL;
-// Column-oriented forward substitution for a lower-triangular system L u = b of size n:
-//   u_k = (b_k - sum_{j<k} L(k,j) u_j) * rdiag(k).  Each lane owns rows lane, lane+NL, ..., keeps their running sums in
-//   registers and subtracts the terms in ascending j, the order of the reference's row loops; u_k travels by one shuffle.
-//   Diagonals enter as precomputed reciprocals (fp64 division is ~20x the latency of a multiply and sat on the critical
-//   path of every one of the 42 steps); pivots are validated where the reciprocals are formed.
-template<class LGet,class BGet,class ASet,class RGet>
-WBC_DEV void trisolve(int lane,int n,LGet L,BGet B,ASet A,RGet RD){
-    double sum_[SLOTS], rd_[SLOTS], l_[SLOTS];
-    #pragma unroll
-    for(int s_=0;s_<SLOTS;s_++){ const int r_=lane+WBC_NL*s_; const bool in=r_<n; sum_[s_]=in?B(r_):0.0; rd_[s_]=in?RD(r_):0.0; l_[s_]=(in&&r_>0)?L(r_,0):0.0; }
-    WBC_SYNC();
-    for(int k_=0;k_<n;k_++){
-        double mine_=0.0;
-        #pragma unroll
-        for(int s_=0;s_<SLOTS;s_++) if(lane+WBC_NL*s_==k_) mine_=sum_[s_]*rd_[s_];
-        const double ak_=wbc_bcast(mine_,k_%WBC_NL);
-        if((k_%WBC_NL)==lane) A(k_,ak_);
-        #pragma unroll
-        for(int s_=0;s_<SLOTS;s_++){ const int r_=lane+WBC_NL*s_; const bool act=(r_>k_&&r_<n);
-            const double nl=(r_>k_+1&&r_<n)?L(r_,k_+1):0.0;         // next column's entry, independent of the chain
-            if(act) sum_[s_]-=l_[s_]*ak_;
-            l_[s_]=nl; }
+// Forward substitution L u = b,  u_k = (b[k*bs] - sum_{j<k} L(k,j) u_j) * rd[k*rs],  a[k*as] = u_k, for the four triangular
+// systems of the method (QProblem::backsolveT :4518-4565, QProblemB::backsolveR :1635-1688) on the packed R/T buffer:
+//   kind 0: T    L(i,j) = TT(i,sizeT-1-j)          kind 1: T'   L(i,j) = TT(n-1-j,sizeT-n+i)
+//   kind 2: R'   L(i,j) = RR(j,i)                  kind 3: R    L(i,j) = RR(n-1-i,n-1-j)
+// In packed storage the address of L(i,j+1) is that of L(i,j) plus d0 + j*dd with (d0,dd) = (1,0), (-(n-1),1), (-1,0), (n-1,-1),
+// so ONE routine (one copy of the code: the solver is instruction-cache bound) walks all four.
+// Column-oriented: lane r owns row r (and r+32), keeps its running sum in a register and subtracts the terms in
+// ascending j, the order of the reference's row loops; u_k travels by one shuffle.  Diagonals enter as precomputed
+// reciprocals (fp64 division is ~20x the latency of a multiply and sat on the critical path of every step).
+WBC_DEV int trisolve_row0(int kind,int n,int i){      // packed index of L(i,0)
+    return kind==0? tri(i) : kind==1? tri(n-1)+n-1-i : kind==2? TRI42-1-tri(i) : TRI42-1-(tri(n-1)+n-1-i);
+}
+WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,int bs,double* a,int as,const double* rd,int rs){
+    const int d0= kind==0? 1 : kind==1? -(n-1) : kind==2? -1 : n-1, dd= kind==1? 1 : kind==3? -1 : 0;
+#if WBC_NL==1
+    (void)lane; double u[42];
+    for(int k=0;k<n;k++){ double sum=b[k*bs]; int off=trisolve_row0(kind,n,k), d=d0;
+        for(int j=0;j<k;j++){ sum-=RT[off]*u[j]; off+=d; d+=dd; }
+        u[k]=sum*rd[k*rs]; }
+    for(int k=0;k<n;k++) a[k*as]=u[k];
+#else
+    const bool in0=lane<n, in1=lane+32<n;
+    int o0=in0?trisolve_row0(kind,n,lane):0, d=d0;
+    double s0=in0?b[lane*bs]:0.0, r0=in0?rd[lane*rs]:0.0, l0=(in0&&lane>0)?RT[o0]:0.0;
+    WBC_SYNC();                                              // a may alias b
+    if(n<=32){
+        for(int k=0;k<n;k++){
+            const double ak=__shfl_sync(0xffffffffu,s0*r0,k);
+            o0+=d; d+=dd;
+            const double nl=(lane>k+1&&in0)?RT[o0]:0.0;      // next column's entry, independent of the chain
+            if(lane==k) a[k*as]=ak;
+            if(lane>k) s0-=l0*ak;
+            l0=nl;
+        }
+    } else {
+        int o1=in1?trisolve_row0(kind,n,lane+32):0;
+        double s1=in1?b[(lane+32)*bs]:0.0, r1=in1?rd[(lane+32)*rs]:0.0, l1=in1?RT[o1]:0.0;
+        for(int k=0;k<n;k++){
+            const double mine=(k<32)?s0*r0:s1*r1;
+            const double ak=__shfl_sync(0xffffffffu,mine,k&31);
+            o0+=d; o1+=d; d+=dd;
+            const double nl0=(lane>k+1&&in0)?RT[o0]:0.0, nl1=(lane+32>k+1&&in1)?RT[o1]:0.0;
+            if(lane==(k&31)) a[k*as]=ak;
+            if(lane>k) s0-=l0*ak;
+            if(lane+32>k&&in1) s1-=l1*ak;
+            l0=nl0; l1=nl1;
+        }
     }
+#endif
     WBC_SYNC();
 }
 // reciprocals of T's diagonal TT(k, sizeT-1-k); false if a pivot fails the |.| > EPS test of QProblem::backsolveT
-WBC_DEV bool prepare_T(QPWork& w,const QPCtx& c){
+WBC_FN bool prepare_T(QPWork& w,const QPCtx& c){
     const int lane=c.lane; bool bad=false; WBC_SYNC();
     LANE_FOR(k,c.nAC){ const double d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=1.0/d; }
     WBC_SYNC();
     return wbc_ballot(bad)==0u;
 }
 // QProblem::backsolveT (QProblem.cpp:4518-4565).  b, a indexed by AC position.  prepare_T must have run since T last changed.
+// unknown u_k = a[nT-1-k]; row i, column j<i:  TT(i,sizeT-1-j)  resp.  TT(nT-1-j,tcol+i) for the transposed system
 WBC_DEV void backsolveT(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a){
-    const int lane=c.lane, nT=c.nAC, tcol=SIZET-nT;
+    const int nT=c.nAC;
     if(nT<=0) return;
-    WBC_SYNC();
-    // unknown u_k = a[nT-1-k]; row i, column j<i:  TT(i,sizeT-1-j)  resp.  TT(nT-1-j,tcol+i) for the transposed system
-    if(!transposed) trisolve(lane,nT,[&](int i,int j){ return TT(i,SIZET-1-j); },[&](int r){ return b[r]; },[&](int k,double v){ a[nT-1-k]=v; },[&](int k){ return w.rdT[k]; });
-    else trisolve(lane,nT,[&](int i,int j){ return TT(nT-1-j,tcol+i); },[&](int r){ return b[r]; },[&](int k,double v){ a[nT-1-k]=v; },[&](int k){ return w.rdT[nT-1-k]; });
+    if(!transposed) trisolve(c.lane,0,nT,w.RT,b,1,a+nT-1,-1,w.rdT,1);
+    else            trisolve(c.lane,1,nT,w.RT,b,1,a+nT-1,-1,w.rdT+nT-1,-1);
 }
 // QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b.  w.rdR = 1/diag(R).
 WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a,int nR){
-    const int lane=c.lane;
     if(nR<=0) return;
-    WBC_SYNC();
-    if(transposed) trisolve(lane,nR,[&](int i,int j){ return RR(j,i); },[&](int r){ return b[r]; },[&](int k,double v){ a[k]=v; },[&](int k){ return w.rdR[k]; });
-    else trisolve(lane,nR,[&](int i,int j){ return RR(nR-1-i,nR-1-j); },[&](int r){ return b[nR-1-r]; },[&](int k,double v){ a[nR-1-k]=v; },[&](int k){ return w.rdR[nR-1-k]; });
+    if(transposed) trisolve(c.lane,2,nR,w.RT,b,1,a,1,w.rdR,1);
+    else           trisolve(c.lane,3,nR,w.RT,b+nR-1,-1,a+nR-1,-1,w.rdR+nR-1,-1);
 }
 
 // ---------------------------------------------------------------- factorisations
 // QProblem::setupTQfactorisation (QProblem.cpp:2169-2193)
 WBC_DEV void setupTQfactorisation(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(e,42*LD){ w.Q[e]=0.0; w.T[e]=0.0; }
+    LANE_FOR(e,42*LD) w.Q[e]=0.0;                     // packed T needs no clearing: every entry of a row is written when the row is created
     WBC_SYNC();
     LANE_FOR(i,c.nFR) QQ((int)w.FR[i],i)=1.0;
     WBC_SYNC();
 }
-// DPOTRF "U" of LAPACKReplacement.cpp:39-77 on the leading n x n block of R; column j is owned by lane j%NL and its
-// inner products run k = i-1 .. 0 like the reference.  returns false if not SPD.
+// DPOTRF "U" of LAPACKReplacement.cpp:39-77 on the leading n x n block of R.  Row i: lane t owns column i+t (+32); its
+// inner product runs k = i-1 .. 0 like the reference; lane 0 holds the diagonal's sum, which travels by one shuffle.
+// returns false if not SPD.
 WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
     const int lane=c.lane;
+    WBC_SYNC();
+#if WBC_NL==1
     for(int i=0;i<n;i++){
-        WBC_SYNC();
-        double sum=RR(i,i);
-        #pragma unroll 4
-        for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);      // every lane, same value (broadcast reads)
+        double sum=RR(i,i); for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);
+        if(!(sum>0.0)) return false;
+        const double d=sqrt(sum), rd=1.0/d; RR(i,i)=d; w.rdR[i]=rd;
+        for(int j=i+1;j<n;j++){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=s2*rd; }
+    }
+#else
+    for(int i=0;i<n;i++){
+        const int j0=i+lane, j1=j0+32;
+        double s0=(j0<n)?RR(i,j0):0.0, s1=(j1<n)?RR(i,j1):0.0;
+        if(j1<n){
+            #pragma unroll 2
+            for(int k=i-1;k>=0;k--){ const double rki=RR(k,i); s0-=rki*RR(k,j0); s1-=rki*RR(k,j1); }
+        } else if(j0<n){
+            #pragma unroll 4
+            for(int k=i-1;k>=0;k--) s0-=RR(k,i)*RR(k,j0);
+        }
+        const double sum=wbc_bcast(s0,0);
         if(!(sum>0.0)) return false;
         const double d=sqrt(sum), rd=1.0/d;
+        if(lane==0){ RR(i,i)=d; w.rdR[i]=rd; }
+        else if(j0<n) RR(i,j0)=s0*rd;
+        if(j1<n) RR(i,j1)=s1*rd;
         WBC_SYNC();
-        if(lane==(i%WBC_NL)){ RR(i,i)=d; w.rdR[i]=rd; }
-        for(int j=i+1+lane;j<n;j+=WBC_NL){ double s2=RR(i,j);
-            #pragma unroll 4
-            for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j);
-            RR(i,j)=s2*rd; }
     }
-    WBC_SYNC();
+#endif
     return true;
+}
+// R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk) for the upper triangle, register-tiled: each lane accumulates one TS x TS
+// tile (the upper tiles of an nt x nt tile grid, nt(nt+1)/2 <= 32) over the free variables in list order -- same products
+// and same summation order as the scalar loops of SymDenseMat::bilinear (Matrices.cpp:630-667).
+template<int TS> WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
+    const int lane=c.lane, nt=(nZ+TS-1)/TS, ntiles=nt*(nt+1)/2;
+    LANE_FOR(t,ntiles){
+        int ti=0, rem=t; while(rem>=nt-ti){ rem-=nt-ti; ti++; } const int tj=ti+rem;
+        double acc[TS][TS];
+        #pragma unroll
+        for(int a=0;a<TS;a++){
+            #pragma unroll
+            for(int b=0;b<TS;b++) acc[a][b]=0.0; }
+        for(int ii=0;ii<nFR;ii++){
+            const int v=(int)w.FR[ii]; double zj[TS],wk[TS];
+            #pragma unroll
+            for(int b=0;b<TS;b++) zj[b]=QQ(v,TS*tj+b);
+            if(v>=18&&v<30){
+                #pragma unroll
+                for(int a=0;a<TS;a++) wk[a]=w.HZf[(v-18)*LD+TS*ti+a];
+            } else { const double dv=(v>=30)?w.qp.rho:1.0;
+                #pragma unroll
+                for(int a=0;a<TS;a++) wk[a]=dv*QQ(v,TS*ti+a); }
+            #pragma unroll
+            for(int a=0;a<TS;a++){
+                #pragma unroll
+                for(int b=0;b<TS;b++) acc[a][b]+=zj[b]*wk[a]; }
+        }
+        #pragma unroll
+        for(int a=0;a<TS;a++){
+            #pragma unroll
+            for(int b=0;b<TS;b++){ const int kk=TS*ti+a, jj=TS*tj+b; if(kk<=jj&&jj<nZ) RR(kk,jj)=acc[a][b]; } }
+    }
 }
 // QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
 WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
     { const double f=nFR,z=nZ; c.flops+=2*f*f*z+2*f*z*z+z*z*z/3.0; }
     WBC_SYNC();
-    LANE_FOR(e,42*LD) w.R[e]=0.0;
-    WBC_SYNC();
     if(c.nFX+c.nAC==0){
-        LANE_FOR(i,nFR) for(int j=0;j<nFR;j++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+        LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
         if(!potrf_R(w,c,nFR)) return QP_RET_HESSIAN_NOT_SPD;
         return QP_OK;
     }
@@ -258,46 +341,20 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
         LANE_FOR(i,42) for(int j=0;j<nZ;j++) QQ(i,j)=0.0;
         WBC_SYNC();
         LANE_FOR(j,nZ) QQ((int)w.FR[j],j)=1.0;
-        LANE_FOR(i,nFR) for(int j=0;j<nFR;j++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+        LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
     } else {
         // Z'HZ (SymDenseMat::bilinear, Matrices.cpp:630-667).  H = diag except the 12x12 force block, so
-        // (HZ)(v,k) = H_vv Z(v,k) for v outside the block; inside, the sum runs over the free force variables in list order.
-        LANE_FOR(k,nZ) for(int a=0;a<12;a++){ double s=0;
-            if(w.bstat[18+a]==0){ for(int i=0;i<nFR;i++){ int v=(int)w.FR[i]; if(v>=18&&v<30) s+=w.qp.Hff[12*a+(v-18)]*QQ(v,k); } }
+        // (HZ)(v,k) = H_vv Z(v,k) for v outside the block; inside, the sum runs over the free force variables in list order
+        // (w.rdT = that sub-list, built with ballots; prepare_T rewrites rdT before its next use).  Hff is bitwise symmetric, read as Hff[u][a] for unit stride in a.
+        int nff=0;
+        for(int base=0;base<nFR;base+=WBC_NL){ const int i=base+lane; const int v=(i<nFR)?(int)w.FR[i]:0; const bool isf=(i<nFR)&&v>=18&&v<30;
+            const unsigned m=wbc_ballot(isf); if(isf) w.rdT[nff+wbc_rank(m,lane)]=(double)(v-18); nff+=wbc_popc(m); }
+        WBC_SYNC();
+        LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; double s=0;
+            for(int i=0;i<nff;i++){ const int u=(int)w.rdT[i]; s+=w.qp.Hff[12*u+a]*QQ(18+u,k); }
             w.HZf[a*LD+k]=s; }
         WBC_SYNC();
-        // R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk), upper triangle only (the rest is never read).
-        // Register-tiled: each lane accumulates one 6x6 tile (28 upper tiles of the 7x7 tile grid) over the free
-        // variables in list order -- same products, same summation order as the scalar loops, ~36 FMAs per 12 loads.
-        LANE_FOR(t,28){
-            int ti=0, rem=t; while(rem>=7-ti){ rem-=7-ti; ti++; } const int tj=ti+rem;
-            if(6*tj>=nZ&&6*ti>=nZ) continue;
-            if(6*ti>=nZ) continue;
-            double acc[6][6];
-            #pragma unroll
-            for(int a=0;a<6;a++){
-                #pragma unroll
-                for(int b=0;b<6;b++) acc[a][b]=0.0; }
-            for(int ii=0;ii<nFR;ii++){
-                const int v=(int)w.FR[ii]; double zj[6],wk[6];
-                #pragma unroll
-                for(int b=0;b<6;b++) zj[b]=QQ(v,6*tj+b);
-                if(v>=18&&v<30){
-                    #pragma unroll
-                    for(int a=0;a<6;a++) wk[a]=w.HZf[(v-18)*LD+6*ti+a];
-                } else { const double dv=(v>=30)?w.qp.rho:1.0;
-                    #pragma unroll
-                    for(int a=0;a<6;a++) wk[a]=dv*QQ(v,6*ti+a); }
-                #pragma unroll
-                for(int a=0;a<6;a++){
-                    #pragma unroll
-                    for(int b=0;b<6;b++) acc[a][b]+=zj[b]*wk[a]; }
-            }
-            #pragma unroll
-            for(int a=0;a<6;a++){
-                #pragma unroll
-                for(int b=0;b<6;b++){ const int kk=6*ti+a, jj=6*tj+b; if(kk<=jj&&jj<nZ) RR(kk,jj)=acc[a][b]; } }
-        }
+        if(nZ<=14) zhz_tiles<2>(w,c,nFR,nZ); else if(nZ<=28) zhz_tiles<4>(w,c,nFR,nZ); else zhz_tiles<6>(w,c,nFR,nZ);
     }
     if(!potrf_R(w,c,nZ)) return QP_RET_HESSIAN_NOT_SPD;
     return QP_OK;
@@ -312,9 +369,9 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
     if(!prepare_T(w,c)) return QP_RET_STEPDIRECTION_FAILED_TQ;
     // I) delta_xFX
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= bBzero?0.0:((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= (bBzero||!dlb)?0.0:((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=0.0; }
-    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=0.0; w.tB[i]= bCzero?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
+    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=0.0; w.tB[i]= (bCzero||!dlbA)?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
     WBC_SYNC();
     int nref=0;
     for(int r=0;r<=OPT_numRefinementSteps;r++){
@@ -353,15 +410,16 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.dx[ii]+=w.xTMP[ii]; }
         LANE_FOR(i,nAC) w.dyAC[i]+=w.yTMP[i];
         WBC_SYNC();
+        nref=r;
+        if(r==OPT_numRefinementSteps) break;                 // the reference computes one more residual here and never reads it
         // residuals for the next refinement pass
         double rnrm=0.0;
         scatter_yAC(w,c,w.dyAC);
         LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0); t+=Hrow_dot(w,ii,w.dx,1); t-=Acol_times(w.qp,ii,w.ym); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= bCzero?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= (bCzero||!dlbA)?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
             t-=Arow_times(w.qp,ii,w.dx); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
         rnrm=wbc_max(rnrm);
         WBC_SYNC();
-        nref=r;
         if(rnrm<OPT_epsIterRef) break;
     }
     { const double a=nAC,f=nFR,z=nZ; c.flops+=(1.0+nref)*(2*a*a+4*f*a+4*f*z+4*f*f+4*z*z)+nref*(2*f*f+4*a*42.0); }
@@ -377,7 +435,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
 // list sequentially, replacing the candidate whenever num_i < t*den_i with the CURRENT t.  Exactly the same chain of
 // winners is produced here: a ballot finds the first later entry that beats the current t, t is updated, repeat.
 // stat == 0: plain test (performPlainRatioTest, QProblem.cpp:4256-4275: num > epsNum, den > epsDen, t*den > num).
-WBC_DEV void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const double* num,const double* den,
+WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const double* num,const double* den,
                               double& t,int& BC_idx){
     const int lane=c.lane; BC_idx=-1; int pos=0;
     WBC_SYNC();
@@ -400,11 +458,20 @@ WBC_DEV void performRatioTest(const QPCtx& c,int n,const signed char* idx,const 
 }
 
 // ---------------------------------------------------------------- data shift, step, termination
-// QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are w.qp.gf (g_new), lbF/ubF/lbAF/ubAF
-WBC_DEV void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
+// Targets of the current homotopy = the user's data with every infinite side replaced by a far bound (QProblem::updateFarBounds,
+// QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246: +-farbound*(1+ramp(i)), ramp offset as of the call).  There are no user bounds on
+// x; the targets are functions of (index, farbound, offset) and are evaluated where needed instead of being stored.
+WBC_DEV double far_rv(const QPCtx& c,int idx){ const int nRamp=42+70; const double t=(double)((idx+c.farRampOffset)%nRamp)/(double)(nRamp-1);
+    return c.farbound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1); }
+WBC_DEV double tgt_lb(const QPCtx& c,int i){ return -far_rv(c,i); }
+WBC_DEV double tgt_ub(const QPCtx& c,int i){ return far_rv(c,i); }
+WBC_DEV double tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),w.qp.lbA[i]); }
+WBC_DEV double tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),w.qp.ubA[i]); }
+// QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are w.qp.gf (g_new) and the far-bounded data
+WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; w.dg[i]=gn-w.g[i]; w.dlb[i]=w.lbF[i]-w.lb[i]; w.dub[i]=w.ubF[i]-w.ub[i]; }
-    LANE_FOR(i,70){ w.dlbA[i]=w.lbAF[i]-w.lbA[i]; w.dubA[i]=w.ubAF[i]-w.ubA[i]; }
+    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; w.dg[i]=gn-w.g[i]; const double rv=far_rv(c,i); w.dlb[i]=-rv-w.lb[i]; w.dub[i]=rv-w.ub[i]; }
+    LANE_FOR(i,70){ const double rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,w.qp.lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,w.qp.ubA[i])-w.ubA[i]; }
     WBC_SYNC();
     bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(w.dlb[ii])>QEPS||fabs(w.dub[ii])>QEPS) nz=true; }
     bBzero=(wbc_ballot(nz)==0u);
@@ -412,15 +479,15 @@ WBC_DEV void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBze
     bCzero=(wbc_ballot(nz)==0u);
 }
 // QProblem::getRelativeHomotopyLength (QProblem.cpp:5372-5410, QProblemB.cpp:2113-2157)
-WBC_DEV double relativeHomotopyLength(const QPWork& w,const QPCtx& c){
+WBC_FN double relativeHomotopyLength(const QPWork& w,const QPCtx& c){
     const int lane=c.lane; double len=0.0;
     LANE_FOR(i,42){ double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; double s=fmax(fabs(gn),1.0); len=fmax(len,fabs(gn-w.g[i])/s);
-                    s=fmax(fabs(w.lbF[i]),1.0); len=fmax(len,fabs(w.lbF[i]-w.lb[i])/s); s=fmax(fabs(w.ubF[i]),1.0); len=fmax(len,fabs(w.ubF[i]-w.ub[i])/s); }
-    LANE_FOR(i,70){ double s=fmax(fabs(w.lbAF[i]),1.0); len=fmax(len,fabs(w.lbAF[i]-w.lbA[i])/s); s=fmax(fabs(w.ubAF[i]),1.0); len=fmax(len,fabs(w.ubAF[i]-w.ubA[i])/s); }
+                    const double rv=far_rv(c,i); s=fmax(rv,1.0); len=fmax(len,fabs(-rv-w.lb[i])/s); len=fmax(len,fabs(rv-w.ub[i])/s); }
+    LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); double s=fmax(fabs(l),1.0); len=fmax(len,fabs(l-w.lbA[i])/s); s=fmax(fabs(u),1.0); len=fmax(len,fabs(u-w.ubA[i])/s); }
     return wbc_max(len);
 }
 // QProblem::setupAuxiliaryQPgradient (QProblem.cpp:2602-2641): g = y_B - H x + A' y_C
-WBC_DEV void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
+WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
     LANE_FOR(i,42){ double t=w.y[i]; t-=Hrow_dot(w,i,w.x,2);
         w.g[i]=t+Acol_times(w.qp,i,w.y+42); }
@@ -528,7 +595,7 @@ WBC_DEV void computeGivens(double xold,double yold,double& xnew,double& ynew,dou
 // The column-wise Givens chains of addConstraint / addBound: rotation j is defined by (wv[j+1], wv[j]) where wv[j] is the
 // result of rotation j-1 -- a scalar recurrence every lane evaluates redundantly -- and then applied to the column
 // pair (j+1, j) of Q.  The rows of Q are independent, so each lane sweeps its own rows through the whole chain.
-WBC_DEV void givens_chain(QPWork& w,const QPCtx& c,int nrot){
+WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
     // The recurrence t_j = hypot(w[j+1], t_{j-1}) of the reference's loop is t_j = sgn(w[j+1]) |w[0..j+1]|_2, so every
     // rotation follows from prefix sums of squares: one lane per rotation, no serial sqrt/divide chain.
     const int lane=c.lane; WBC_SYNC();
@@ -546,7 +613,7 @@ WBC_DEV void givens_chain(QPWork& w,const QPCtx& c,int nrot){
     if(nrot>0){ const int owner=(nrot-1)%WBC_NL; tlast=wbc_bcast(tlast,owner); if(lane==0) w.wv[nrot]=tlast; }
     WBC_SYNC();
 }
-WBC_DEV void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
+WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
     const int lane=c.lane;
     LANE_FOR(i,nrows){ int ii=(int)w.FR[i]; double qa=QQ(ii,0);
         for(int j=0;j<nrot;j++){ double qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
@@ -564,7 +631,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     if(fullTest){
         LANE_FOR(j,42) w.tmpv[j]=Ael(w.qp,number,j);
         WBC_SYNC();
-        int rv=determineStepDirection(w,c,w.tmpv,w.zero,w.zero,w.zero,w.zero,false,false);
+        int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
         if(rv!=QP_OK) return false;
         double weight=0.0, zero=0.0;
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
@@ -587,7 +654,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     if(fullTest){
         LANE_FOR(j,42) w.tmpv[j]=(j==number)?1.0:0.0;
         WBC_SYNC();
-        int rv=determineStepDirection(w,c,w.tmpv,w.zero,w.zero,w.zero,w.zero,false,false);
+        int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
         if(rv!=QP_OK) return false;
         double weight=0.0, zero=0.0;
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
@@ -709,17 +776,19 @@ WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
     WBC_SYNC();
     const int number_idx=(int)w.posAC[number];
     if(number_idx<nAC-1){
-        // shift rows up; lane per column so that the upward copy is ordered inside one lane
-        LANE_FOR(j,nAC){ for(int i=number_idx+1;i<nAC;i++) if(j>=nAC-i-1) TT(i-1,tcol+j)=TT(i,tcol+j); TT(nAC-1,tcol+j)=0.0; }
+        // shift rows up; lane per reverse-column m so that the upward copy is ordered inside one lane.  Row i has i+1 entries
+        // (m = 0..i); moved to row i-1 it keeps m = 0..i-1 in place and its leading entry m = i -- the one the Givens sweep
+        // below annihilates -- in w.wv[i-1] (packed storage has no room for it).
+        LANE_FOR(m,nAC){ for(int i=number_idx+1;i<nAC;i++){ if(m<i) TT(i-1,SIZET-1-m)=TT(i,SIZET-1-m); else if(m==i) w.wv[i-1]=TT(i,SIZET-1-m); } }
         for(int j=nAC-2-number_idx;j>=0;j--){
             WBC_SYNC();
-            const int pr=nAC-2-j; double xn,yn,cc,ss; computeGivens(TT(pr,tcol+1+j),TT(pr,tcol+j),xn,yn,cc,ss);
+            const int pr=nAC-2-j; double xn,yn,cc,ss; computeGivens(TT(pr,tcol+1+j),w.wv[pr],xn,yn,cc,ss);
             WBC_SYNC();
-            if(lane==0){ TT(pr,tcol+1+j)=xn; TT(pr,tcol+j)=yn; }
+            if(lane==0){ TT(pr,tcol+1+j)=xn; w.wv[pr]=yn; }
             for(int i=nAC-j-1+lane;i<nAC-1;i+=WBC_NL){ double xo=TT(i,tcol+1+j), yo=TT(i,tcol+j); TT(i,tcol+1+j)=cc*xo+ss*yo; TT(i,tcol+j)=-ss*xo+cc*yo; }
             LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
         }
-    } else { LANE_FOR(j,nAC) TT(nAC-1,tcol+j)=0.0; }
+    }
     moveActiveToInactive(w,c,number);
     return QP_OK;
 }
@@ -761,14 +830,8 @@ WBC_FN int changeActiveSet(QPWork& w,QPCtx& c,int BC_idx,int BC_status,bool BC_i
     }
     return rv;
 }
-// QProblem::updateFarBounds (QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246); user bounds: none on x, w.qp.lbA/ubA on Ax
-WBC_DEV void updateFarBounds(QPWork& w,const QPCtx& c,double curFarBound){
-    const int lane=c.lane, nRamp=42+70; WBC_SYNC();
-    LANE_FOR(i,42){ double t=(double)((i+c.rampOffset)%nRamp)/(double)(nRamp-1); double rv=curFarBound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1); w.lbF[i]=-rv; w.ubF[i]=rv; }
-    LANE_FOR(i,70){ double t=(double)((42+i+c.rampOffset)%nRamp)/(double)(nRamp-1); double rv=curFarBound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1);
-        w.lbAF[i]=fmax(-rv,w.qp.lbA[i]); w.ubAF[i]=fmin(rv,w.qp.ubA[i]); }
-    WBC_SYNC();
-}
+// QProblem::updateFarBounds (QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246): see far_rv
+WBC_DEV void updateFarBounds(QPWork&,QPCtx& c,double curFarBound){ c.farbound=curFarBound; c.farRampOffset=c.rampOffset; }
 // QProblem::solveQP (QProblem.cpp:1477-1747); nWSR in/out like the reference
 WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
@@ -819,8 +882,8 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
             updateFarBounds(w,c,farbound);
         } else if(c.status==QPS_SOLVED){
             const double tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
-            LANE_FOR(i,42){ if(fabs(w.lbF[i]-w.x[i])<tol) na++; if(fabs(w.ubF[i]-w.x[i])<tol) na++; }
-            LANE_FOR(i,70){ if(w.lbAF[i]>w.qp.lbA[i]&&fabs(w.lbAF[i]-w.Ax[i])<tol) na++; if(w.ubAF[i]<w.qp.ubA[i]&&fabs(w.ubAF[i]-w.Ax[i])<tol) na++; }
+            LANE_FOR(i,42){ if(fabs(tgt_lb(c,i)-w.x[i])<tol) na++; if(fabs(tgt_ub(c,i)-w.x[i])<tol) na++; }
+            LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>w.qp.lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<w.qp.ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
             if(wbc_ballot(na>0)==0u) break;
             c.status=QPS_HOMOTOPYQPSOLVED;
             if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
@@ -834,9 +897,9 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
 // fixed at its (far) lower bound (initialStatusBounds = ST_LOWER) and no active constraint.
 WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ w.x[i]=0.0; w.y[i]=0.0; w.g[i]=0.0; w.lb[i]=0.0; w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; w.zero[i]=0.0; }
+    LANE_FOR(i,42){ w.x[i]=0.0; w.y[i]=0.0; w.g[i]=0.0; w.lb[i]=0.0; w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
     LANE_FOR(i,70){ w.y[42+i]=0.0; w.Ax[i]=0.0; w.lbA[i]=-OPT_boundRelaxation; w.ubA[i]=OPT_boundRelaxation; w.Ax_l[i]=OPT_boundRelaxation; w.Ax_u[i]=OPT_boundRelaxation;
-                    w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; w.zero[i]=0.0; }
+                    w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
     c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=0.0;
     setupTQfactorisation(w,c);
     c.status=QPS_AUXILIARYQPSOLVED;
@@ -856,7 +919,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
     c.flops+=4.0*42*42+4.0*70*42;
-    LANE_FOR(i,70){ w.zero[i]=0.0; double ax=Arow_times(w.qp,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    LANE_FOR(i,70){ double ax=Arow_times(w.qp,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;
