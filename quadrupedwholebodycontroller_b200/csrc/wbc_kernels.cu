@@ -4,6 +4,7 @@
 // that need 100 working-set changes do not hold up robots that need none.
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -206,6 +207,7 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,32,h->qpSmem)!=cudaSuccess||nb<1){
         h->err=std::string("occupancy query: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     h->qpBlocksPerSM=nb;
+    if(const char* e=getenv("WBC_QP_CTAS_PER_SM")){ int v=atoi(e); if(v>=1&&v<nb) h->qpBlocksPerSM=v; }     // tuning knob: fewer resident solver warps per SM
     for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
     *out=h;
     int rcode=wbc_reset(h,0,n);

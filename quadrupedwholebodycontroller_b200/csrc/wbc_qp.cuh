@@ -172,6 +172,26 @@ WBC_FN double Hrow_dot(const QPWork& w,int i,const double* v,int sel,unsigned fm
 WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
 WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const double* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:0.0; WBC_SYNC(); }
 
+// ---------------------------------------------------------------- products with Q = [Z Y] (one copy each: instruction cache)
+// out[i] = sgn * sum_j Q(FR[j], col0+i) t[FR[j]],  i < ncols   (t by variable number; lane per column; FR-list order like the reference)
+WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const double* t,double sgn,double* out){
+    const int lane=c.lane, nFR=c.nFR;
+    LANE_FOR(i,ncols){ const double* q=&w.Q[LD*(col0+i)]; double s=0.0;
+        #pragma unroll 4
+        for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s+=q[jj]*t[jj]; }
+        out[i]=sgn*s; }
+    WBC_SYNC();
+}
+// v = sum_j Q(FR[i], col0+j) x[j] for every free variable FR[i]:  acc[FR[i]] += v,  and keep[FR[i]] = v if keep != null   (lane per row)
+WBC_FN void Q_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const double* x,double* acc,double* keep){
+    const int lane=c.lane;
+    LANE_FOR(i,c.nFR){ const int ii=(int)w.FR[i]; const double* q=&w.Q[ii+LD*col0]; double s=0.0;
+        #pragma unroll 4
+        for(int j=0;j<ncols;j++) s+=q[LD*j]*x[j];
+        if(keep) keep[ii]=s; acc[ii]+=s; }
+    WBC_SYNC();
+}
+
 // ---------------------------------------------------------------- index lists (Indexlist.cpp: insertion-ordered number[])
 // removal keeps the order of the remaining entries; every lane holds the same counters, one lane edits the list
 WBC_DEV void list_remove(signed char* L,int& n,int number,int lane){
@@ -287,30 +307,28 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
     }
 #else
     for(int i=0;i<n;i++){
-        const int j0=i+lane, j1=j0+32;
-        double s0=(j0<n)?RR(i,j0):0.0, s1=(j1<n)?RR(i,j1):0.0;
-        if(j1<n){
-            #pragma unroll 2
-            for(int k=i-1;k>=0;k--){ const double rki=RR(k,i); s0-=rki*RR(k,j0); s1-=rki*RR(k,j1); }
-        } else if(j0<n){
-            #pragma unroll 4
-            for(int k=i-1;k>=0;k--) s0-=RR(k,i)*RR(k,j0);
-        }
+        const int j0=i+lane, j1=j0+32; const bool in0=j0<n, in1=j1<n;
+        // packed column j lives at RT[TRI42-1-tri(j) - k]: walk k = i-1 .. 0 with three pointers
+        const double* pi=&RR(i,i); const double* p0=&RR(i,in0?j0:i); const double* p1=&RR(i,in1?j1:i);
+        double s0=in0?*p0:0.0, s1=in1?*p1:0.0;
+        #pragma unroll 2
+        for(int k=1;k<=i;k++){ const double rki=pi[k]; s0-=rki*p0[k]; s1-=rki*p1[k]; }     // RR(i-k,.) = p[k]
         const double sum=wbc_bcast(s0,0);
         if(!(sum>0.0)) return false;
         const double d=sqrt(sum), rd=1.0/d;
         if(lane==0){ RR(i,i)=d; w.rdR[i]=rd; }
-        else if(j0<n) RR(i,j0)=s0*rd;
-        if(j1<n) RR(i,j1)=s1*rd;
+        else if(in0) RR(i,j0)=s0*rd;
+        if(in1) RR(i,j1)=s1*rd;
         WBC_SYNC();
     }
 #endif
     return true;
 }
-// R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk) for the upper triangle, register-tiled: each lane accumulates one TS x TS
-// tile (the upper tiles of an nt x nt tile grid, nt(nt+1)/2 <= 32) over the free variables in list order -- same products
-// and same summation order as the scalar loops of SymDenseMat::bilinear (Matrices.cpp:630-667).
-template<int TS> WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
+// R(kk,jj) = sum_ii Z(FR[ii],jj) (HZ)(FR[ii],kk) for the upper triangle, register-tiled: each lane accumulates 4 x 4 tiles (the
+// upper tiles of the tile grid, <= 66 of them -> <= 3 per lane) over the free variables in list order -- same products and same
+// summation order as the scalar loops of SymDenseMat::bilinear (Matrices.cpp:630-667).
+WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
+    constexpr int TS=4;
     const int lane=c.lane, nt=(nZ+TS-1)/TS, ntiles=nt*(nt+1)/2;
     LANE_FOR(t,ntiles){
         int ti=0, rem=t; while(rem>=nt-ti){ rem-=nt-ti; ti++; } const int tj=ti+rem;
@@ -319,6 +337,7 @@ template<int TS> WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ)
         for(int a=0;a<TS;a++){
             #pragma unroll
             for(int b=0;b<TS;b++) acc[a][b]=0.0; }
+        #pragma unroll 1
         for(int ii=0;ii<nFR;ii++){
             const int v=(int)w.FR[ii]; double zj[TS],wk[TS];
             #pragma unroll
@@ -340,23 +359,24 @@ template<int TS> WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ)
             for(int b=0;b<TS;b++){ const int kk=TS*ti+a, jj=TS*tj+b; if(kk<=jj&&jj<nZ) RR(kk,jj)=acc[a][b]; } }
     }
 }
+// the two cases without an active constraint (first iterations of a cold start): R'R = H_FR,FR directly
+WBC_FN void fill_R_with_H(QPWork& w,const QPCtx& c){
+    const int lane=c.lane, nFR=c.nFR;
+    LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+}
 // QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
 WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
     { const double f=nFR,z=nZ; c.flops+=2*f*f*z+2*f*z*z+z*z*z/3.0; }
     WBC_SYNC();
-    if(c.nFX+c.nAC==0){
-        LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
-        if(!potrf_R(w,c,nFR)) return QP_RET_HESSIAN_NOT_SPD;
-        return QP_OK;
-    }
-    if(nZ==0) return QP_OK;
+    if(nZ==0&&c.nFX+c.nAC!=0) return QP_OK;
     if(c.nAC==0){
-        // make Z trivial
-        LANE_FOR(i,42) for(int j=0;j<nZ;j++) QQ(i,j)=0.0;
-        WBC_SYNC();
-        LANE_FOR(j,nZ) QQ((int)w.FR[j],j)=1.0;
-        LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+        if(c.nFX!=0){ // make Z trivial
+            LANE_FOR(i,42) for(int j=0;j<nZ;j++) QQ(i,j)=0.0;
+            WBC_SYNC();
+            LANE_FOR(j,nZ) QQ((int)w.FR[j],j)=1.0;
+        }
+        fill_R_with_H(w,c);
     } else {
         // Z'HZ (SymDenseMat::bilinear, Matrices.cpp:630-667).  H = diag except the 12x12 force block, so
         // (HZ)(v,k) = H_vv Z(v,k) for v outside the block; inside, the sum runs over the free force variables in list order
@@ -369,7 +389,7 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
             for(int i=0;i<nff;i++){ const int u=(int)w.rdT[i]; s+=w.qp.Hff[12*u+a]*QQ(18+u,k); }
             w.HZf[a*LD+k]=s; }
         WBC_SYNC();
-        if(nZ<=14) zhz_tiles<2>(w,c,nFR,nZ); else if(nZ<=28) zhz_tiles<4>(w,c,nFR,nZ); else zhz_tiles<6>(w,c,nFR,nZ);
+        zhz_tiles(w,c,nFR,nZ);
     }
     if(!potrf_R(w,c,nZ)) return QP_RET_HESSIAN_NOT_SPD;
     return QP_OK;
@@ -399,8 +419,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
                 else {
                     if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]-=Arow_times(w.qp,(int)w.AC[i],w.vm); WBC_SYNC(); }
                     backsolveT(w,c,w.tB,false,w.xFRy);
-                    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=w.xTMP[ii]; for(int j=0;j<nAC;j++) s+=QQ(ii,nZ+j)*w.xFRy[j]; w.xTMP[ii]=s; }
-                    WBC_SYNC();
+                    Q_times(w,c,nZ,nAC,w.xFRy,w.xTMP,nullptr);
                 }
             }
             LANE_FOR(i,nZ) w.xFRz[i]=0.0;
@@ -409,17 +428,16 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
             if(nAC>0&&(!bCzero||!bBzero)){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.xTMP,0,ffm); } }
             WBC_SYNC();
             if(nZ>0){
-                LANE_FOR(i,nZ){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s-=QQ(jj,i)*w.tA[jj]; } w.xFRz[i]=s; }
+                Qt_times(w,c,0,nZ,w.tA,-1.0,w.xFRz);
                 backsolveR(w,c,w.xFRz,true,w.xFRz,nZ);
                 backsolveR(w,c,w.xFRz,false,w.xFRz,nZ);
-                LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double s=0; for(int j=0;j<nZ;j++) s+=QQ(ii,j)*w.xFRz[j]; w.Zdz[ii]=s; w.xTMP[ii]+=s; }
-                WBC_SYNC();
+                Q_times(w,c,0,nZ,w.xFRz,w.xTMP,w.Zdz);
             }
         }
         // III) delta_yAC
         if(nAC>0){
             if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.Zdz,0,ffm); } WBC_SYNC(); }
-            LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*w.tA[jj]; } w.tB[i]=s; }
+            Qt_times(w,c,nZ,nAC,w.tA,1.0,w.tB);
             backsolveT(w,c,w.tB,true,w.yTMP);
         }
         WBC_SYNC();
@@ -653,7 +671,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
           // this QP family: independent rows have max|Z'a| >= 1e-2 |a|, dependent ones exactly 0).  Only the band in between
           // runs the reference's test.
             double l2=0.0; for(int i=0;i<nFR;i++){ const double a=w.tmpv[(int)w.FR[i]]; l2+=a*a; }
-            double mx=0.0; LANE_FOR(j,nZ){ double sum=0.0; for(int i=0;i<nFR;i++){ const int ii=(int)w.FR[i]; sum+=w.tmpv[ii]*QQ(ii,j); } mx=fmax(mx,fabs(sum)); }
+            Qt_times(w,c,0,nZ,w.tmpv,1.0,w.xFRz); double mx=0.0; LANE_FOR(j,nZ) mx=fmax(mx,fabs(w.xFRz[j]));
             mx=wbc_max(mx);
             const double nrm=sqrt(l2);
             const bool sureLI=mx>LI_SURE*nrm, sureLD=mx<=LI_NONE*nrm;
@@ -677,7 +695,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     WBC_SYNC();
     double l2=0.0; for(int i=0;i<nFR;i++){ double a=w.arow[(int)w.FR[i]]; l2+=a*a; }
     bool li=false;
-    LANE_FOR(j,nZ){ double sum=0.0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=w.arow[ii]*QQ(ii,j); } if(fabs(sum)>OPT_epsLITests*l2) li=true; }
+    Qt_times(w,c,0,nZ,w.arow,1.0,w.xFRz); LANE_FOR(j,nZ) if(fabs(w.xFRz[j])>OPT_epsLITests*l2) li=true;
     return wbc_ballot(li)!=0u;
 }
 // QProblem::addBound_checkLI (QProblem.cpp:3487-3590)
@@ -743,7 +761,7 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
     if(nAC>0){
         LANE_FOR(j,42) w.arow[j]=sg*Ael_dev(w.qp,number,j);
         WBC_SYNC();
-        LANE_FOR(i,nAC){ double s=0; for(int j=0;j<nFR;j++){ int jj=(int)w.FR[j]; s+=QQ(jj,nZ+i)*w.arow[jj]; } w.tB[i]=s; }
+        Qt_times(w,c,nZ,nAC,w.arow,1.0,w.tB);
         if(!prepare_T(w,c)) return QP_RET_UNSUPPORTED_PATH;
         backsolveT(w,c,w.tB,true,w.xFRy);
     }
@@ -779,8 +797,9 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
     // row [wZ wY] = aFR' [Z Y]
     LANE_FOR(j,42) w.arow[j]=Ael_dev(w.qp,number,j);
     WBC_SYNC();
-    LANE_FOR(j,nFR){ double s=0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; s+=w.arow[ii]*QQ(ii,j); }
-        if(j<nZ) w.wv[j]=s; else TT(nAC,tcol+(j-nZ))=s; }
+    Qt_times(w,c,0,nFR,w.arow,1.0,w.wv);
+    LANE_FOR(j,nAC) TT(nAC,tcol+j)=w.wv[nZ+j];
+    WBC_SYNC();
     if(nZ>0){
         givens_chain(w,c,nZ-1);
         apply_chain_Q(w,c,nZ-1,nFR);
