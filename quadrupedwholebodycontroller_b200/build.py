@@ -4,7 +4,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB_PATH = os.path.join(HERE, "libwbc_b200.so")
+LIB_PATH = os.environ.get("WBC_B200_LIB") or os.path.join(HERE, "libwbc_b200.so")     # override = DEV experiments with another build of the same CUDA library
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
 
 
@@ -14,6 +14,14 @@ def _stale():
     t = os.path.getmtime(LIB_PATH)
     srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "wbc_b200.h")]
     return any(os.path.getmtime(s) > t for s in srcs)
+
+
+def build_variant(out_path, defines=(), verbose=False):
+    """DEV: build the same library with extra -D switches to another path (tools/gpu_* experiments)."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "wbc_kernels.cu"), "-o", out_path]
+    subprocess.check_call(cmd)
+    return out_path
 
 
 def build_library(force=False, verbose=False):

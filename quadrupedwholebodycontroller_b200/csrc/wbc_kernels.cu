@@ -60,7 +60,11 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
         if(r>=N) break;
         const bool isFirst=first[r]!=0;
+#if defined(WBC_QPDATA_GLOBAL)
+        if(lane==0) w.qpg=&qpd[r];
+#else
         { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
+#endif
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
         for(int k=0;k<8;k++) c.prof[k]=0;
         c.flops=0.0;

@@ -49,6 +49,11 @@ constexpr double LI_SURE=1.0e-6, LI_NONE=1.0e-12;
 
 constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
 constexpr int SIZET=42;               // sizeT = min(nV,nC)
+#if defined(WBC_QPDATA_GLOBAL)
+  #define WQP (*w.qpg)
+#else
+  #define WQP (w.qp)
+#endif
 #define QQ(i,j) w.Q[(i)+LD*(j)]       // Types.hpp:141-147: Q column-major
 // R (nZ x nZ upper triangular) and T (nAC x nAC reverse triangular) are the only parts of the reference's 42x42 R and T
 // arrays that are ever read, and nZ + nAC = nFR <= 42, so both live PACKED in one 903-entry buffer: T's row i (its i+1
@@ -76,7 +81,11 @@ struct QPState {
 struct QPWork {
     double Q[42*LD];
     double RT[TRI42+1];                         // packed R and T (see RR / TT)
+#if defined(WBC_QPDATA_GLOBAL)
+    const QPData* qpg;                          // compact H, A, new g / lbA / ubA stay in global memory (L1/L2): read-only during the solve
+#else
     QPData qp;                                  // compact H, A, new g / lbA / ubA
+#endif
     double x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
     double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
     double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
@@ -161,12 +170,12 @@ WBC_DEV unsigned force_mask(const QPWork& w,const QPCtx& c,int sel){
 #endif
 }
 WBC_FN double Hrow_dot(const QPWork& w,int i,const double* v,int sel,unsigned fm){
-    if(i>=18&&i<30){ const double* h=&w.qp.Hff[i-18]; double s=0.0;
+    if(i>=18&&i<30){ const double* h=&WQP.Hff[i-18]; double s=0.0;
         #pragma unroll
         for(int u=0;u<12;u++) if((fm>>u)&1u) s+=h[12*u]*v[18+u];
         return s; }
     if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return 0.0;
-    return ((i>=30)?w.qp.rho:1.0)*v[i];
+    return ((i>=30)?WQP.rho:1.0)*v[i];
 }
 // masked copies: vm = v restricted to free (sel 0) / fixed (sel 1) variables; ym = yAC scattered to constraint numbers
 WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
@@ -345,7 +354,7 @@ WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
             if(v>=18&&v<30){
                 #pragma unroll
                 for(int a=0;a<TS;a++) wk[a]=w.HZf[(v-18)*LD+TS*ti+a];
-            } else { const double dv=(v>=30)?w.qp.rho:1.0;
+            } else { const double dv=(v>=30)?WQP.rho:1.0;
                 #pragma unroll
                 for(int a=0;a<TS;a++) wk[a]=dv*QQ(v,TS*ti+a); }
             #pragma unroll
@@ -362,7 +371,7 @@ WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
 // the two cases without an active constraint (first iterations of a cold start): R'R = H_FR,FR directly
 WBC_FN void fill_R_with_H(QPWork& w,const QPCtx& c){
     const int lane=c.lane, nFR=c.nFR;
-    LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(w.qp,(int)w.FR[i],(int)w.FR[j]);
+    LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(WQP,(int)w.FR[i],(int)w.FR[j]);
 }
 // QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
 WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
@@ -386,7 +395,7 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
             const unsigned m=wbc_ballot(isf); if(isf) w.rdT[nff+wbc_rank(m,lane)]=(double)(v-18); nff+=wbc_popc(m); }
         WBC_SYNC();
         LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; double s=0;
-            for(int i=0;i<nff;i++){ const int u=(int)w.rdT[i]; s+=w.qp.Hff[12*u+a]*QQ(18+u,k); }
+            for(int i=0;i<nff;i++){ const int u=(int)w.rdT[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
             w.HZf[a*LD+k]=s; }
         WBC_SYNC();
         zhz_tiles(w,c,nFR,nZ);
@@ -417,7 +426,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
             if(nAC>0){
                 if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=0.0; WBC_SYNC(); }
                 else {
-                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]-=Arow_times(w.qp,(int)w.AC[i],w.vm); WBC_SYNC(); }
+                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]-=Arow_times(WQP,(int)w.AC[i],w.vm); WBC_SYNC(); }
                     backsolveT(w,c,w.tB,false,w.xFRy);
                     Q_times(w,c,nZ,nAC,w.xFRy,w.xTMP,nullptr);
                 }
@@ -449,9 +458,9 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         // residuals for the next refinement pass
         double rnrm=0.0;
         scatter_yAC(w,c,w.dyAC);
-        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); t-=Acol_times(w.qp,ii,w.ym); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); t-=Acol_times(WQP,ii,w.ym); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= (bCzero||!dlbA)?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
-            t-=Arow_times(w.qp,ii,w.dx); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
+            t-=Arow_times(WQP,ii,w.dx); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
         rnrm=wbc_max(rnrm);
         WBC_SYNC();
         if(rnrm<OPT_epsIterRef) break;
@@ -459,7 +468,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
     { const double a=nAC,f=nFR,z=nZ; c.flops+=(1.0+nref)*(2*a*a+4*f*a+4*f*z+4*f*f+4*z*z)+nref*(2*f*f+4*a*42.0); }
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=Acol_times(w.qp,ii,w.ym); t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); w.dyFX[ii]=t; }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=Acol_times(WQP,ii,w.ym); t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); w.dyFX[ii]=t; }
     WBC_SYNC();
     return QP_OK;
 }
@@ -499,13 +508,13 @@ WBC_DEV double far_rv(const QPCtx& c,int idx){ const int nRamp=42+70; const doub
     return c.farbound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1); }
 WBC_DEV double tgt_lb(const QPCtx& c,int i){ return -far_rv(c,i); }
 WBC_DEV double tgt_ub(const QPCtx& c,int i){ return far_rv(c,i); }
-WBC_DEV double tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),w.qp.lbA[i]); }
-WBC_DEV double tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),w.qp.ubA[i]); }
-// QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are w.qp.gf (g_new) and the far-bounded data
+WBC_DEV double tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),WQP.lbA[i]); }
+WBC_DEV double tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),WQP.ubA[i]); }
+// QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are WQP.gf (g_new) and the far-bounded data
 WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; w.dg[i]=gn-w.g[i]; const double rv=far_rv(c,i); w.dlb[i]=-rv-w.lb[i]; w.dub[i]=rv-w.ub[i]; }
-    LANE_FOR(i,70){ const double rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,w.qp.lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,w.qp.ubA[i])-w.ubA[i]; }
+    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?WQP.gf[i-18]:0.0; w.dg[i]=gn-w.g[i]; const double rv=far_rv(c,i); w.dlb[i]=-rv-w.lb[i]; w.dub[i]=rv-w.ub[i]; }
+    LANE_FOR(i,70){ const double rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,WQP.lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,WQP.ubA[i])-w.ubA[i]; }
     WBC_SYNC();
     bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(w.dlb[ii])>QEPS||fabs(w.dub[ii])>QEPS) nz=true; }
     bBzero=(wbc_ballot(nz)==0u);
@@ -516,7 +525,7 @@ WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzer
 // tolerance: max_i |d_i|/s_i <= tol  <=>  no |d_i| > tol*s_i -- evaluated in that form (no fp64 divisions), s_i = max(|target_i|,1).
 WBC_FN bool homotopyFinished(const QPWork& w,const QPCtx& c){
     const int lane=c.lane; const double tol=OPT_terminationTolerance; bool over=false;
-    LANE_FOR(i,42){ const double gn=(i>=18&&i<30)?w.qp.gf[i-18]:0.0; if(fabs(gn-w.g[i])>tol*fmax(fabs(gn),1.0)) over=true;
+    LANE_FOR(i,42){ const double gn=(i>=18&&i<30)?WQP.gf[i-18]:0.0; if(fabs(gn-w.g[i])>tol*fmax(fabs(gn),1.0)) over=true;
                     const double rv=far_rv(c,i), s=tol*fmax(rv,1.0); if(fabs(-rv-w.lb[i])>s||fabs(rv-w.ub[i])>s) over=true; }
     LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(fabs(l-w.lbA[i])>tol*fmax(fabs(l),1.0)||fabs(u-w.ubA[i])>tol*fmax(fabs(u),1.0)) over=true; }
     return wbc_ballot(over)==0u;
@@ -525,7 +534,7 @@ WBC_FN bool homotopyFinished(const QPWork& w,const QPCtx& c){
 WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
     LANE_FOR(i,42){ double t=w.y[i]; t-=Hrow_dot(w,i,w.x,2,0xfffu);
-        w.g[i]=t+Acol_times(w.qp,i,w.y+42); }
+        w.g[i]=t+Acol_times(WQP,i,w.y+42); }
     WBC_SYNC();
 }
 // QProblem::performStep (QProblem.cpp:4981-5278)
@@ -545,7 +554,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
     WBC_SYNC();
     // II.1 inactive constraints
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_times(w.qp,ii,w.dx); }
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_times(WQP,ii,w.dx); }
     WBC_SYNC();
     LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],0.0); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
@@ -573,7 +582,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
         LANE_FOR(i,42){ w.g[i]+=tau*w.dg[i]; w.lb[i]+=tau*w.dlb[i]; w.ub[i]+=tau*w.dub[i]; }
         LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
         WBC_SYNC();
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_times(w.qp,ii,w.x); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_times(WQP,ii,w.x); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
         LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; double da=w.dAx[ii];
             w.Ax[ii]+=tau*da; w.Ax_l[ii]+=tau*(da-w.dlbA[ii]); w.Ax_u[ii]+=tau*(w.dubA[ii]-da); }
         WBC_SYNC();
@@ -664,7 +673,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_SYNC();
     if(fullTest){
-        LANE_FOR(j,42) w.tmpv[j]=Ael_dev(w.qp,number,j);
+        LANE_FOR(j,42) w.tmpv[j]=Ael_dev(WQP,number,j);
         WBC_SYNC();
         { // The full test costs a whole step-direction solve and only its verdict is used.  |Z'a| decides it beforehand in all but
           // borderline cases: the full test's "zero" is |Z (Z'HZ)^-1 Z'a|, which vanishes with Z'a (measured on 6655 tests of
@@ -691,7 +700,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
 #endif
         return zero>OPT_epsLITests*weight;
     }
-    LANE_FOR(j,42) w.arow[j]=Ael_dev(w.qp,number,j);
+    LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
     WBC_SYNC();
     double l2=0.0; for(int i=0;i<nFR;i++){ double a=w.arow[(int)w.FR[i]]; l2+=a*a; }
     bool li=false;
@@ -759,7 +768,7 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
     const int nFR=c.nFR, nAC=c.nAC, nFX=c.nFX, nZ=nFR-nAC; const double sg=(C_status==ST_LOWER)?1.0:-1.0;
     WBC_SYNC();
     if(nAC>0){
-        LANE_FOR(j,42) w.arow[j]=sg*Ael_dev(w.qp,number,j);
+        LANE_FOR(j,42) w.arow[j]=sg*Ael_dev(WQP,number,j);
         WBC_SYNC();
         Qt_times(w,c,nZ,nAC,w.arow,1.0,w.tB);
         if(!prepare_T(w,c)) return QP_RET_UNSUPPORTED_PATH;
@@ -767,7 +776,7 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=sg*Ael_dev(w.qp,number,ii)-Acol_times(w.qp,ii,w.ym); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=sg*Ael_dev(WQP,number,ii)-Acol_times(WQP,ii,w.ym); }
     return ensureLI_exchange(w,c,number,C_status,false);
 }
 // QProblem::addBound_ensureLI (QProblem.cpp:3596-3780)
@@ -783,7 +792,7 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=0.0-Acol_times(w.qp,ii,w.ym); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=0.0-Acol_times(WQP,ii,w.ym); }
     return ensureLI_exchange(w,c,number,B_status,true);
 }
 
@@ -795,7 +804,7 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
     { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
     WBC_SYNC();
     // row [wZ wY] = aFR' [Z Y]
-    LANE_FOR(j,42) w.arow[j]=Ael_dev(w.qp,number,j);
+    LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
     WBC_SYNC();
     Qt_times(w,c,0,nFR,w.arow,1.0,w.wv);
     LANE_FOR(j,nAC) TT(nAC,tcol+j)=w.wv[nZ+j];
@@ -862,7 +871,7 @@ WBC_FN int removeBound(QPWork& w,QPCtx& c,int number){
     WBC_SYNC();
     if(lane==0) QQ(number,nFR)=1.0;
     if(nAC>0){
-        LANE_FOR(i,nAC) w.tmpv[i]=Ael_dev(w.qp,(int)w.AC[i],number);
+        LANE_FOR(i,nAC) w.tmpv[i]=Ael_dev(WQP,(int)w.AC[i],number);
         for(int j=nAC-1;j>=0;j--){
             WBC_SYNC();
             const int pr=nAC-1-j; double xn,yn,cc,ss; computeGivens(w.tmpv[pr],TT(pr,tcol+j),xn,yn,cc,ss);
@@ -930,7 +939,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
 WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane; const int nWSR_max=nWSR; int nWSR_performed=0;
     double farbound=OPT_initialFarBounds;
-    { double m=0.0; LANE_FOR(i,70){ double u=w.qp.ubA[i], l=w.qp.lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
+    { double m=0.0; LANE_FOR(i,70){ double u=WQP.ubA[i], l=WQP.lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
     updateFarBounds(w,c,farbound);
     int rv;
     for(;;){
@@ -944,7 +953,7 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
         } else if(c.status==QPS_SOLVED){
             const double tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
             LANE_FOR(i,42){ if(fabs(tgt_lb(c,i)-w.x[i])<tol) na++; if(fabs(tgt_ub(c,i)-w.x[i])<tol) na++; }
-            LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>w.qp.lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<w.qp.ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
+            LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>WQP.lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<WQP.ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
             if(wbc_ballot(na>0)==0u) break;
             c.status=QPS_HOMOTOPYQPSOLVED;
             if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
@@ -980,7 +989,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
     c.flops+=4.0*42*42+4.0*70*42;
-    LANE_FOR(i,70){ double ax=Arow_times(w.qp,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    LANE_FOR(i,70){ double ax=Arow_times(WQP,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;
