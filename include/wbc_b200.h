@@ -90,6 +90,50 @@ int wbc_get_outputs(wbc_handle* h, double* tau, double* grf, double* x, int* rc,
  * A[70*42], lbA[70], ubA[70]; whole_body_controller.cpp:479-515), expanded on the host from the compact device form. */
 int wbc_get_dense_qp(wbc_handle* h, int robot, double* H, double* g, double* A, double* lbA, double* ubA);
 
+/* ------------------------------------------------------------------------------------------------------------------------------
+ * "Next" rows of the hot path: the producer of the references and a plant, so that a closed-loop
+ * rollout of N robots never leaves the GPU.
+ * ------------------------------------------------------------------------------------------------------------------------------ */
+
+/* Replaces MotionPlanner::params / load_parameters (include/anymal_wbc/motion_planner.hpp:40-51, src/motion_planner.cpp:99-119,
+ * config/params_planner.yaml).  cycle_duration = 4 * step_duration is derived like :118. */
+typedef struct wbc_planner_params {
+    double step_length, height_control_point, x_offset, y_offset, step_duration, body_height, body_final_velocity, dt;
+} wbc_planner_params;
+void wbc_planner_default_params(wbc_planner_params* p);          /* config/params_planner.yaml:1-8 */
+
+/* Replaces MotionPlanner::MotionPlanner() (src/motion_planner.cpp:130-177): one planner per robot of the handle, velocity command
+ * zero, body at (0,0,body_height), feet at (+-x_offset, +-y_offset, 0), latched message = stand at body_height, contacts 1111. */
+int wbc_planner_create(wbc_handle* h, const wbc_planner_params* params);
+int wbc_planner_reset(wbc_handle* h, int first, int count);
+/* Replaces MotionPlanner::input_callback (src/motion_planner.cpp:122-127; geometry_msgs/Twist linear.x, linear.y, angular.z):
+ * arrays of N, host or device; NULL keeps the previous values.  Takes effect at the next planner period (ros::spinOnce). */
+int wbc_planner_set_cmd_vel(wbc_handle* h, const double* vx, const double* vy, const double* yaw_rate);
+/* One period (params.dt) of MotionPlanner::plannerLoop (src/motion_planner.cpp:180-376) for every robot.  Where the reference
+ * publishes /anymal/reference in that period, the message is handed to the controller exactly like referenceCallback
+ * (src/whole_body_controller.cpp:150-185: all six reference vectors, footContacts, isSwitchingFootState_ re-derived from the previous
+ * message); where it does not (phase change, end of cycle), the controller's reference and switching flag stay latched. */
+int wbc_planner_tick(wbc_handle* h);
+/* Inspection: the controller's current reference buffers (what referenceCallback last stored), the switching flag and whether the
+ * last planner period published (bytes; needs wbc_planner_create).  Any pointer may be NULL. */
+int wbc_get_reference(wbc_handle* h, double* pose, double* vel, double* acc, double* sw_pos, double* sw_vel, double* sw_acc,
+                      unsigned char* contacts, unsigned char* switching, unsigned char* published);
+/* Inspection: the controller's current state inputs (what the state callbacks last stored, or what the plant integrated). */
+int wbc_get_state(wbc_handle* h, double* q, double* qd, double* base_pos, double* base_quat_wxyz, double* base_twist);
+
+/* Plant for closed-loop rollouts.  The reference has none (Gazebo, launch/spawn.launch:27-59); this is an ideal-actuator rigid-body
+ * plant: it integrates the generalized accelerations implied by the QP solution (its equality rows ARE the floating-base dynamics
+ * and the stance constraints), nu_dot = T^-1 (x[0:18] - Tdot nu), with semi-implicit Euler at loopRate and writes the new
+ * q, qd, base pose and twist into the controller's state inputs.  wbc_plant_enable makes wbc_update_state export T^-1 / Tdot nu. */
+int wbc_plant_enable(wbc_handle* h);
+int wbc_plant_step(wbc_handle* h);
+/* `ticks` control ticks of the closed loop (src/whole_body_controller.cpp:639-673 with the planner node beside it):
+ * every `planner_every`-th tick (4 = 400 Hz / 100 Hz) one planner period, then updateState, solveQP, computeJointTorques, plant step.
+ * Asynchronous on the stream.  Needs wbc_planner_create and wbc_plant_enable. */
+int wbc_rollout(wbc_handle* h, int ticks, int planner_every);
+/* per-robot rollout statistics since the last reset: control ticks, ticks whose solve did not return 0, sum and max of nWSR */
+int wbc_rollout_stats(wbc_handle* h, int* ticks, int* failed_ticks, int* nwsr_sum, int* nwsr_max, int reset);
+
 int wbc_num_robots(const wbc_handle* h);
 /* number of kernel launches issued by this handle so far (bench.py reports it as gpu_launches) */
 long long wbc_launch_count(const wbc_handle* h);

@@ -90,6 +90,28 @@ class OracleBatch:
     def step(self, nthreads=0, assemble_only=False):
         return lib().orc_step(self._h, nthreads, int(assemble_only))
 
+    def rollout(self, ticks, cmd, planner_every=4, planner_params=None, nthreads=0, record=True):
+        """closed loop of `ticks` control ticks from the current state: restated planner (constant /cmd_vel per robot, cmd (3, N)) ->
+        controller -> plant (DEFINED in oracle_capi.cpp: no reference counterpart).  Returns wall seconds and per-tick records."""
+        P = dict(DEFAULT_PLANNER_PARAMS)
+        if planner_params:
+            P.update(planner_params)
+        pp = np.array([P[k] for k in PLANNER_PARAM_ORDER], dtype=np.float64)
+        cmd = _f64(cmd); assert cmd.shape == (3, self.N)
+        N, K = self.N, int(ticks)
+        rec = dict(tau=np.zeros((K, 12, N)), rc=np.zeros((K, N), np.int32), nwsr=np.zeros((K, N), np.int32), q=np.zeros((K, 12, N)), pos=np.zeros((K, 3, N))) if record else {}
+        f = lib().orc_rollout; f.restype = C.c_double
+        f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 5
+        secs = f(self._h, K, int(planner_every), _p(pp), _p(cmd), int(nthreads), *[_p(rec.get(k)) for k in ("tau", "rc", "nwsr", "q", "pos")])
+        rec["seconds"] = secs
+        return rec
+
+    def state(self):
+        N = self.N
+        o = dict(q=np.zeros((12, N)), qd=np.zeros((12, N)), base_pos=np.zeros((3, N)), base_quat=np.zeros((4, N)), base_twist=np.zeros((6, N)))
+        lib().orc_get_state(self._h, *[_p(o[k]) for k in ("q", "qd", "base_pos", "base_quat", "base_twist")])
+        return o
+
     def outputs(self):
         N = self.N
         o = dict(tau=np.zeros((12, N)), grf=np.zeros((12, N)), x=np.zeros((42, N)), rc=np.zeros(N, np.int32),
@@ -128,3 +150,21 @@ def qp_sequence(H, g, A, lbA, ubA, nwsr_max=100):
     o = dict(x=np.zeros((T, 42)), y=np.zeros((T, 112)), ws=np.zeros((T, 112), np.int8), rc=np.zeros(T, np.int32), nwsr=np.zeros(T, np.int32))
     lib().orc_qp_sequence(T, _p(H), _p(g), _p(A), _p(lbA), _p(ubA), nwsr_max, _p(o["x"]), _p(o["y"]), _p(o["ws"]), _p(o["rc"]), _p(o["nwsr"]))
     return o
+
+
+PLANNER_PARAM_ORDER = ["step_length", "height_control_point", "x_offset", "y_offset", "step_duration", "body_height", "body_final_velocity", "dt"]
+DEFAULT_PLANNER_PARAMS = dict(step_length=0.1, height_control_point=0.1, x_offset=0.50, y_offset=0.33, step_duration=0.2, body_height=0.50,
+                              body_final_velocity=0.40, dt=0.01)                       # config/params_planner.yaml
+
+
+def planner_run(cmd, params=None):
+    """restated MotionPlanner::plannerLoop for len(cmd) planner periods; cmd (K, 3) = /cmd_vel (linear.x, linear.y, angular.z) per period.
+    Returns published (K,), and the latched message at the end of each period: pose/vel/acc (K, 6), sw_pos/sw_vel/sw_acc (K, 12), contacts (K, 4)."""
+    P = dict(DEFAULT_PLANNER_PARAMS)
+    if params:
+        P.update(params)
+    pp = np.array([P[k] for k in PLANNER_PARAM_ORDER], dtype=np.float64)
+    cmd = _f64(cmd); K = cmd.shape[0]
+    pub = np.zeros(K, np.uint8); msg = np.zeros((K, 54)); con = np.zeros((K, 4), np.uint8)
+    lib().orc_planner_run(_p(pp), K, _p(cmd), _p(pub), _p(msg), _p(con))
+    return dict(published=pub, pose=msg[:, 0:6], vel=msg[:, 6:12], acc=msg[:, 12:18], sw_pos=msg[:, 18:30], sw_vel=msg[:, 30:42], sw_acc=msg[:, 42:54], contacts=con)

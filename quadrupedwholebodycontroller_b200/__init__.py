@@ -16,13 +16,20 @@ _lib = None
 
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
            "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
-           "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error"]
+           "wbc_planner_default_params", "wbc_planner_create", "wbc_planner_reset", "wbc_planner_set_cmd_vel", "wbc_planner_tick", "wbc_get_reference",
+           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error"]
 
 
 class WbcParams(C.Structure):
     """wbc_params == WholeBodyController::params (reference whole_body_controller.hpp:91-104)."""
     _fields_ = [(k, C.c_double) for k in ("friction", "loopRate", "maxTorque", "kpValue", "kpValueZ", "kdValue", "kiValue",
                                           "kpSwingValue", "kdSwingValue", "slackWeight")] + [("initialReferencePose", C.c_double * 6)]
+
+
+class WbcPlannerParams(C.Structure):
+    """wbc_planner_params == MotionPlanner::params (reference motion_planner.hpp:40-51, config/params_planner.yaml)."""
+    _fields_ = [(k, C.c_double) for k in ("step_length", "height_control_point", "x_offset", "y_offset", "step_duration", "body_height",
+                                          "body_final_velocity", "dt")]
 
 
 def load_library():
@@ -48,6 +55,16 @@ def load_library():
         lib.wbc_default_params.argtypes = [C.POINTER(WbcParams)]
         lib.wbc_profile.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.wbc_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        lib.wbc_planner_default_params.argtypes = [C.POINTER(WbcPlannerParams)]
+        lib.wbc_planner_create.argtypes = [C.c_void_p, C.POINTER(WbcPlannerParams)]
+        lib.wbc_planner_reset.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        lib.wbc_planner_set_cmd_vel.argtypes = [C.c_void_p] + [C.c_void_p] * 3
+        lib.wbc_get_reference.argtypes = [C.c_void_p] + [C.c_void_p] * 9
+        lib.wbc_get_state.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        for name in ("wbc_planner_tick", "wbc_plant_enable", "wbc_plant_step"):
+            getattr(lib, name).argtypes = [C.c_void_p]
+        lib.wbc_rollout.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        lib.wbc_rollout_stats.argtypes = [C.c_void_p] + [C.c_void_p] * 4 + [C.c_int]
         _lib = lib
     return _lib
 
@@ -156,3 +173,50 @@ class WholeBodyController:
         a, b, c = C.c_float(), C.c_float(), C.c_float()
         self._ck(load_library().wbc_last_kernel_ms(self._h, C.byref(a), C.byref(b), C.byref(c)))
         return dict(update_state=a.value, solve_qp=b.value, compute_joint_torques=c.value)
+
+    # ---- planner, plant, closed-loop rollout (reference src/motion_planner.cpp) ----
+    def plannerCreate(self, params=None):
+        p = params
+        if p is None:
+            p = WbcPlannerParams(); load_library().wbc_planner_default_params(C.byref(p))
+        self._ck(load_library().wbc_planner_create(self._h, C.byref(p)))
+
+    def plannerReset(self, first=0, count=None):
+        self._ck(load_library().wbc_planner_reset(self._h, first, self.N - first if count is None else count))
+
+    def plannerSetCmdVel(self, vx=None, vy=None, yaw_rate=None):
+        self._ck(load_library().wbc_planner_set_cmd_vel(self._h, _ptr(vx), _ptr(vy), _ptr(yaw_rate)))
+
+    def plannerTick(self):
+        self._ck(load_library().wbc_planner_tick(self._h))
+
+    def getReference(self, with_published=True):
+        N = self.N
+        o = dict(pose=np.zeros((6, N)), vel=np.zeros((6, N)), acc=np.zeros((6, N)), sw_pos=np.zeros((12, N)), sw_vel=np.zeros((12, N)), sw_acc=np.zeros((12, N)),
+                 contacts=np.zeros((4, N), np.uint8), switching=np.zeros(N, np.uint8))
+        pub = np.zeros(N, np.uint8) if with_published else None
+        self._ck(load_library().wbc_get_reference(self._h, *[_ptr(o[k]) for k in ("pose", "vel", "acc", "sw_pos", "sw_vel", "sw_acc", "contacts", "switching")], _ptr(pub)))
+        if with_published:
+            o["published"] = pub
+        return o
+
+    def getState(self):
+        N = self.N
+        o = dict(q=np.zeros((12, N)), qd=np.zeros((12, N)), base_pos=np.zeros((3, N)), base_quat=np.zeros((4, N)), base_twist=np.zeros((6, N)))
+        self._ck(load_library().wbc_get_state(self._h, *[_ptr(o[k]) for k in ("q", "qd", "base_pos", "base_quat", "base_twist")]))
+        return o
+
+    def plantEnable(self):
+        self._ck(load_library().wbc_plant_enable(self._h))
+
+    def plantStep(self):
+        self._ck(load_library().wbc_plant_step(self._h))
+
+    def rollout(self, ticks, planner_every=4):
+        self._ck(load_library().wbc_rollout(self._h, int(ticks), int(planner_every)))
+
+    def rolloutStats(self, reset=False):
+        N = self.N
+        o = dict(ticks=np.zeros(N, np.int32), failed_ticks=np.zeros(N, np.int32), nwsr_sum=np.zeros(N, np.int32), nwsr_max=np.zeros(N, np.int32))
+        self._ck(load_library().wbc_rollout_stats(self._h, *[_ptr(o[k]) for k in ("ticks", "failed_ticks", "nwsr_sum", "nwsr_max")], int(reset)))
+        return o

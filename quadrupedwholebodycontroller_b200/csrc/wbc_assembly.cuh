@@ -20,7 +20,9 @@ WBC_DEV void eul_rpy(const double* R,double* rpy){
 
 // Everything after the leg phase.  `st` is this instance's persistent state (global memory), `out` its compact QP.
 // `first` != 0 resets the state like setInitialState (wbc.cpp:65-120): oldT = I, oldJ = 0, Tdot^-1 = 0, integral = 0.
-WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,CtrlState& st,QPData& out,int lane,int switching,int first){
+// `plant` (nullable, SoA with stride N): what wbc_plant_step needs to turn the QP's centroidal accelerations back into generalized
+// ones, nu_dot = T^-1 (a - Tdot nu):  d = p_com - p_base (3), B = Mbb^-1 Mbj (72), Tdot_top nu (6).
+WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,CtrlState& st,QPData& out,int lane,int switching,int first,double* plant,int N){
     const double* R=s.Rwb;
     // ---- D1: base totals (locked inertia, CoM, momentum, gravity-free base wrench) ----
     if(lane==0){
@@ -120,6 +122,11 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
         if(!switching){ double told=first?((i==j)?1.0:0.0):st.Told[e]; v=(s.Ttop[e]-told)/timeStep; }
         s.Tdot[e]=v; }
     WBC_SYNC();
+    if(plant){
+        LANE_FOR(i,3) plant[(size_t)i*N]=s.d[i];
+        LANE_FOR(e,72) plant[(size_t)(3+e)*N]=s.B[e];
+        LANE_FOR(i,6){ double v=0; for(int k=0;k<6;k++) v+=s.Tdot[18*i+k]*s.twist[k]; for(int k=0;k<12;k++) v+=s.Tdot[18*i+6+k]*s.qd[k]; plant[(size_t)(75+i)*N]=v; }
+    }
     LANE_FOR(e,108){ int i=e/18,j=e%18; double v=0;
         if(j<6){ for(int k=0;k<6;k++) v+=s.Tdot[18*i+k]*s.X[6*k+j]; }
         else { v=s.Tdot[18*i+j]; for(int k=0;k<6;k++) v-=s.Tdot[18*i+k]*s.B[12*k+(j-6)]; }

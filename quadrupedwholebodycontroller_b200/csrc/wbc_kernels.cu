@@ -11,6 +11,7 @@
 #include "../../include/wbc_b200.h"
 #include "wbc_assembly.cuh"
 #include "wbc_qp.cuh"
+#include "wbc_planner.cuh"
 #include "anymal_model.h"
 
 using namespace wbc;
@@ -26,7 +27,7 @@ __constant__ ModelConst c_model;
 
 // ---------------------------------------------------------------- kernel 1: RBD + centroidal transform + QP assembly
 // grid-stride over instances; the RBD stage is ~40 kFLOP per robot, far below the solver's cost
-__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,double* com){
+__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,double* com,double* plantAux){
     __shared__ ModelConst mc;
     __shared__ RbdScratch s;
     __shared__ QPData qp;
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,B
         WBC_SYNC();
         if(lane<4) rbd_leg(mc,s,lane);
         WBC_SYNC();
-        wbc_assemble(mc,prm,s,st[r],qp,lane,(int)in.switching[r],(int)first[r]);
+        wbc_assemble(mc,prm,s,st[r],qp,lane,(int)in.switching[r],(int)first[r],plantAux?plantAux+r:nullptr,N);
         { const double* src=(const double*)&qp; double* dst=(double*)&qpd[r]; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
         LANE_FOR(k,3) com[k*N+r]=s.com[k];
         WBC_SYNC();
@@ -91,9 +92,10 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
 
 // ---------------------------------------------------------------- kernel 3: torque recovery (wbc.cpp:553-577)
 // tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*;  a robot whose QP failed publishes zero torques (terminate(), :626-635)
-__global__ void wbc_compute_torques_kernel(int N,const QPData* qpd,BatchOut out){
+__global__ void wbc_compute_torques_kernel(int N,const QPData* qpd,BatchOut out,int* stats){
     const int r=blockIdx.x*blockDim.x+threadIdx.x;
     if(r>=N) return;
+    if(stats){ const int nw=out.nwsr[r]; stats[r]+=1; if(out.rc[r]!=0) stats[N+r]+=1; stats[2*N+r]+=nw; if(nw>stats[3*N+r]) stats[3*N+r]=nw; }   // ticks, failed ticks, sum / max of nWSR
     const QPData& q=qpd[r];
     const bool ok=out.rc[r]==0;
     double xs[24]; for(int k=0;k<24;k++) xs[k]=out.x[(6+k)*N+r];
@@ -103,6 +105,53 @@ __global__ void wbc_compute_torques_kernel(int N,const QPData* qpd,BatchOut out)
         out.tau[i*N+r]= ok? (s+q.biasj[i]-t) : 0.0;
         out.grf[i*N+r]= xs[12+i];
     }
+}
+
+
+// ---------------------------------------------------------------- batched MotionPlanner (wbc_planner.cuh), one planner per thread
+// mode 0: one planner period + hand-over of a published message (referenceCallback, wbc.cpp:150-185); mode 1: constructor state
+struct RefOut { double *pose,*vel,*acc,*swp,*swv,*swa; unsigned char *contacts,*prevc,*switching,*published; };
+__global__ void wbc_planner_kernel(int N,PlannerParams P,PlannerState* ps,const double* cmd,RefOut o,int mode,int first,int count){
+    const int r=first+blockIdx.x*blockDim.x+threadIdx.x;
+    if(r>=first+count||r>=N) return;
+    PlannerState& s=ps[r];
+    if(mode==1){ planner_init(P,s); o.published[r]=0; return; }
+    for(int k=0;k<3;k++) s.cmd[k]=cmd[(size_t)k*N+r];             // input_callback (motion_planner.cpp:122-127), delivered by the spinOnce before this period
+    const bool pub=planner_tick(P,s);
+    o.published[r]=pub?1:0;
+    if(!pub) return;
+    for(int k=0;k<6;k++){ o.pose[(size_t)k*N+r]=s.pose[k]; o.vel[(size_t)k*N+r]=s.vel[k]; o.acc[(size_t)k*N+r]=s.acc[k]; }
+    for(int k=0;k<12;k++){ o.swp[(size_t)k*N+r]=s.swp[k]; o.swv[(size_t)k*N+r]=s.swv[k]; o.swa[(size_t)k*N+r]=s.swa[k]; }
+    bool sw=false; for(int l=0;l<4;l++){ const unsigned char c=s.contacts[l]; if(o.prevc[(size_t)l*N+r]!=c) sw=true; o.prevc[(size_t)l*N+r]=c; o.contacts[(size_t)l*N+r]=c; }
+    o.switching[r]=sw?1:0;
+}
+
+// ---------------------------------------------------------------- ideal-actuator plant, one robot per thread
+// The QP's equality rows are the floating-base dynamics and the stance constraints, so the generalized acceleration implied by its
+// solution, nu_dot = T^-1 (a* - Tdot nu) with a* = x[0:18], is what the rigid-body model does under (tau*, f*).  T^-1 = [[X,-B],[0,1]]
+// (wbc_assembly.cuh).  Semi-implicit Euler at the control rate: velocities first, then positions; the orientation is advanced by the
+// world-frame rotation vector omega*dt.  A robot whose solve failed coasts (zero acceleration).
+__global__ void wbc_plant_step_kernel(int N,double dt,const double* aux,const double* x,const int* rc,double* q,double* qd,double* pos,double* quat,double* twist){
+    const int r=blockIdx.x*blockDim.x+threadIdx.x;
+    if(r>=N) return;
+    const bool ok=rc[r]==0;
+    double d[3],ab[6],qdd[12],nb[6];
+    for(int k=0;k<3;k++) d[k]=aux[(size_t)k*N+r];
+    for(int k=0;k<6;k++) ab[k]=x[(size_t)k*N+r]-aux[(size_t)(75+k)*N+r];
+    for(int k=0;k<12;k++) qdd[k]=ok?x[(size_t)(6+k)*N+r]:0.0;
+    double c[3]; cross3(d,ab+3,c);
+    for(int k=0;k<3;k++){ nb[k]=ab[k]+c[k]; nb[3+k]=ab[3+k]; }
+    for(int i=0;i<6;i++){ double v=nb[i]; for(int j=0;j<12;j++) v-=aux[(size_t)(3+12*i+j)*N+r]*qdd[j]; nb[i]=ok?v:0.0; }
+    double tw[6]; for(int k=0;k<6;k++){ tw[k]=twist[(size_t)k*N+r]+nb[k]*dt; twist[(size_t)k*N+r]=tw[k]; }
+    for(int k=0;k<12;k++){ const double v=qd[(size_t)k*N+r]+qdd[k]*dt; qd[(size_t)k*N+r]=v; q[(size_t)k*N+r]+=v*dt; }
+    for(int k=0;k<3;k++) pos[(size_t)k*N+r]+=tw[k]*dt;
+    const double rx=tw[3]*dt, ry=tw[4]*dt, rz=tw[5]*dt, ang=sqrt(rx*rx+ry*ry+rz*rz);
+    double dw=1.0,dx=0.5*rx,dy=0.5*ry,dz=0.5*rz;                      // small-angle limit of (cos(a/2), sin(a/2) r/a)
+    if(ang>1e-12){ const double sh=sin(0.5*ang)/ang; dw=cos(0.5*ang); dx=sh*rx; dy=sh*ry; dz=sh*rz; }
+    const double qw=quat[r],qx=quat[(size_t)N+r],qy=quat[(size_t)2*N+r],qz=quat[(size_t)3*N+r];
+    double nw=dw*qw-dx*qx-dy*qy-dz*qz, nx=dw*qx+dx*qw+dy*qz-dz*qy, ny=dw*qy-dx*qz+dy*qw+dz*qx, nz=dw*qz+dx*qy-dy*qx+dz*qw;
+    const double nn=sqrt(nw*nw+nx*nx+ny*ny+nz*nz); nw/=nn; nx/=nn; ny/=nn; nz/=nn;
+    quat[r]=nw; quat[(size_t)N+r]=nx; quat[(size_t)2*N+r]=ny; quat[(size_t)3*N+r]=nz;
 }
 
 // wbc.cpp:176-184: isSwitchingFootState_ = (contacts != previous message's contacts); also rolls prev <- current
@@ -139,6 +188,9 @@ struct wbc_handle {
     // outputs
     double *tau=nullptr,*grf=nullptr,*x=nullptr,*com=nullptr; int *rc=nullptr,*nwsr=nullptr; signed char* ws=nullptr;
     cudaEvent_t ev[4]={nullptr,nullptr,nullptr,nullptr};
+    // planner / plant / rollout
+    PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
+    double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
     int smCount=0, qpBlocksPerSM=1; size_t qpSmem=0;
     long long launches=0;
     std::string err;
@@ -224,7 +276,7 @@ extern "C" int wbc_destroy(wbc_handle* h){
     cudaSetDevice(h->device);
     if(h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
-                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof};
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats};
     for(void* p:ptrs) if(p) cudaFree(p);
     for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
     if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
@@ -242,6 +294,7 @@ extern "C" int wbc_reset(wbc_handle* h,int first,int count){
     wbc_reset_kernel<<<(count+127)/128,128,0,h->stream>>>(h->N,h->devParams,first,count,h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,
                                                          h->contacts,h->prevc,h->switching,h->first,h->rc,h->nwsr,h->tau,h->grf,h->x);
     h->launches++; CK(cudaGetLastError());
+    if(first==0&&count==h->N) h->tick=0;
     return WBC_OK;
 }
 extern "C" int wbc_set_state(wbc_handle* h,const double* q,const double* qd,const double* pos,const double* quat,const double* twist){
@@ -269,7 +322,7 @@ extern "C" int wbc_update_state(wbc_handle* h){
     CK(cudaSetDevice(h->device));
     int grid=h->smCount*16; if(grid>h->N) grid=h->N;
     CK(cudaEventRecord(h->ev[0],h->stream));
-    wbc_update_state_kernel<<<grid,32,0,h->stream>>>(h->N,h->devParams,batch_in(h),h->ctrl,h->qpd,h->first,h->com);
+    wbc_update_state_kernel<<<grid,32,0,h->stream>>>(h->N,h->devParams,batch_in(h),h->ctrl,h->qpd,h->first,h->com,h->plantAux);
     h->launches++; CK(cudaGetLastError());
     CK(cudaEventRecord(h->ev[1],h->stream));
     return WBC_OK;
@@ -288,7 +341,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
 extern "C" int wbc_compute_joint_torques(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
-    wbc_compute_torques_kernel<<<(h->N+63)/64,64,0,h->stream>>>(h->N,h->qpd,batch_out(h));
+    wbc_compute_torques_kernel<<<(h->N+63)/64,64,0,h->stream>>>(h->N,h->qpd,batch_out(h),h->stats);
     h->launches++; CK(cudaGetLastError());
     CK(cudaEventRecord(h->ev[3],h->stream));
     return WBC_OK;
@@ -313,6 +366,111 @@ extern "C" int wbc_get_dense_qp(wbc_handle* h,int robot,double* H,double* g,doub
     if(g) for(int i=0;i<42;i++) g[i]=(i>=18&&i<30)?q.gf[i-18]:0.0;
     if(A) for(int i=0;i<70;i++) for(int j=0;j<42;j++) A[i*42+j]=Ael(q,i,j);
     if(lbA) memcpy(lbA,q.lbA,sizeof(q.lbA)); if(ubA) memcpy(ubA,q.ubA,sizeof(q.ubA));
+    return WBC_OK;
+}
+
+// ================================================================= planner, plant, rollout (include/wbc_b200.h, section "next rows")
+static void fill_quintic(double* a,double T,double vi,double vf){       // generateQuinticPolynomial (motion_planner.cpp:77-97), host doubles
+    const double T2=T*T, T3=T2*T, T4=T3*T, T5=T4*T;
+    a[0]=0.0; a[1]=vi; a[2]=0.0; a[3]=(10.0 - 4.0 * vf * T - 6.0 * vi * T) / T3; a[4]=(-15.0 + 7.0 * vf * T + 8.0 * vi * T) / T4; a[5]=(6.0 - 3.0 * vf * T - 3.0 * vi * T) / T5;
+}
+extern "C" void wbc_planner_default_params(wbc_planner_params* p){
+    if(!p) return;
+    p->step_length=0.1; p->height_control_point=0.1; p->x_offset=0.50; p->y_offset=0.33; p->step_duration=0.2; p->body_height=0.50; p->body_final_velocity=0.40; p->dt=0.01;
+}
+static RefOut ref_out(const wbc_handle* h){ RefOut o; o.pose=h->pose; o.vel=h->vel; o.acc=h->acc; o.swp=h->swp; o.swv=h->swv; o.swa=h->swa; o.contacts=h->contacts; o.prevc=h->prevc;
+    o.switching=h->switching; o.published=h->published; return o; }
+extern "C" int wbc_planner_reset(wbc_handle* h,int first,int count){
+    if(!h||!h->planner||first<0||count<0||first+count>h->N) return WBC_ERR_ARG;
+    if(count==0) return WBC_OK;
+    CK(cudaSetDevice(h->device));
+    wbc_planner_kernel<<<(count+127)/128,128,0,h->stream>>>(h->N,h->plannerParams,h->planner,h->plannerCmd,ref_out(h),1,first,count);
+    h->launches++; CK(cudaGetLastError());
+    return WBC_OK;
+}
+extern "C" int wbc_planner_create(wbc_handle* h,const wbc_planner_params* p){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    wbc_planner_params d; if(p) d=*p; else wbc_planner_default_params(&d);
+    PlannerParams& P=h->plannerParams;
+    P.step_length=d.step_length; P.height_control_point=d.height_control_point; P.x_offset=d.x_offset; P.y_offset=d.y_offset; P.step_duration=d.step_duration;
+    P.cycle_duration=4*d.step_duration; P.body_height=d.body_height; P.body_final_velocity=d.body_final_velocity; P.dt=d.dt;     // load_parameters (motion_planner.cpp:99-119)
+    fill_quintic(P.poly_foot,P.step_duration,0.0,0.0); fill_quintic(P.poly_body_start,P.cycle_duration,0.0,P.body_final_velocity);
+    fill_quintic(P.poly_body_continue,P.cycle_duration,P.body_final_velocity,P.body_final_velocity);                                  // motion_planner.cpp:190-195
+    const size_t N=(size_t)h->N;
+    if(!h->planner){
+        if(dalloc(h->planner,N)!=cudaSuccess||dalloc(h->plannerCmd,3*N)!=cudaSuccess||dalloc(h->published,N)!=cudaSuccess){ h->err="cudaMalloc (planner)"; return WBC_ERR_NOMEM; }
+        CK(cudaMemsetAsync(h->plannerCmd,0,3*N*sizeof(double),h->stream));
+    }
+    return wbc_planner_reset(h,0,h->N);
+}
+extern "C" int wbc_planner_set_cmd_vel(wbc_handle* h,const double* vx,const double* vy,const double* yaw_rate){
+    if(!h||!h->planner) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N, D=sizeof(double); int r;
+    if((r=copy_in(h,h->plannerCmd,vx,N*D))||(r=copy_in(h,h->plannerCmd+N,vy,N*D))||(r=copy_in(h,h->plannerCmd+2*N,yaw_rate,N*D))) return r;
+    return WBC_OK;
+}
+extern "C" int wbc_planner_tick(wbc_handle* h){
+    if(!h||!h->planner) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    wbc_planner_kernel<<<(h->N+127)/128,128,0,h->stream>>>(h->N,h->plannerParams,h->planner,h->plannerCmd,ref_out(h),0,0,h->N);
+    h->launches++; CK(cudaGetLastError());
+    return WBC_OK;
+}
+extern "C" int wbc_get_reference(wbc_handle* h,double* pose,double* vel,double* acc,double* swp,double* swv,double* swa,unsigned char* contacts,unsigned char* switching,
+                                 unsigned char* published){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N, D=sizeof(double); bool host=false; int r;
+    if((r=copy_out(h,pose,h->pose,6*N*D,host))||(r=copy_out(h,vel,h->vel,6*N*D,host))||(r=copy_out(h,acc,h->acc,6*N*D,host))||(r=copy_out(h,swp,h->swp,12*N*D,host))
+       ||(r=copy_out(h,swv,h->swv,12*N*D,host))||(r=copy_out(h,swa,h->swa,12*N*D,host))||(r=copy_out(h,contacts,h->contacts,4*N,host))||(r=copy_out(h,switching,h->switching,N,host))) return r;
+    if(published){ if(!h->published) return WBC_ERR_ARG; if((r=copy_out(h,published,h->published,N,host))) return r; }
+    if(host) CK(cudaStreamSynchronize(h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_get_state(wbc_handle* h,double* q,double* qd,double* pos,double* quat,double* twist){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N, D=sizeof(double); bool host=false; int r;
+    if((r=copy_out(h,q,h->q,12*N*D,host))||(r=copy_out(h,qd,h->qd,12*N*D,host))||(r=copy_out(h,pos,h->pos,3*N*D,host))||(r=copy_out(h,quat,h->quat,4*N*D,host))
+       ||(r=copy_out(h,twist,h->twist,6*N*D,host))) return r;
+    if(host) CK(cudaStreamSynchronize(h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_plant_enable(wbc_handle* h){
+    if(!h) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N;
+    if(!h->plantAux){ if(dalloc(h->plantAux,81*N)!=cudaSuccess){ h->err="cudaMalloc (plant)"; return WBC_ERR_NOMEM; } CK(cudaMemsetAsync(h->plantAux,0,81*N*sizeof(double),h->stream)); }
+    if(!h->stats){ if(dalloc(h->stats,4*N)!=cudaSuccess){ h->err="cudaMalloc (stats)"; return WBC_ERR_NOMEM; } CK(cudaMemsetAsync(h->stats,0,4*N*sizeof(int),h->stream)); }
+    return WBC_OK;
+}
+extern "C" int wbc_plant_step(wbc_handle* h){
+    if(!h||!h->plantAux) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    wbc_plant_step_kernel<<<(h->N+127)/128,128,0,h->stream>>>(h->N,1.0/h->devParams.loopRate,h->plantAux,h->x,h->rc,h->q,h->qd,h->pos,h->quat,h->twist);
+    h->launches++; CK(cudaGetLastError());
+    return WBC_OK;
+}
+extern "C" int wbc_rollout(wbc_handle* h,int ticks,int planner_every){
+    if(!h||ticks<0||planner_every<1||!h->plantAux||!h->planner) return WBC_ERR_ARG;
+    int r;
+    for(int t=0;t<ticks;t++){
+        if(h->tick%planner_every==0) if((r=wbc_planner_tick(h))) return r;
+        if((r=wbc_step(h))||(r=wbc_plant_step(h))) return r;
+        h->tick++;
+    }
+    return WBC_OK;
+}
+extern "C" int wbc_rollout_stats(wbc_handle* h,int* ticks,int* failed_ticks,int* nwsr_sum,int* nwsr_max,int reset){
+    if(!h||!h->stats) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N; bool host=false; int r;
+    if((r=copy_out(h,ticks,h->stats,N*sizeof(int),host))||(r=copy_out(h,failed_ticks,h->stats+N,N*sizeof(int),host))||(r=copy_out(h,nwsr_sum,h->stats+2*N,N*sizeof(int),host))
+       ||(r=copy_out(h,nwsr_max,h->stats+3*N,N*sizeof(int),host))) return r;
+    if(host) CK(cudaStreamSynchronize(h->stream));
+    if(reset) CK(cudaMemsetAsync(h->stats,0,4*N*sizeof(int),h->stream));
     return WBC_OK;
 }
 extern "C" int wbc_num_robots(const wbc_handle* h){ return h?h->N:0; }

@@ -1,0 +1,148 @@
+"""GPU (-m gpu): the batched MotionPlanner, the hand-over of its messages to the controller, the plant and the closed-loop rollout,
+called through the C ABI, against the committed golden vectors and the oracle (restated src/motion_planner.cpp; the plant has no
+reference counterpart and is defined densely in oracle/oracle_capi.cpp).
+
+Tolerances: planner outputs bit-exact when the yaw rate is zero (no FMA contraction on the device: __dmul_rn/__dadd_rn), <= 1e-12
+relative when sin/cos of a non-zero yaw enter; discrete outputs (published, contacts, switching) always exact.  Closed loop: return
+codes identical, torques within 1e-9 relative per tick as long as both sides took the same number of working-set changes, and within
+1e-6 over the whole trajectory (a closed loop feeds rounding differences back through the state).
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", "tools"))
+import make_golden_planner as mgp          # noqa: E402
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(HERE, "golden", "planner_golden.npz"))
+MSG = ("pose", "vel", "acc", "sw_pos", "sw_vel", "sw_acc")
+
+
+def run_device_planner(wbc, cmd_per_robot):
+    """cmd_per_robot: (N, K, 3).  Returns per-period arrays (K, ..., N) of what the controller holds after each planner period."""
+    N, K, _ = cmd_per_robot.shape
+    ctl = wbc.WholeBodyController(N); ctl.plannerCreate()
+    rec = {k: [] for k in MSG + ("contacts", "switching", "published")}
+    for p in range(K):
+        c = np.ascontiguousarray(cmd_per_robot[:, p, :].T)
+        ctl.plannerSetCmdVel(c[0], c[1], c[2]); ctl.plannerTick()
+        r = ctl.getReference()
+        for k in rec:
+            rec[k].append(r[k])
+    ctl.close()
+    return {k: np.stack(v) for k, v in rec.items()}
+
+
+def test_planner_matches_golden_profiles(wbc):
+    names = ["straight", "turning", "startstop"]
+    cmd = np.stack([GOLD[f"p_{n}_cmd"] for n in names])
+    dev = run_device_planner(wbc, cmd)
+    for i, n in enumerate(names):
+        pub = GOLD[f"p_{n}_published"].astype(bool)
+        assert np.array_equal(dev["published"][:, i].astype(bool), pub), n
+        # the controller holds the LAST PUBLISHED message (referenceCallback); the oracle records the latched ref_msg_ of every period,
+        # which only changes in periods that publish -> equal in every period from the first publication on
+        for k in MSG:
+            want = GOLD[f"p_{n}_{k}"]; got = dev[k][:, :, i]
+            if n == "turning":
+                assert np.abs(got - want).max() <= 1e-12 * max(1.0, np.abs(want).max()), (n, k)
+            else:
+                assert np.array_equal(got, want), (n, k)
+        assert np.array_equal(dev["contacts"][:, :, i], GOLD[f"p_{n}_contacts"]), n
+        # isSwitchingFootState_ (whole_body_controller.cpp:176-184): set by the first message with new contacts, cleared by the next
+        # message, latched over silent periods
+        con = GOLD[f"p_{n}_contacts"]; sw = np.zeros(len(con), bool); prev = np.ones(4, np.uint8); cur = False
+        for p in range(len(con)):
+            if pub[p]:
+                cur = bool((con[p] != prev).any()); prev = con[p]
+            sw[p] = cur
+        assert np.array_equal(dev["switching"][:, i].astype(bool), sw), n
+
+
+def test_planner_matches_oracle_on_random_commands(wbc, orc):
+    rng = np.random.default_rng(5)
+    N, K = 64, 120
+    cmd = np.zeros((N, K, 3)); cmd[:, :, 0] = rng.uniform(-0.4, 0.4, (N, 1)); cmd[:, :, 1] = rng.uniform(-0.2, 0.2, (N, 1))
+    cmd[N // 2:, :, 2] = rng.uniform(-0.5, 0.5, (N // 2, 1))              # second half turns
+    cmd[::8, :30, :] = 0.0                                                # some robots stand for a while first
+    dev = run_device_planner(wbc, cmd)
+    for i in range(N):
+        r = orc.planner_run(cmd[i])
+        assert np.array_equal(dev["published"][:, i], r["published"]), i
+        assert np.array_equal(dev["contacts"][:, :, i], r["contacts"]), i
+        for k in MSG:
+            if i < N // 2:
+                assert np.array_equal(dev[k][:, :, i], r[k]), (i, k)
+            else:
+                assert np.abs(dev[k][:, :, i] - r[k]).max() <= 1e-12 * max(1.0, np.abs(r[k]).max()), (i, k)
+
+
+def rel(a, b):
+    return np.abs(a - b).max() / max(1.0, np.abs(b).max())
+
+
+def test_closed_loop_rollout_matches_golden(wbc):
+    st, ref, cmd = mgp.rollout_inputs()
+    N, K = mgp.ROLLOUT_N, mgp.ROLLOUT_TICKS
+    ctl = wbc.WholeBodyController(N); ctl.plannerCreate(); ctl.plantEnable()
+    ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.plannerSetCmdVel(cmd[0].copy(), cmd[1].copy(), cmd[2].copy())
+    worst_same, worst_all = 0.0, 0.0
+    for t in range(K):
+        ctl.rollout(1)
+        o = ctl.getOutputs(); s = ctl.getState()
+        assert np.array_equal(o["rc"], GOLD["r_rc"][t]), t
+        for i in range(N):
+            e = rel(o["tau"][:, i], GOLD["r_tau"][t][:, i]); worst_all = max(worst_all, e)
+            if o["nwsr"][i] == GOLD["r_nwsr"][t][i]:
+                worst_same = max(worst_same, e)
+        assert rel(s["q"], GOLD["r_q"][t]) < 1e-8 and rel(s["base_pos"], GOLD["r_pos"][t]) < 1e-8, t
+    assert worst_same < 1e-9, worst_same
+    assert worst_all < 1e-6, worst_all
+    fin = ctl.getState()
+    for k in ("q", "qd", "base_pos", "base_quat", "base_twist"):
+        assert rel(fin[k], GOLD[f"r_final_{k}"]) < 1e-8, k
+    stats = ctl.rolloutStats()
+    assert (stats["ticks"] == K).all() and (stats["failed_ticks"] == 0).all()
+    assert (stats["nwsr_max"] >= 40).all()                      # the cold start of tick 0
+    ctl.close()
+
+
+def test_plant_step_matches_oracle_from_random_states(wbc, orc, wl):
+    """one controller tick + one plant step from 64 randomised states with large velocities: closed-form T^-1 (device) vs dense 18x18
+    inverse (oracle)"""
+    N = 64
+    st, ref = wl.randomised(N, seed=99, contacts="mixed")
+    ctl = wbc.WholeBodyController(N); ctl.plannerCreate(); ctl.plantEnable()
+    ctl.setJointAndBaseState(**st); ctl.setReference(**ref)
+    # two ticks: the second one has a non-trivial Tdot (first tick: old T = identity)
+    for t in range(2):
+        ctl.step(); ctl.plantStep()
+    got = ctl.getState()
+    ctl.close()
+    # compare against the dense definition evaluated here in numpy from the oracle's intermediates
+    ob3 = orc.OracleBatch(N); ob3.set_state(**st); ob3.set_reference(**ref)
+    cur = {k: v.copy() for k, v in st.items()}
+    dt = 1.0 / 400.0
+    for t in range(2):
+        ob3.set_state(**cur); ob3.step(); w = ob3.outputs()
+        Told = [ob3.intermediates(i)["T"] for i in range(N)]
+        if t == 0:
+            Tprev = [np.eye(18)] * N
+        for i in range(N):
+            T = Told[i]; Tdot = (T - Tprev[i]) / dt if not ref["switching"][i] else np.zeros((18, 18))
+            nu = np.concatenate([cur["base_twist"][:, i], cur["qd"][:, i]])
+            nud = np.linalg.solve(T, w["x"][:18, i] - Tdot @ nu) if w["rc"][i] == 0 else np.zeros(18)
+            cur["base_twist"][:, i] += nud[:6] * dt; cur["qd"][:, i] += nud[6:] * dt
+            cur["q"][:, i] += cur["qd"][:, i] * dt; cur["base_pos"][:, i] += cur["base_twist"][:3, i] * dt
+            rv = cur["base_twist"][3:, i] * dt; a = np.linalg.norm(rv)
+            dq = np.concatenate([[np.cos(a / 2)], np.sin(a / 2) / a * rv]) if a > 1e-12 else np.concatenate([[1.0], 0.5 * rv])
+            qw, qx, qy, qz = cur["base_quat"][:, i]; dw, dx, dy, dz = dq
+            nq = np.array([dw * qw - dx * qx - dy * qy - dz * qz, dw * qx + dx * qw + dy * qz - dz * qy, dw * qy - dx * qz + dy * qw + dz * qx, dw * qz + dx * qy - dy * qx + dz * qw])
+            cur["base_quat"][:, i] = nq / np.linalg.norm(nq)
+        Tprev = Told
+    for k in ("q", "qd", "base_pos", "base_quat", "base_twist"):
+        assert rel(got[k], cur[k]) < 1e-9, k
