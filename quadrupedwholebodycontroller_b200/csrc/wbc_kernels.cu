@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
 #else
         { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
 #endif
-        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
         for(int k=0;k<8;k++) c.prof[k]=0;
         c.flops=0.0;
         const long long tstart=clock64();

@@ -108,6 +108,7 @@ struct QPCtx {
     int lane;
     int nFR,nFX,nAC,nIAC;
     int status, infeasible, unbounded, rampOffset;
+    int frIdentity;      // 1 while the free list is 0,1,..,41 in this order (every warm start until a bound becomes active): products with Q skip the list indirection
     int farRampOffset;   // rampOffset at the last updateFarBounds
     double farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
     double tau;
@@ -182,41 +183,88 @@ WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const i
 WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const double* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:0.0; WBC_SYNC(); }
 
 // ---------------------------------------------------------------- products with Q = [Z Y] (one copy each: instruction cache)
-// out[i] = sgn * sum_j Q(FR[j], col0+i) t[FR[j]],  i < ncols   (t by variable number; lane per column; FR-list order like the reference)
+// out[i] = sgn * sum_j Q(FR[j], col0+i) t[FR[j]],  i < ncols   (t by variable number; lane per column; FR-list order like the reference).
+// A lane owns columns i and i+32 and walks both in the same loop (two independent chains, t loaded once).  While the free list is
+// the identity (c.frIdentity) the list indirection is skipped -- same terms, same order.
 WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const double* t,double sgn,double* out){
     const int lane=c.lane, nFR=c.nFR;
-    LANE_FOR(i,ncols){ const double* q=&w.Q[LD*(col0+i)]; double s=0.0;
+#if WBC_NL==1
+    for(int i=0;i<ncols;i++){ const double* q=&w.Q[LD*(col0+i)]; double s=0.0; for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s+=q[jj]*t[jj]; } out[i]=sgn*s; }
+#else
+    const bool in0=lane<ncols, in1=lane+32<ncols;
+    const double* q0=&w.Q[LD*(col0+(in0?lane:0))]; const double* q1=&w.Q[LD*(col0+(in1?lane+32:0))];
+    double s0=0.0,s1=0.0;
+    if(c.frIdentity){
+        if(ncols>32){
+            #pragma unroll 6
+            for(int j=0;j<42;j++){ const double tj=t[j]; s0+=q0[j]*tj; s1+=q1[j]*tj; }
+        } else {
+            #pragma unroll 6
+            for(int j=0;j<42;j++) s0+=q0[j]*t[j];
+        }
+    } else if(ncols>32){
         #pragma unroll 4
-        for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s+=q[jj]*t[jj]; }
-        out[i]=sgn*s; }
+        for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; const double tj=t[jj]; s0+=q0[jj]*tj; s1+=q1[jj]*tj; }
+    } else {
+        #pragma unroll 4
+        for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s0+=q0[jj]*t[jj]; }
+    }
+    if(in0) out[lane]=sgn*s0;
+    if(in1) out[lane+32]=sgn*s1;
+#endif
     WBC_SYNC();
 }
-// v = sum_j Q(FR[i], col0+j) x[j] for every free variable FR[i]:  acc[FR[i]] += v,  and keep[FR[i]] = v if keep != null   (lane per row)
+// v = sum_j Q(FR[i], col0+j) x[j] for every free variable FR[i]:  acc[FR[i]] += v,  and keep[FR[i]] = v if keep != null   (lane per row,
+// rows i and i+32 of the list in one loop)
 WBC_FN void Q_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const double* x,double* acc,double* keep){
-    const int lane=c.lane;
-    LANE_FOR(i,c.nFR){ const int ii=(int)w.FR[i]; const double* q=&w.Q[ii+LD*col0]; double s=0.0;
+    const int lane=c.lane, nFR=c.nFR;
+#if WBC_NL==1
+    for(int i=0;i<nFR;i++){ const int ii=(int)w.FR[i]; const double* q=&w.Q[ii+LD*col0]; double s=0.0; for(int j=0;j<ncols;j++) s+=q[LD*j]*x[j]; if(keep) keep[ii]=s; acc[ii]+=s; }
+#else
+    const bool in0=lane<nFR, in1=lane+32<nFR;
+    const int i0=in0?(int)w.FR[lane]:0, i1=in1?(int)w.FR[lane+32]:0;
+    const double* q0=&w.Q[i0+LD*col0]; const double* q1=&w.Q[i1+LD*col0];
+    double s0=0.0,s1=0.0;
+    if(nFR>32){
         #pragma unroll 4
-        for(int j=0;j<ncols;j++) s+=q[LD*j]*x[j];
-        if(keep) keep[ii]=s; acc[ii]+=s; }
+        for(int j=0;j<ncols;j++){ const double xj=x[j]; s0+=q0[LD*j]*xj; s1+=q1[LD*j]*xj; }
+    } else {
+        #pragma unroll 4
+        for(int j=0;j<ncols;j++) s0+=q0[LD*j]*x[j];
+    }
+    if(in0){ if(keep) keep[i0]=s0; acc[i0]+=s0; }
+    if(in1){ if(keep) keep[i1]=s1; acc[i1]+=s1; }
+#endif
     WBC_SYNC();
 }
 
 // ---------------------------------------------------------------- index lists (Indexlist.cpp: insertion-ordered number[])
 // removal keeps the order of the remaining entries; every lane holds the same counters, one lane edits the list
 WBC_DEV void list_remove(signed char* L,int& n,int number,int lane){
-    if(lane==0){ int k=0; while(k<n&&L[k]!=number) k++; for(;k<n-1;k++) L[k]=L[k+1]; }
+#if WBC_NL==1
+    { int k=0; while(k<n&&L[k]!=number) k++; for(;k<n-1;k++) L[k]=L[k+1]; }
+#else
+    int k=n;                                                    // position of `number`: ballot over chunks of 32
+    for(int base=0;base<n;base+=32){ const int i=base+lane; const unsigned m=wbc_ballot(i<n&&(int)L[i]==number); if(m){ k=base+wbc_ffs(m); break; } }
+    signed char v[3]; bool mv[3];
+    #pragma unroll
+    for(int u=0;u<3;u++){ const int i=lane+32*u; mv[u]=(i>=k&&i<n-1); v[u]=mv[u]?L[i+1]:(signed char)0; }
+    WBC_SYNC();
+    #pragma unroll
+    for(int u=0;u<3;u++) if(mv[u]) L[lane+32*u]=v[u];
+#endif
     n--; WBC_SYNC();
 }
 WBC_DEV void list_append(signed char* L,int& n,int number,int lane){ if(lane==0) L[n]=(signed char)number; n++; WBC_SYNC(); }
 WBC_DEV void rebuild_posAC(QPWork& w,const QPCtx& c){ const int lane=c.lane; LANE_FOR(k,c.nAC) w.posAC[(int)w.AC[k]]=(signed char)k; WBC_SYNC(); }
 
 // Bounds::moveFreeToFixed / moveFixedToFree, Constraints::moveInactiveToActive / moveActiveToInactive (Bounds.cpp, Constraints.cpp)
-WBC_DEV void moveFreeToFixed(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.FR,c.nFR,number,c.lane); list_append(w.FX,c.nFX,number,c.lane); if(c.lane==0) w.bstat[number]=(signed char)st; WBC_SYNC(); }
-WBC_DEV void moveFixedToFree(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); list_remove(w.FX,c.nFX,number,c.lane); list_append(w.FR,c.nFR,number,c.lane); if(c.lane==0) w.bstat[number]=0; WBC_SYNC(); }
-WBC_DEV void moveInactiveToActive(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.IAC,c.nIAC,number,c.lane); list_append(w.AC,c.nAC,number,c.lane); if(c.lane==0) w.cstat[number]=(signed char)st; WBC_SYNC(); rebuild_posAC(w,c); }
+WBC_DEV void moveFreeToFixed(QPWork& w,QPCtx& c,int number,int st){ c.frIdentity=0; WBC_SYNC(); list_remove(w.FR,c.nFR,number,c.lane); list_append(w.FX,c.nFX,number,c.lane); if(c.lane==0) w.bstat[number]=(signed char)st; WBC_SYNC(); }
+WBC_DEV void moveFixedToFree(QPWork& w,QPCtx& c,int number){ c.frIdentity=0; WBC_SYNC(); list_remove(w.FX,c.nFX,number,c.lane); list_append(w.FR,c.nFR,number,c.lane); if(c.lane==0) w.bstat[number]=0; WBC_SYNC(); }
+WBC_DEV void moveInactiveToActive(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.IAC,c.nIAC,number,c.lane); if(c.lane==0){ w.cstat[number]=(signed char)st; w.posAC[number]=(signed char)c.nAC; } list_append(w.AC,c.nAC,number,c.lane); }
 WBC_DEV void moveActiveToInactive(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); list_remove(w.AC,c.nAC,number,c.lane); list_append(w.IAC,c.nIAC,number,c.lane); if(c.lane==0) w.cstat[number]=0; WBC_SYNC(); rebuild_posAC(w,c); }
 // Indexlist::swapNumbers on the free list (Bounds::swapFree)
-WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ WBC_SYNC(); if(c.lane==0){ int a=0,b=0; while(w.FR[a]!=n1) a++; while(w.FR[b]!=n2) b++; signed char t=w.FR[a]; w.FR[a]=w.FR[b]; w.FR[b]=t; } WBC_SYNC(); }
+WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ c.frIdentity=0; WBC_SYNC(); if(c.lane==0){ int a=0,b=0; while(w.FR[a]!=n1) a++; while(w.FR[b]!=n2) b++; signed char t=w.FR[a]; w.FR[a]=w.FR[b]; w.FR[b]=t; } WBC_SYNC(); }
 
 // ---------------------------------------------------------------- triangular solves
 // Forward substitution L u = b,  u_k = (b[k*bs] - sum_{j<k} L(k,j) u_j) * rd[k*rs],  a[k*as] = u_k, for the four triangular
@@ -659,9 +707,26 @@ WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
 }
 WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
     const int lane=c.lane;
-    LANE_FOR(i,nrows){ int ii=(int)w.FR[i]; double qa=QQ(ii,0);
+#if WBC_NL==1
+    for(int i=0;i<nrows;i++){ int ii=(int)w.FR[i]; double qa=QQ(ii,0);
         for(int j=0;j<nrot;j++){ double qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
         QQ(ii,nrot)=qa; }
+#else
+    const bool in0=lane<nrows, in1=lane+32<nrows;
+    double* r0=&w.Q[in0?(int)w.FR[lane]:0]; double* r1=&w.Q[in1?(int)w.FR[lane+32]:0];
+    if(in1){                                                    // two independent rows per lane: the rotation is loaded once
+        double a0=r0[0], a1=r1[0];
+        #pragma unroll 2
+        for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=r1[LD*(j+1)];
+            r0[LD*j]=-ss*b0+cc*a0; r1[LD*j]=-ss*b1+cc*a1; a0=cc*b0+ss*a0; a1=cc*b1+ss*a1; }
+        r0[LD*nrot]=a0; r1[LD*nrot]=a1;
+    } else if(in0){
+        double a0=r0[0];
+        #pragma unroll 2
+        for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
+        r0[LD*nrot]=a0;
+    }
+#endif
     WBC_SYNC();
 }
 
@@ -796,17 +861,10 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
     return ensureLI_exchange(w,c,number,B_status,true);
 }
 
-// QProblem::addConstraint (QProblem.cpp:2819-2975)
-WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateCholesky,bool ensureLI){
-    const int lane=c.lane;
-    if(updateCholesky&&ensureLI){ int rv=addConstraint_ensureLI(w,c,number,C_status); if(rv!=QP_OK) return rv; }
-    const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+// QProblem::addConstraint (QProblem.cpp:2819-2975), second half: w.wv = aFR' [Z Y] is given; new row of T, Givens chain on Z, index lists
+WBC_FN void addConstraint_tail(QPWork& w,QPCtx& c,int number,int C_status){
+    const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
-    WBC_SYNC();
-    // row [wZ wY] = aFR' [Z Y]
-    LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
-    WBC_SYNC();
-    Qt_times(w,c,0,nFR,w.arow,1.0,w.wv);
     LANE_FOR(j,nAC) TT(nAC,tcol+j)=w.wv[nZ+j];
     WBC_SYNC();
     if(nZ>0){
@@ -815,7 +873,35 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
         if(lane==0) TT(nAC,tcol-1)=(nZ>1)?w.wv[nZ-1]:w.wv[0];
     }
     moveInactiveToActive(w,c,number,C_status);
+}
+WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateCholesky,bool ensureLI){
+    const int lane=c.lane;
+    if(updateCholesky&&ensureLI){ int rv=addConstraint_ensureLI(w,c,number,C_status); if(rv!=QP_OK) return rv; }
+    WBC_SYNC();
+    // row [wZ wY] = aFR' [Z Y]
+    LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
+    WBC_SYNC();
+    Qt_times(w,c,0,c.nFR,w.arow,1.0,w.wv);
+    addConstraint_tail(w,c,number,C_status);
     return QP_OK;
+}
+// setupAuxiliaryWorkingSet step of the warm start (SQProblem.cpp:340-515 -> QProblem.cpp:2212-2378): cheap LI test
+// (addConstraint_checkLI, QProblem.cpp:3081-3105) and addConstraint without LI exchange.  Both need aFR'Z; it is computed once
+// (the first nZ entries of aFR'[Z Y] are the very same sums).
+WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,int number,int C_status){
+    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    WBC_SYNC();
+    LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
+    WBC_SYNC();
+    double l2=0.0;
+    if(c.frIdentity){
+        #pragma unroll 6
+        for(int i=0;i<42;i++){ const double a=w.arow[i]; l2+=a*a; }
+    } else for(int i=0;i<nFR;i++){ const double a=w.arow[(int)w.FR[i]]; l2+=a*a; }
+    Qt_times(w,c,0,nFR,w.arow,1.0,w.wv);
+    bool li=false; LANE_FOR(j,nZ) if(fabs(w.wv[j])>OPT_epsLITests*l2) li=true;
+    if(wbc_ballot(li)==0u) return;
+    addConstraint_tail(w,c,number,C_status);
 }
 // QProblem::addBound (QProblem.cpp:3307-3480)
 WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholesky,bool ensureLI){
@@ -970,7 +1056,7 @@ WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     LANE_FOR(i,42){ w.x[i]=0.0; w.y[i]=0.0; w.g[i]=0.0; w.lb[i]=0.0; w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
     LANE_FOR(i,70){ w.y[42+i]=0.0; w.Ax[i]=0.0; w.lbA[i]=-OPT_boundRelaxation; w.ubA[i]=OPT_boundRelaxation; w.Ax_l[i]=OPT_boundRelaxation; w.Ax_u[i]=OPT_boundRelaxation;
                     w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
-    c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=0.0;
+    c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.frIdentity=0; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=0.0;
     setupTQfactorisation(w,c);
     c.status=QPS_AUXILIARYQPSOLVED;
     performRamping(w,c);
@@ -998,13 +1084,13 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
     LANE_FOR(i,70){ w.IAC[i]=(signed char)i; w.num[i]=(double)w.cstat[i]; }      // park the old statuses in w.num
     WBC_SYNC();
     LANE_FOR(i,70) w.cstat[i]=ST_INACTIVE;
-    c.nFR=42; c.nFX=0; c.nAC=0; c.nIAC=70;
+    c.nFR=42; c.nFX=0; c.nAC=0; c.nIAC=70; c.frIdentity=1;
     setupTQfactorisation(w,c);
     // setupAuxiliaryWorkingSet(old, setupAfresh): re-add the old active constraints in ascending order, cheap LI test, no LI exchange
     for(int i=0;i<70;i++){
         const int os=(int)w.num[i];
         if(os==ST_INACTIVE) continue;
-        if(addConstraint_checkLI(w,c,i,false)){ int rv=addConstraint(w,c,i,os,false,false); if(rv!=QP_OK) return QP_RET_SETUP_AUXILIARYQP_FAILED; }
+        setup_readd_constraint(w,c,i,os);
     }
     int rv=computeProjectedCholesky(w,c);
     if(rv!=QP_OK) return QP_RET_UNSUPPORTED_PATH;

@@ -110,3 +110,19 @@ def shard_range(n_total, rank, world_size):
     count = base + (1 if rank < rem else 0)
     first = rank * base + min(rank, rem)
     return first, count
+
+
+def rollout_start(N, seed=2024, first=0):
+    """config 5: start of a closed-loop rollout -- nominal stance with 20 % of the randomised offsets of `randomised`, references =
+    initial pose, and one constant /cmd_vel per robot: forward 0.1..0.4 m/s, lateral +-0.1 m/s, every 4th robot turning (yaw rate
+    +-0.3 rad/s), every 16th standing.  Keyed by the global robot index like `randomised`, so sharding does not change the data."""
+    st, ref = nominal(N)
+    rs, _ = randomised(N, seed=seed, first=first, contacts="stance")
+    st = {k: st[k] + 0.2 * (rs[k] - st[k]) for k in st}
+    st["base_quat"] /= np.linalg.norm(st["base_quat"], axis=0, keepdims=True)
+    idx = np.arange(first, first + N)
+    u = ((idx * 2654435761) % 1000) / 999.0                     # cheap counter-based uniform in [0,1]
+    v = ((idx * 40503 + 17) % 1000) / 999.0
+    cmd = np.zeros((3, N)); cmd[0] = 0.1 + 0.3 * u; cmd[1] = 0.2 * v - 0.1; cmd[2] = np.where(idx % 4 == 3, 0.6 * u - 0.3, 0.0)
+    cmd[:, idx % 16 == 15] = 0.0
+    return st, ref, cmd
