@@ -29,6 +29,9 @@ WORKLOADS = {
     # name: (robots per GPU, contacts, cold?)
     "cold4096": dict(n=4096, contacts="stance", cold=True, desc="BASELINE configs[1]: 4096 randomised 4-contact ANYmal stance states per GPU, 42-var/70-constraint QP, cold SQProblem::init every step"),
     "warm65536": dict(n=65536, contacts="diagonal", cold=False, desc="BASELINE configs[2]: 65536 diagonal-pair states per GPU, hot-started SQProblem::hotstart ticks"),
+    "rollout16384": dict(n=16384, contacts="stance", cold=False, rollout=100,
+                         desc="BASELINE configs[4]: closed loop of 16384 ANYmal WBC instances per GPU fed by the batched motion planner (crawl gait, /cmd_vel per robot), "
+                              "ideal-actuator plant; one step = 100 consecutive 400 Hz control ticks (25 planner periods) of the running rollout, hot-started solves incl. contact switches"),
 }
 IN_BYTES_PER_ROBOT = (12 + 12 + 3 + 4 + 6 + 6 + 6 + 6 + 12 + 12 + 12) * 8 + 4 + 1      # state + reference + contacts + switching
 OUT_BYTES_PER_ROBOT = (12 + 12) * 8 + 4 + 4                                            # tau, grf, rc, nwsr
@@ -70,10 +73,20 @@ class ClockSampler(threading.Thread):
                     reasons=reasons, samples=len(self.samples))
 
 
-def cpu_reference(n_sample, contacts, cold, threads=0):
+def cpu_reference(n_sample, contacts, cold, threads=0, rollout=0):
     """the reference's CPU path (oracle) on `n_sample` robots of the same workload; returns (solves/s, seconds, cores)"""
     from oracle import oracle as orc
     from quadrupedwholebodycontroller_b200 import workloads as wl
+    if rollout:
+        st, ref, cmd = wl.rollout_start(n_sample)
+        ob = orc.OracleBatch(n_sample); cores = threads or orc.lib().orc_max_threads()
+        ob.set_state(**st); ob.set_reference(**ref)
+        devnull = os.open(os.devnull, os.O_WRONLY); saved = os.dup(2); os.dup2(devnull, 2)
+        try:
+            secs = ob.rollout(rollout, cmd, nthreads=cores, record=False)["seconds"]        # includes the cold first tick (1 of `rollout` ticks)
+        finally:
+            os.dup2(saved, 2); os.close(devnull); os.close(saved)
+        return n_sample * rollout / secs, secs, cores
     st, ref = wl.randomised(n_sample, seed=1234, contacts=contacts)
     ob = orc.OracleBatch(n_sample)
     cores = threads or orc.lib().orc_max_threads()
@@ -92,16 +105,17 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     spec = WORKLOADS[args.workload]
-    n_sample = 512 if spec["cold"] else 4096
+    ro = spec.get("rollout", 0)
+    n_sample = 64 if ro else (512 if spec["cold"] else 4096)
     for _ in range(args.warmup if args.warmup < 2 else 1):
-        cpu_reference(min(64, n_sample), spec["contacts"], spec["cold"])
+        cpu_reference(min(64, n_sample), spec["contacts"], spec["cold"], rollout=min(ro, 8))
     vals, secs = [], []
     for _ in range(args.steps):
-        v, s, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"]); vals.append(v); secs.append(s)
-    value = n_sample * len(secs) / sum(secs)
+        v, s, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro); vals.append(v); secs.append(s)
+    value = n_sample * max(1, ro) * len(secs) / sum(secs)
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * sum(secs) / len(secs),
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic", impl="reference",
-                config=dict(workload=args.workload, description=spec["desc"], robots_per_step=n_sample, l2="n/a (host)"),
+                config=dict(workload=args.workload, description=spec["desc"], robots_per_step=n_sample, ticks_per_step=max(1, ro), l2="n/a (host)"),
                 cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind="port+reference",
                                   sample=f"{n_sample} robots of the {args.workload} workload per step: restated iDynTree/controller algebra (port) + the real vendored qpOASES 3.2.2 (reference), {cores} host threads"),
                 e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
@@ -149,14 +163,32 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    ro = spec.get("rollout", 0)
+    if ro:
+        rst, rref, rcmd = wl.rollout_start(n, first=first)
+        pcmd = [torch.from_numpy(np.ascontiguousarray(rcmd[k])).pin_memory() for k in range(3)]
+        ctl.plannerCreate(); ctl.plantEnable()
+        ctl.setJointAndBaseState(**{k: torch.from_numpy(v).to(dev) for k, v in rst.items()}); ctl.setReference(**{k: torch.from_numpy(v).to(dev) for k, v in rref.items()})
+        ctl.plannerSetCmdVel(*[c.to(dev) for c in pcmd])
+        ctl.rollout(4)                                                 # untimed: the cold tick (SQProblem::init) and the first hot starts
+
     def prepare(host):
         """untimed: L2 flush; for the warm workload also the cold tick that the timed hot start follows"""
+        if ro:
+            flush.fill_(rank + 1); return
         if not spec["cold"]:
             ctl.setInitialState(); ctl.setJointAndBaseState(**(dst)); ctl.setReference(**dref); ctl.step()
         flush.fill_(rank + 1)
 
     def one_step(host):
         """timed: (reset for the cold workload) + inputs + the three hot methods (+ result read-back when host=True)"""
+        if ro:                                                         # `ro` consecutive ticks of the running closed loop, all on the device
+            if host:
+                ctl.plannerSetCmdVel(*pcmd)                            # /cmd_vel from pinned host memory
+            ctl.rollout(ro)
+            if host:
+                ctl.getOutputs(tau=out_host["tau"], grf=out_host["grf"], rc=out_host["rc"], nwsr=out_host["nwsr"])
+            return
         s_in, r_in = ((pst, pref) if spec["cold"] else (pst1, pref)) if host else ((dst, dref) if spec["cold"] else (dst1, dref))
         if spec["cold"]:
             ctl.setInitialState()
@@ -190,8 +222,16 @@ def main():
     ms_e2e, _ = timed(True, args.steps)
     clocks = sampler.summary()
     total_robots = n * world
-    value = total_robots * args.steps / (ms_dev.sum() * 1e-3)
-    e2e = total_robots * args.steps / (ms_e2e.sum() * 1e-3)
+    solves_per_step = total_robots * max(1, ro)
+    value = solves_per_step * args.steps / (ms_dev.sum() * 1e-3)
+    e2e = solves_per_step * args.steps / (ms_e2e.sum() * 1e-3)
+    if ro:                                                             # per-launch kernel times / flop counts: one more step replayed tick by tick
+        kms, fl, nw, it, cy = [], 0.0, 0.0, 0.0, 0.0
+        for _ in range(ro):
+            ctl.rollout(1); kms.append(ctl.lastKernelMs()); pp = ctl.profile(True, fetch=True)
+            fl += float(pp[:, 8].sum()); it += float(pp[:, 7].sum()); cy += float(pp[:, 6].sum())
+        prof = np.zeros((1, 10)); prof[0, 8] = fl / ro; prof[0, 7] = it; prof[0, 6] = cy
+        o = ctl.getOutputs(); st_ro = ctl.rolloutStats()
     qp_ms = float(np.mean([k["solve_qp"] for k in kms])); rbd_ms = float(np.mean([k["update_state"] for k in kms]))
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
@@ -205,7 +245,8 @@ def main():
                 latency_ms=dict(p50=float(np.percentile(ms_dev, 50)), p99=float(np.percentile(ms_dev, 99)), min=float(ms_dev.min()), max=float(ms_dev.max())),
                 e2e=dict(value=e2e, unit=UNIT, h2d_bytes_per_step=IN_BYTES_PER_ROBOT * n, d2h_bytes_per_step=OUT_BYTES_PER_ROBOT * n, ms_per_step=float(ms_e2e.mean())),
                 gpu_launches=int(launches), clocks=clocks,
-                kernels_ms=dict(update_state=rbd_ms, solve_qp=qp_ms, solve_qp_share=qp_ms / float(ms_dev.mean())),
+                kernels_ms=dict(update_state=rbd_ms, solve_qp=qp_ms, solve_qp_share=qp_ms * max(1, ro) / float(ms_dev.mean()),
+                                note="per launch; rollout: mean over the ticks of one extra step replayed tick by tick" if ro else "per launch, mean over the timed steps"),
                 roofline=dict(bound="hbm", achieved=alg_bytes / (qp_ms * 1e-3) / 1e9, peak=hbm_peak, unit="GB/s", frac=alg_bytes / (qp_ms * 1e-3) / 1e9 / hbm_peak,
                               traffic=None, kernel="wbc_solve_qp_kernel", peak_source="MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                               note="solver is FP64-latency / shared-memory bound, not HBM bound: see fp64_roofline and DESIGN.md section 4"),
@@ -213,11 +254,18 @@ def main():
                                    algorithmic_mflop_per_solve=alg_flops / n / 1e6, peak_source="wbc_measure_fp64_peak (DFMA microbenchmark, this run)"),
                 solver=dict(rc0_frac=float((o["rc"] == 0).mean()), rc64_frac=float((o["rc"] == 64).mean()), nwsr_mean=float(o["nwsr"].mean()),
                             cycles_per_iteration=float(prof[:, 6].sum() / max(1, prof[:, 7].sum()))))
+    if ro:
+        tick_ms = np.array([k["update_state"] + k["solve_qp"] + k["compute_joint_torques"] for k in kms])
+        line["tick_latency_ms"] = dict(p50=float(np.percentile(tick_ms, 50)), p99=float(np.percentile(tick_ms, 99)), min=float(tick_ms.min()), max=float(tick_ms.max()),
+                                       note="one control tick of the whole batch (updateState + solveQP + computeJointTorques kernels), replayed step")
+        line["config"]["ticks_per_step"] = ro
+        line["solver"].update(failed_ticks=int(st_ro["failed_ticks"].sum()), nwsr_mean_rollout=float(st_ro["nwsr_sum"].sum() / max(1, st_ro["ticks"].sum())),
+                              nwsr_max_rollout=int(st_ro["nwsr_max"].max()), ticks_run_per_robot=int(st_ro["ticks"].max()))
     if rank == 0 and not args.no_cpu_baseline:
-        n_sample = 2048 if spec["cold"] else 8192
-        v, secs, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"])
+        n_sample = 128 if ro else (2048 if spec["cold"] else 8192)
+        v, secs, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro)
         line["cpu_baseline"] = dict(value=v, unit=UNIT, cores=cores, kind="port+reference", seconds=secs,
-                                    sample=f"{n_sample} robots of the same workload, one pass: restated iDynTree/controller algebra (port) + the real vendored qpOASES 3.2.2 (reference), {cores} host threads")
+                                    sample=f"{n_sample} robots of the same workload, {'%d closed-loop ticks from the cold start' % ro if ro else 'one pass'}: restated iDynTree/controller algebra{' + planner + plant' if ro else ''} (port) + the real vendored qpOASES 3.2.2 (reference), {cores} host threads")
     if rank == 0:
         print(json.dumps(line), flush=True)
     ctl.close()

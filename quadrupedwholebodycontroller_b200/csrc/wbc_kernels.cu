@@ -53,8 +53,9 @@ __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,B
 }
 
 // ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart)
-__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof){
+__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int smStride){
     extern __shared__ double smem[];
+    if(smStride>1){ unsigned smid; asm volatile("mov.u32 %0, %%smid;":"=r"(smid)); if(smid%(unsigned)smStride) return; }      // DEV experiment: leave SMs idle
     QPWork& w=*reinterpret_cast<QPWork*>(smem);
     const int lane=threadIdx.x;
     for(;;){
@@ -191,7 +192,7 @@ struct wbc_handle {
     // planner / plant / rollout
     PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
     double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
-    int smCount=0, qpBlocksPerSM=1; size_t qpSmem=0;
+    int smCount=0, qpBlocksPerSM=1, smStride=1; size_t qpSmem=0;
     long long launches=0;
     std::string err;
 };
@@ -264,6 +265,7 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
         h->err=std::string("occupancy query: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     h->qpBlocksPerSM=nb;
     if(const char* e=getenv("WBC_QP_CTAS_PER_SM")){ int v=atoi(e); if(v>=1&&v<nb) h->qpBlocksPerSM=v; }     // tuning knob: fewer resident solver warps per SM
+    if(const char* e=getenv("WBC_QP_SM_STRIDE")){ int v=atoi(e); if(v>=1) h->smStride=v; }                              // DEV experiment
     for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
     *out=h;
     int rcode=wbc_reset(h,0,n);
@@ -333,7 +335,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     int grid=h->smCount*h->qpBlocksPerSM; if(grid>h->N) grid=h->N;
     CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
     CK(cudaEventRecord(h->ev[1],h->stream));
-    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof);
+    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->smStride);
     h->launches++; CK(cudaGetLastError());
     CK(cudaEventRecord(h->ev[2],h->stream));
     return WBC_OK;

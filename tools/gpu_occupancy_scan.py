@@ -9,7 +9,7 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 st, ref = wl.randomised(N, seed=1234, contacts="stance")
 st1 = wl.advance_state(st)
 KMAX = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-print('library', os.environ.get('WBC_B200_LIB', 'default'), flush=True)
+print('library', os.environ.get('WBC_B200_LIB', 'default'), 'sm stride', os.environ.get('WBC_QP_SM_STRIDE', '1'), flush=True)
 for k in range(1, KMAX + 1):
     os.environ["WBC_QP_CTAS_PER_SM"] = str(k)
     ctl = wbc.WholeBodyController(N)
