@@ -88,6 +88,20 @@ public:
     // the dense QP of one robot exactly as the reference hands it to qpOASES (wbc.cpp:479-515), row-major
     void getDenseQP(int robot, double* H, double* g, double* A, double* lbA, double* ubA) { check(wbc_get_dense_qp(h_, robot, H, g, A, lbA, ubA)); }
 
+    // state inputs as last delivered by the callbacks or integrated by the plant; reference as last stored by referenceCallback
+    void getState(double* q, double* qd, double* basePos, double* baseQuatWXYZ, double* baseTwist) { check(wbc_get_state(h_, q, qd, basePos, baseQuatWXYZ, baseTwist)); }
+    void getReference(double* pose, double* vel, double* acc, double* swPos, double* swVel, double* swAcc, unsigned char* contacts, unsigned char* switching) {
+        check(wbc_get_reference(h_, pose, vel, acc, swPos, swVel, swAcc, contacts, switching, nullptr));
+    }
+    // closed loop on the device (needs a MotionPlanner attached to this controller): plant + `ticks` control ticks, one planner period
+    // every `plannerEvery` ticks (400 Hz loop, wbc.cpp:639-673; 100 Hz planner, motion_planner.cpp:182)
+    void enablePlant() { check(wbc_plant_enable(h_)); }
+    void plantStep() { check(wbc_plant_step(h_)); }
+    void rollout(int ticks, int plannerEvery = 4) { check(wbc_rollout(h_, ticks, plannerEvery)); }
+    void getRolloutStatistics(int* ticks, int* failedTicks, int* nwsrSum, int* nwsrMax, bool reset = false) {
+        check(wbc_rollout_stats(h_, ticks, failedTicks, nwsrSum, nwsrMax, reset ? 1 : 0));
+    }
+
     wbc_handle* handle() { return h_; }
 
 private:
@@ -96,6 +110,29 @@ private:
     }
     wbc_handle* h_ = nullptr;
     int n_ = 0;
+};
+
+// Batched mirror of the reference's MotionPlanner (include/anymal_wbc/motion_planner.hpp:10-52, src/motion_planner.cpp): one planner
+// per robot of a WholeBodyController, living on the same GPU.  plannerLoop() is a blocking loop paced by ros::Rate in the
+// reference; here one call of plannerPeriod() is one period (params.dt) of that loop for the whole batch, and a published
+// message reaches the controller exactly like referenceCallback.
+class MotionPlanner {
+public:
+    struct Params : wbc_planner_params {                   // motion_planner.hpp:40-51; defaults = config/params_planner.yaml
+        Params() { wbc_planner_default_params(this); }
+    };
+    explicit MotionPlanner(WholeBodyController& controller, const Params& params = Params()) : h_(controller.handle()) {
+        if (wbc_planner_create(h_, &params) != WBC_OK) throw std::runtime_error(std::string("MotionPlanner: ") + wbc_last_error(h_));
+    }
+    // input_callback (motion_planner.cpp:122-127): linear.x, linear.y, angular.z of /cmd_vel, arrays of nRobots (host or device), nullptr keeps
+    void input_callback(const double* linearX, const double* linearY, const double* angularZ) { check(wbc_planner_set_cmd_vel(h_, linearX, linearY, angularZ)); }
+    void plannerPeriod() { check(wbc_planner_tick(h_)); }   // one pass of the pacing of plannerLoop (motion_planner.cpp:180-376)
+    void reset() { check(wbc_planner_reset(h_, 0, wbc_num_robots(h_))); }
+    void getPublished(unsigned char* published) { check(wbc_get_reference(h_, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, published)); }
+
+private:
+    void check(int rc) const { if (rc != WBC_OK) throw std::runtime_error(std::string("MotionPlanner: ") + wbc_last_error(h_) + " (code " + std::to_string(rc) + ")"); }
+    wbc_handle* h_;
 };
 
 }  // namespace anymal_wbc_b200
