@@ -368,8 +368,13 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
         // packed column j lives at RT[TRI42-1-tri(j) - k]: walk k = i-1 .. 0 with three pointers
         const double* pi=&RR(i,i); const double* p0=&RR(i,in0?j0:i); const double* p1=&RR(i,in1?j1:i);
         double s0=in0?*p0:0.0, s1=in1?*p1:0.0;
-        #pragma unroll 2
-        for(int k=1;k<=i;k++){ const double rki=pi[k]; s0-=rki*p0[k]; s1-=rki*p1[k]; }     // RR(i-k,.) = p[k]
+        if(n>32){
+            #pragma unroll 2
+            for(int k=1;k<=i;k++){ const double rki=pi[k]; s0-=rki*p0[k]; s1-=rki*p1[k]; } // RR(i-k,.) = p[k]
+        } else {
+            #pragma unroll 2
+            for(int k=1;k<=i;k++) s0-=pi[k]*p0[k];
+        }
         const double sum=wbc_bcast(s0,0);
         if(!(sum>0.0)) return false;
         const double d=sqrt(sum), rd=1.0/d;
@@ -693,7 +698,7 @@ WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
     const int lane=c.lane; WBC_SYNC();
     double tlast=w.wv[0];
     LANE_FOR(j,nrot){
-        double P=0.0; for(int k=0;k<=j;k++) P+=w.wv[k]*w.wv[k];
+        double P=0.0; for(int k=0;k<=j;k++) P+=w.wv[k]*w.wv[k];      // sequential on purpose: a warp scan re-associates the sum and moved one degenerate working set
         const double xold=w.wv[j+1];
         const double yold=(j==0)?w.wv[0]:((w.wv[j]<0.0)?-sqrt(P):sqrt(P));
         double cc,ss,t;
@@ -714,12 +719,12 @@ WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
 #else
     const bool in0=lane<nrows, in1=lane+32<nrows;
     double* r0=&w.Q[in0?(int)w.FR[lane]:0]; double* r1=&w.Q[in1?(int)w.FR[lane+32]:0];
-    if(in1){                                                    // two independent rows per lane: the rotation is loaded once
-        double a0=r0[0], a1=r1[0];
+    if(nrows>32){                                               // (uniform) two independent rows per lane: the rotation is loaded once;
+        double a0=r0[0], a1=in1?r1[0]:0.0;                      // lanes without a second row run the same code with its loads/stores predicated off
         #pragma unroll 2
-        for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=r1[LD*(j+1)];
-            r0[LD*j]=-ss*b0+cc*a0; r1[LD*j]=-ss*b1+cc*a1; a0=cc*b0+ss*a0; a1=cc*b1+ss*a1; }
-        r0[LD*nrot]=a0; r1[LD*nrot]=a1;
+        for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=in1?r1[LD*(j+1)]:0.0;
+            r0[LD*j]=-ss*b0+cc*a0; if(in1) r1[LD*j]=-ss*b1+cc*a1; a0=cc*b0+ss*a0; a1=cc*b1+ss*a1; }
+        r0[LD*nrot]=a0; if(in1) r1[LD*nrot]=a1;
     } else if(in0){
         double a0=r0[0];
         #pragma unroll 2
