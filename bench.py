@@ -29,6 +29,9 @@ WORKLOADS = {
     # name: (robots per GPU, contacts, cold?)
     "cold4096": dict(n=4096, contacts="stance", cold=True, desc="BASELINE configs[1]: 4096 randomised 4-contact ANYmal stance states per GPU, 42-var/70-constraint QP, cold SQProblem::init every step"),
     "warm65536": dict(n=65536, contacts="diagonal", cold=False, desc="BASELINE configs[2]: 65536 diagonal-pair states per GPU, hot-started SQProblem::hotstart ticks"),
+    "mixed1m": dict(n=1 << 20, contacts="mixed", cold=True, strong=True, switching_frac=0.1,
+                    desc="BASELINE configs[3]: 2^20 randomised states in total, contacts 1111 / single swing / diagonal pairs (50/40/10 %), switching flag on 10 %, cold SQProblem::init, "
+                         "sharded by robot index over the GPUs (strong scaling)"),
     "rollout16384": dict(n=16384, contacts="stance", cold=False, rollout=100,
                          desc="BASELINE configs[4]: closed loop of 16384 ANYmal WBC instances per GPU fed by the batched motion planner (crawl gait, /cmd_vel per robot), "
                               "ideal-actuator plant; one step = 100 consecutive 400 Hz control ticks (25 planner periods) of the running rollout, hot-started solves incl. contact switches"),
@@ -73,7 +76,7 @@ class ClockSampler(threading.Thread):
                     reasons=reasons, samples=len(self.samples))
 
 
-def cpu_reference(n_sample, contacts, cold, threads=0, rollout=0):
+def cpu_reference(n_sample, contacts, cold, threads=0, rollout=0, switching_frac=0.0):
     """the reference's CPU path (oracle) on `n_sample` robots of the same workload; returns (solves/s, seconds, cores)"""
     from oracle import oracle as orc
     from quadrupedwholebodycontroller_b200 import workloads as wl
@@ -87,7 +90,7 @@ def cpu_reference(n_sample, contacts, cold, threads=0, rollout=0):
         finally:
             os.dup2(saved, 2); os.close(devnull); os.close(saved)
         return n_sample * rollout / secs, secs, cores
-    st, ref = wl.randomised(n_sample, seed=1234, contacts=contacts)
+    st, ref = wl.randomised(n_sample, seed=1234, contacts=contacts, switching_frac=switching_frac)
     ob = orc.OracleBatch(n_sample)
     cores = threads or orc.lib().orc_max_threads()
     ob.set_state(**st); ob.set_reference(**ref)
@@ -111,7 +114,7 @@ def run_reference(args, rank, world):
         cpu_reference(min(64, n_sample), spec["contacts"], spec["cold"], rollout=min(ro, 8))
     vals, secs = [], []
     for _ in range(args.steps):
-        v, s, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro); vals.append(v); secs.append(s)
+        v, s, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro, switching_frac=spec.get("switching_frac", 0.0)); vals.append(v); secs.append(s)
     value = n_sample * max(1, ro) * len(secs) / sum(secs)
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * sum(secs) / len(secs),
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic", impl="reference",
@@ -145,8 +148,11 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     spec = WORKLOADS[args.workload]
     n = args.robots or spec["n"]
-    first = rank * n                                                   # weak scaling: contiguous shard [rank*n, (rank+1)*n) of the global batch
-    st, ref = wl.randomised(n, seed=1234, first=first, contacts=spec["contacts"])
+    if spec.get("strong"):
+        first, n = wl.shard_range(n, rank, world)                      # strong scaling: the global batch is split over the ranks
+    else:
+        first = rank * n                                               # weak scaling: contiguous shard [rank*n, (rank+1)*n) of the global batch
+    st, ref = wl.randomised(n, seed=1234, first=first, contacts=spec["contacts"], switching_frac=spec.get("switching_frac", 0.0))
     stream = torch.cuda.Stream(device=dev)                          # a real (non-NULL) stream shared by torch's events and the library
     torch.cuda.set_stream(stream)
     ctl = wbc.WholeBodyController(n, device=local, stream=stream.cuda_stream)
@@ -221,7 +227,7 @@ def main():
     o = ctl.getOutputs()
     ms_e2e, _ = timed(True, args.steps)
     clocks = sampler.summary()
-    total_robots = n * world
+    total_robots = (args.robots or spec["n"]) if spec.get("strong") else n * world
     solves_per_step = total_robots * max(1, ro)
     value = solves_per_step * args.steps / (ms_dev.sum() * 1e-3)
     e2e = solves_per_step * args.steps / (ms_e2e.sum() * 1e-3)
@@ -239,7 +245,7 @@ def main():
     fp64_peak = ctl.measureFp64Peak()
     alg_flops = float(prof[:, 8].sum())
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=float(ms_dev.mean()),
-                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+                higher_is_better=True, scaling="strong" if spec.get("strong") else "weak", vs_baseline=None, dtype="f64", data="synthetic",
                 config=dict(workload=args.workload, description=spec["desc"], robots_per_gpu=n, robots_total=total_robots, parallelism=f"instance-sharded x{world}",
                             l2="flushed between timed steps (256 MiB write)", peaks="measured (MEASURED_PEAKS.json)" if peaks else "fallback"),
                 latency_ms=dict(p50=float(np.percentile(ms_dev, 50)), p99=float(np.percentile(ms_dev, 99)), min=float(ms_dev.min()), max=float(ms_dev.max())),
@@ -263,7 +269,7 @@ def main():
                               nwsr_max_rollout=int(st_ro["nwsr_max"].max()), ticks_run_per_robot=int(st_ro["ticks"].max()))
     if rank == 0 and not args.no_cpu_baseline:
         n_sample = 128 if ro else (2048 if spec["cold"] else 8192)
-        v, secs, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro)
+        v, secs, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro, switching_frac=spec.get("switching_frac", 0.0))
         line["cpu_baseline"] = dict(value=v, unit=UNIT, cores=cores, kind="port+reference", seconds=secs,
                                     sample=f"{n_sample} robots of the same workload, {'%d closed-loop ticks from the cold start' % ro if ro else 'one pass'}: restated iDynTree/controller algebra{' + planner + plant' if ro else ''} (port) + the real vendored qpOASES 3.2.2 (reference), {cores} host threads")
     if rank == 0:
