@@ -28,3 +28,34 @@ def test_layout_is_structure_of_arrays(wl):
     assert np.allclose(np.linalg.norm(st["base_quat"], axis=0), 1.0)
     s2 = wl.advance_state(st)
     assert np.allclose(s2["q"], st["q"] + st["qd"] / 400.0) and np.allclose(np.linalg.norm(s2["base_quat"], axis=0), 1.0)
+
+
+def test_rollout_start_is_sharding_invariant(wl):
+    """config 5 inputs are keyed by the global robot index: any contiguous shard reproduces the same robots"""
+    st, ref, cmd = wl.rollout_start(64)
+    for rank in range(3):
+        first, count = wl.shard_range(64, rank, 3)
+        s2, r2, c2 = wl.rollout_start(count, first=first)
+        for k in st:
+            assert np.array_equal(s2[k], st[k][:, first:first + count]), k
+        assert np.array_equal(c2, cmd[:, first:first + count])
+    assert np.allclose(np.linalg.norm(st["base_quat"], axis=0), 1.0)
+    assert (cmd[:, 15] == 0).all() and (cmd[0, :15] >= 0.1).all() and np.abs(cmd[2]).max() <= 0.3 + 1e-12
+
+
+def test_oracle_closed_loop_is_stable(orc, wl):
+    """the oracle's closed loop (restated planner + controller + real qpOASES + dense plant) walks for one second without a failed solve"""
+    import os
+    N = 4
+    st, ref, cmd = wl.rollout_start(N)
+    ob = orc.OracleBatch(N); ob.set_state(**st); ob.set_reference(**ref)
+    fd = os.open(os.devnull, os.O_WRONLY); saved = os.dup(2); os.dup2(fd, 2)
+    try:
+        r = ob.rollout(400, cmd)
+    finally:
+        os.dup2(saved, 2); os.close(fd); os.close(saved)
+    assert (r["rc"] == 0).all()
+    assert r["nwsr"][0].min() > 40 and np.median(r["nwsr"][1:]) <= 2
+    z = r["pos"][:, 2, :]
+    assert (z > 0.4).all() and (z < 0.7).all()
+    assert np.abs(r["tau"]).max() <= 80.0 + 1e-9
