@@ -17,6 +17,11 @@
   #define WBC_FN  __device__ __noinline__
   #define WBC_NL 32
   #define WBC_SYNC() __syncwarp()
+  // explicit shared-space loads with a 32-bit address held in a register: through C++ pointers ptxas re-derives the shared window
+  // base (S2R SR_CgaCtaId + MOV + LEA) at every predicated access inside the noinline routines.  READ-ONLY data of the calling routine only
+  // (the asm is not volatile and has no memory clobber, so the compiler may move or merge these loads).
+  WBC_DEV unsigned wbc_saddr(const void* p){ unsigned a=(unsigned)__cvta_generic_to_shared(p); asm volatile("" : "+r"(a)); return a; }   // opaque: stays in a register
+  WBC_DEV double wbc_lds(unsigned a){ double v; asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
   WBC_DEV unsigned wbc_ballot(bool p){ return __ballot_sync(0xffffffffu,p); }
   WBC_DEV double wbc_max(double v){ for(int o=16;o>0;o>>=1){ double t=__shfl_xor_sync(0xffffffffu,v,o); v = t>v?t:v; } return v; }
   WBC_DEV double wbc_bcast(double v,int src){ return __shfl_sync(0xffffffffu,v,src); }

@@ -289,31 +289,36 @@ WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,in
     for(int k=0;k<n;k++) a[k*as]=u[k];
 #else
     const bool in0=lane<n, in1=lane+32<n;
+    const unsigned L=wbc_saddr(RT);                           // 32-bit shared address of the packed R/T buffer (read-only here)
     int o0=in0?trisolve_row0(kind,n,lane):0, d=d0;
-    double s0=in0?b[lane*bs]:0.0, r0=in0?rd[lane*rs]:0.0, l0=(in0&&lane>0)?RT[o0]:0.0;
+    double s0=in0?b[lane*bs]:0.0, r0=in0?rd[lane*rs]:0.0, l0=(in0&&lane>0)?wbc_lds(L+8u*o0):0.0;
     WBC_SYNC();                                              // a may alias b
+    // l0 is loaded as 0 for lanes <= k, so the update needs no predicate and a finished lane keeps its final sum: u_k = s0*r0 is
+    // formed for the broadcast at step k and once more, from the same operands, for the store after the loop.
     if(n<=32){
+        #pragma unroll 2
         for(int k=0;k<n;k++){
             const double ak=__shfl_sync(0xffffffffu,s0*r0,k);
             o0+=d; d+=dd;
-            const double nl=(lane>k+1&&in0)?RT[o0]:0.0;      // next column's entry, independent of the chain
-            if(lane==k) a[k*as]=ak;
-            if(lane>k) s0-=l0*ak;
+            const double nl=(lane>k+1&&in0)?wbc_lds(L+8u*o0):0.0;   // next column's entry, independent of the chain
+            s0=fma(-l0,ak,s0);
             l0=nl;
         }
+        if(in0) a[lane*as]=s0*r0;
     } else {
         int o1=in1?trisolve_row0(kind,n,lane+32):0;
-        double s1=in1?b[(lane+32)*bs]:0.0, r1=in1?rd[(lane+32)*rs]:0.0, l1=in1?RT[o1]:0.0;
+        double s1=in1?b[(lane+32)*bs]:0.0, r1=in1?rd[(lane+32)*rs]:0.0, l1=in1?wbc_lds(L+8u*o1):0.0;
+        #pragma unroll 2
         for(int k=0;k<n;k++){
             const double mine=(k<32)?s0*r0:s1*r1;
             const double ak=__shfl_sync(0xffffffffu,mine,k&31);
             o0+=d; o1+=d; d+=dd;
-            const double nl0=(lane>k+1&&in0)?RT[o0]:0.0, nl1=(lane+32>k+1&&in1)?RT[o1]:0.0;
-            if(lane==(k&31)) a[k*as]=ak;
-            if(lane>k) s0-=l0*ak;
-            if(lane+32>k&&in1) s1-=l1*ak;
+            const double nl0=(lane>k+1&&in0)?wbc_lds(L+8u*o0):0.0, nl1=(lane+32>k+1&&in1)?wbc_lds(L+8u*o1):0.0;
+            s0=fma(-l0,ak,s0); s1=fma(-l1,ak,s1);
             l0=nl0; l1=nl1;
         }
+        a[lane*as]=s0*r0;
+        if(in1) a[(lane+32)*as]=s1*r1;
     }
 #endif
     WBC_SYNC();
