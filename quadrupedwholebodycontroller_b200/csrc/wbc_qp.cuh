@@ -354,8 +354,8 @@ WBC_DEV void setupTQfactorisation(QPWork& w,const QPCtx& c){
     LANE_FOR(i,c.nFR) QQ((int)w.FR[i],i)=1.0;
     WBC_SYNC();
 }
-// DPOTRF "U" of LAPACKReplacement.cpp:39-77 on the leading n x n block of R.  Row i: lane t owns column i+t (+32); its
-// inner product runs k = i-1 .. 0 like the reference; lane 0 holds the diagonal's sum, which travels by one shuffle.
+// DPOTRF "U" of LAPACKReplacement.cpp:39-77 on the leading n x n block of R.  Row i: the lane that owns column j forms R(i,j); its
+// inner product runs k = i-1 .. 0 like the reference; the diagonal's sum travels by one shuffle from the lane that owns column i.
 // returns false if not SPD.
 WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
     const int lane=c.lane;
@@ -368,24 +368,29 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
         for(int j=i+1;j<n;j++){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=s2*rd; }
     }
 #else
+    // lane t owns columns t and t+32 for the whole factorisation (fixed pointers, no per-row index arithmetic); packed column j lives
+    // at RT[TRI42-1-tri(j) - row].  At row i the lanes left of the diagonal run the same loop on in-bounds data and discard the result.
+    const bool own0=lane<n, own1=lane+32<n;
+    double* c0=&w.RT[TRI42-1-tri(own0?lane:0)];                // &RR(0,lane)
+    double* c1=&w.RT[TRI42-1-tri(own1?lane+32:0)];
+    const double* ci=&w.RT[TRI42-1];                           // &RR(0,i)
     for(int i=0;i<n;i++){
-        const int j0=i+lane, j1=j0+32; const bool in0=j0<n, in1=j1<n;
-        // packed column j lives at RT[TRI42-1-tri(j) - k]: walk k = i-1 .. 0 with three pointers
-        const double* pi=&RR(i,i); const double* p0=&RR(i,in0?j0:i); const double* p1=&RR(i,in1?j1:i);
-        double s0=in0?*p0:0.0, s1=in1?*p1:0.0;
+        double s0=c0[-i], s1=0.0;
         if(n>32){
+            s1=c1[-i];
             #pragma unroll 2
-            for(int k=1;k<=i;k++){ const double rki=pi[k]; s0-=rki*p0[k]; s1-=rki*p1[k]; } // RR(i-k,.) = p[k]
+            for(int r=i-1;r>=0;r--){ const double rki=ci[-r]; s0-=rki*c0[-r]; s1-=rki*c1[-r]; }
         } else {
             #pragma unroll 2
-            for(int k=1;k<=i;k++) s0-=pi[k]*p0[k];
+            for(int r=i-1;r>=0;r--) s0-=ci[-r]*c0[-r];
         }
-        const double sum=wbc_bcast(s0,0);
+        const double sum=wbc_bcast((i<32)?s0:s1,i&31);
         if(!(sum>0.0)) return false;
         const double d=sqrt(sum), rd=1.0/d;
-        if(lane==0){ RR(i,i)=d; w.rdR[i]=rd; }
-        else if(in0) RR(i,j0)=s0*rd;
-        if(in1) RR(i,j1)=s1*rd;
+        if(lane==(i&31)){ if(i<32) c0[-i]=d; else c1[-i]=d; w.rdR[i]=rd; }
+        if(own0&&lane>i) c0[-i]=s0*rd;
+        if(own1&&lane+32>i) c1[-i]=s1*rd;
+        ci-=i+1;                                                // tri(i+1)-tri(i)
         WBC_SYNC();
     }
 #endif
@@ -448,12 +453,12 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
         // Z'HZ (SymDenseMat::bilinear, Matrices.cpp:630-667).  H = diag except the 12x12 force block, so
         // (HZ)(v,k) = H_vv Z(v,k) for v outside the block; inside, the sum runs over the free force variables in list order
         // (w.rdT = that sub-list, built with ballots; prepare_T rewrites rdT before its next use).  Hff is bitwise symmetric, read as Hff[u][a] for unit stride in a.
-        int nff=0;
+        int nff=0; int* ffl=reinterpret_cast<int*>(w.rdT);      // <= 12 ints in the (currently dead) rdT buffer
         for(int base=0;base<nFR;base+=WBC_NL){ const int i=base+lane; const int v=(i<nFR)?(int)w.FR[i]:0; const bool isf=(i<nFR)&&v>=18&&v<30;
-            const unsigned m=wbc_ballot(isf); if(isf) w.rdT[nff+wbc_rank(m,lane)]=(double)(v-18); nff+=wbc_popc(m); }
+            const unsigned m=wbc_ballot(isf); if(isf) ffl[nff+wbc_rank(m,lane)]=v-18; nff+=wbc_popc(m); }
         WBC_SYNC();
         LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; double s=0;
-            for(int i=0;i<nff;i++){ const int u=(int)w.rdT[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
+            for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
             w.HZf[a*LD+k]=s; }
         WBC_SYNC();
         zhz_tiles(w,c,nFR,nZ);
