@@ -727,15 +727,27 @@ WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
         for(int j=0;j<nrot;j++){ double qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
         QQ(ii,nrot)=qa; }
 #else
-    const bool in0=lane<nrows, in1=lane+32<nrows;
-    double* r0=&w.Q[in0?(int)w.FR[lane]:0]; double* r1=&w.Q[in1?(int)w.FR[lane+32]:0];
-    if(nrows>32){                                               // (uniform) two independent rows per lane: the rotation is loaded once;
-        double a0=r0[0], a1=in1?r1[0]:0.0;                      // lanes without a second row run the same code with its loads/stores predicated off
-        #pragma unroll 2
-        for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=in1?r1[LD*(j+1)]:0.0;
-            r0[LD*j]=-ss*b0+cc*a0; if(in1) r1[LD*j]=-ss*b1+cc*a1; a0=cc*b0+ss*a0; a1=cc*b1+ss*a1; }
-        r0[LD*nrot]=a0; if(in1) r1[LD*nrot]=a1;
-    } else if(in0){
+    if(nrows>32){
+        // more rows than lanes: lane l < ceil(nrows/2) sweeps rows l and l+half together (two independent chains, the rotation is
+        // loaded once, no predicates in the loop); the other lanes have nothing to do
+        const int half=(nrows+1)>>1;
+        if(lane<half){
+            const bool two=lane+half<nrows;
+            double* r0=&w.Q[(int)w.FR[lane]]; double* r1=&w.Q[(int)w.FR[two?lane+half:lane]];
+            if(two){
+                double a0=r0[0], a1=r1[0];
+                #pragma unroll 2
+                for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=r1[LD*(j+1)];
+                    r0[LD*j]=-ss*b0+cc*a0; r1[LD*j]=-ss*b1+cc*a1; a0=cc*b0+ss*a0; a1=cc*b1+ss*a1; }
+                r0[LD*nrot]=a0; r1[LD*nrot]=a1;
+            } else {                                             // odd row count: the last lane of the first half has one row
+                double a0=r0[0];
+                for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
+                r0[LD*nrot]=a0;
+            }
+        }
+    } else if(lane<nrows){
+        double* r0=&w.Q[(int)w.FR[lane]];
         double a0=r0[0];
         #pragma unroll 2
         for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
