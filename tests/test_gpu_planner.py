@@ -146,3 +146,33 @@ def test_plant_step_matches_oracle_from_random_states(wbc, orc, wl):
         Tprev = Told
     for k in ("q", "qd", "base_pos", "base_quat", "base_twist"):
         assert rel(got[k], cur[k]) < 1e-9, k
+
+
+def test_full_size_rollout_properties(wbc, wl):
+    """BASELINE configs[4] size (16384 robots), 120 control ticks incl. the first contact switches: no oracle at this size, only what the
+    domain guarantees -- every QP solves, torque limits and friction pyramids hold for stance legs, the base stays up, hot starts stay cheap,
+    and the run is deterministic whatever order the work queue handed the robots out in."""
+    n, T = 16384, 120
+    st, ref, cmd = wl.rollout_start(n)
+
+    def run():
+        ctl = wbc.WholeBodyController(n); ctl.plannerCreate(); ctl.plantEnable()
+        ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.plannerSetCmdVel(cmd[0].copy(), cmd[1].copy(), cmd[2].copy())
+        ctl.rollout(T)
+        o, s, r, stats = ctl.getOutputs(), ctl.getState(), ctl.getReference(), ctl.rolloutStats()
+        ctl.close()
+        return o, s, r, stats
+    o, s, r, stats = run()
+    assert (stats["ticks"] == T).all() and stats["failed_ticks"].sum() == 0
+    assert (np.abs(o["tau"]) <= 80.0 * (1 + 1e-9)).all()
+    f = o["grf"].reshape(4, 3, n); c = r["contacts"].astype(bool)
+    tol = 1e-7 * np.maximum(1.0, np.abs(f).max(axis=(0, 1)))
+    assert ((np.abs(f[:, 0]) <= f[:, 2] + tol) | ~c).all() and ((np.abs(f[:, 1]) <= f[:, 2] + tol) | ~c).all()
+    assert (np.abs(f[~c]) <= 1e-6).all()                                  # swing legs carry no force (their H block + zero A columns)
+    assert (s["base_pos"][2] > 0.4).all() and (s["base_pos"][2] < 0.7).all()
+    assert np.allclose(np.linalg.norm(s["base_quat"], axis=0), 1.0, atol=1e-12)
+    assert stats["nwsr_sum"].sum() / stats["ticks"].sum() < 6.0 and (stats["nwsr_max"] >= 40).all()
+    walking = np.abs(cmd).sum(axis=0) > 0
+    assert ((r["contacts"].sum(axis=0) == 3) == walking).all()            # tick 120 = planner period 30: second step phase of the crawl
+    o2, s2, _, _ = run()
+    assert all(np.array_equal(o[k], o2[k]) for k in o) and all(np.array_equal(s[k], s2[k]) for k in s)
