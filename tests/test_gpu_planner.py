@@ -168,7 +168,7 @@ def test_full_size_rollout_properties(wbc, wl):
     f = o["grf"].reshape(4, 3, n); c = r["contacts"].astype(bool)
     tol = 1e-7 * np.maximum(1.0, np.abs(f).max(axis=(0, 1)))
     assert ((np.abs(f[:, 0]) <= f[:, 2] + tol) | ~c).all() and ((np.abs(f[:, 1]) <= f[:, 2] + tol) | ~c).all()
-    assert (np.abs(f[~c]) <= 1e-6).all()                                  # swing legs carry no force (their H block + zero A columns)
+    assert (np.abs(f.transpose(0, 2, 1)[~c]) <= 1e-6).all()               # swing legs carry no force (their H block + zero A columns)
     assert (s["base_pos"][2] > 0.4).all() and (s["base_pos"][2] < 0.7).all()
     assert np.allclose(np.linalg.norm(s["base_quat"], axis=0), 1.0, atol=1e-12)
     assert stats["nwsr_sum"].sum() / stats["ticks"].sum() < 6.0 and (stats["nwsr_max"] >= 40).all()
