@@ -119,7 +119,7 @@ def run_reference(args, rank, world):
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * sum(secs) / len(secs),
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic", impl="reference",
                 config=dict(workload=args.workload, description=spec["desc"], robots_per_step=n_sample, ticks_per_step=max(1, ro), l2="n/a (host)"),
-                cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind="port+reference",
+                cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind="port", reference_parts="qpOASES 3.2.2 solver: the real, unmodified vendored library (oracle/_ref); iDynTree subset, controller algebra, planner, plant: restated",
                                   sample=f"{n_sample} robots of the {args.workload} workload per step: restated iDynTree/controller algebra (port) + the real vendored qpOASES 3.2.2 (reference), {cores} host threads"),
                 e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line), flush=True)
@@ -242,6 +242,8 @@ def main():
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     alg_bytes = n * (QPDATA_B + (QPSTATE_B if spec["cold"] else 2 * QPSTATE_B) + XWS_B)
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE solver launch from an `ncu --set full` capture of exactly this launch shape (profiles/): only for 4096 robots
+    traffic = {True: 23.7e6 + 0.015e6, False: 36.5e6 + 0.07e6}[bool(spec["cold"])] if (n == 4096 and not ro) else None
     fp64_peak = ctl.measureFp64Peak()
     alg_flops = float(prof[:, 8].sum())
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=float(ms_dev.mean()),
@@ -254,7 +256,7 @@ def main():
                 kernels_ms=dict(update_state=rbd_ms, solve_qp=qp_ms, solve_qp_share=qp_ms * max(1, ro) / float(ms_dev.mean()),
                                 note="per launch; rollout: mean over the ticks of one extra step replayed tick by tick" if ro else "per launch, mean over the timed steps"),
                 roofline=dict(bound="hbm", achieved=alg_bytes / (qp_ms * 1e-3) / 1e9, peak=hbm_peak, unit="GB/s", frac=alg_bytes / (qp_ms * 1e-3) / 1e9 / hbm_peak,
-                              traffic=None, kernel="wbc_solve_qp_kernel", peak_source="MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                              traffic=traffic, traffic_source="profiles/r01a_ncu_summary.md (cold launch) / profiles/r01f_ncu_summary.md (hot-started launch), 4096 robots" if traffic else None, kernel="wbc_solve_qp_kernel", peak_source="MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                               note="solver is FP64-latency / shared-memory bound, not HBM bound: see fp64_roofline and DESIGN.md section 4"),
                 fp64_roofline=dict(achieved=alg_flops / (qp_ms * 1e-3) / 1e9, peak=fp64_peak, unit="GFLOP/s", frac=alg_flops / (qp_ms * 1e-3) / 1e9 / fp64_peak,
                                    algorithmic_mflop_per_solve=alg_flops / n / 1e6, peak_source="wbc_measure_fp64_peak (DFMA microbenchmark, this run)"),
@@ -270,7 +272,7 @@ def main():
     if rank == 0 and not args.no_cpu_baseline:
         n_sample = 128 if ro else (2048 if spec["cold"] else 8192)
         v, secs, cores = cpu_reference(n_sample, spec["contacts"], spec["cold"], rollout=ro, switching_frac=spec.get("switching_frac", 0.0))
-        line["cpu_baseline"] = dict(value=v, unit=UNIT, cores=cores, kind="port+reference", seconds=secs,
+        line["cpu_baseline"] = dict(value=v, unit=UNIT, cores=cores, kind="port", reference_parts="qpOASES 3.2.2 solver: the real, unmodified vendored library (oracle/_ref); iDynTree subset, controller algebra, planner, plant: restated", seconds=secs,
                                     sample=f"{n_sample} robots of the same workload, {'%d closed-loop ticks from the cold start' % ro if ro else 'one pass'}: restated iDynTree/controller algebra{' + planner + plant' if ro else ''} (port) + the real vendored qpOASES 3.2.2 (reference), {cores} host threads")
     if rank == 0:
         print(json.dumps(line), flush=True)

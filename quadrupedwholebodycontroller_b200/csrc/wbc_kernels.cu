@@ -23,11 +23,14 @@ struct BatchIn {      // SoA, instance index fastest
 };
 struct BatchOut { double *tau,*grf,*x,*com; int *rc,*nwsr; signed char* ws; };
 
+#ifndef WBC_UPD_MINBLOCKS
+#define WBC_UPD_MINBLOCKS 8          // resident CTAs per SM the register allocation of kernel 1 is sized for
+#endif
 __constant__ ModelConst c_model;
 
 // ---------------------------------------------------------------- kernel 1: RBD + centroidal transform + QP assembly
 // grid-stride over instances; the RBD stage is ~40 kFLOP per robot, far below the solver's cost
-__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,double* com,double* plantAux){
+__global__ void __launch_bounds__(32,WBC_UPD_MINBLOCKS) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,double* com,double* plantAux){
     __shared__ ModelConst mc;
     __shared__ RbdScratch s;
     __shared__ QPData qp;
