@@ -936,6 +936,9 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
     if(updateCholesky&&ensureLI){ int rv=addBound_ensureLI(w,c,number,B_status); if(rv!=QP_OK) return rv; }
     const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
+#if !defined(__CUDACC__) && defined(WBC_QP_TRACE)
+    printf("    addBound %2d  nFR %2d nAC %2d\n",number,nFR,nAC);
+#endif
     WBC_SYNC();
     const int lastfree=(int)w.FR[nFR-1];
     if(lastfree!=number) swapFree(w,c,number,lastfree);
