@@ -126,3 +126,41 @@ def rollout_start(N, seed=2024, first=0):
     cmd = np.zeros((3, N)); cmd[0] = 0.1 + 0.3 * u; cmd[1] = 0.2 * v - 0.1; cmd[2] = np.where(idx % 4 == 3, 0.6 * u - 0.3, 0.0)
     cmd[:, idx % 16 == 15] = 0.0
     return st, ref, cmd
+
+
+STRESS_KINDS = ("flight", "one_foot", "saturating", "fast", "tilted", "far_swing", "two_feet_same_side", "crouched")
+
+
+def stress(N, seed=77, first=0):
+    """Edge cases of the path, one kind per robot (kind = global index mod 8), on top of `randomised`:
+    0 flight (contacts 0000: no stance rows, all four friction blocks vanish), 1 a single stance foot, 2 desired CoM accelerations of
+    +-30 m/s^2 / +-60 rad/s^2 (torque limits and friction pyramids saturate), 3 joint rates +-6 rad/s and base twist +-2, 4 base roll /
+    pitch +-0.6 rad, 5 single swing with the swing target 0.4 m away (large swing accelerations -> slacks), 6 both feet of one side in
+    the air, 7 deep crouch (knees +-1.8 rad, base 0.25 m).  Used by the parity tests only; not a BASELINE config."""
+    st, ref = randomised(N, seed=seed, first=first, contacts="stance")
+    u = _uniform(seed + 1, first, N)
+    idx = np.arange(first, first + N); kind = idx % 8
+    c = np.ones((4, N), np.uint8)
+    c[:, kind == 0] = 0
+    one = kind == 1; c[:, one] = 0; c[(idx[one] // 8) % 4, np.nonzero(one)[0]] = 1
+    sat = kind == 2
+    ref["acc"][0:3, sat] = (60.0 * u[sat, 0:3] - 30.0).T; ref["acc"][3:6, sat] = (120.0 * u[sat, 3:6] - 60.0).T
+    fast = kind == 3
+    st["qd"][:, fast] = (12.0 * u[fast, 6:18] - 6.0).T; st["base_twist"][:, fast] = (4.0 * u[fast, 18:24] - 2.0).T
+    tilt = kind == 4
+    rpy = (1.2 * u[tilt, 24:27] - 0.6).T; rpy[2] *= 0.2
+    st["base_quat"][:, tilt] = rpy_to_quat_wxyz(rpy[0], rpy[1], rpy[2])
+    far = kind == 5
+    leg = (idx[far] // 8) % 4; c[leg, np.nonzero(far)[0]] = 0
+    for k, i in zip(leg, np.nonzero(far)[0]):
+        ref["sw_pos"][3 * k:3 * k + 3, i] = [0.4 * (1 if k in (1, 2) else -1), 0.3 * (1 if k < 2 else -1), 0.4]
+        ref["sw_vel"][3 * k:3 * k + 3, i] = 2.0 * u[i, 27:30] - 1.0
+    side = kind == 6
+    left = ((idx[side] // 8) % 2 == 0)
+    c[0, np.nonzero(side)[0]] = (~left).astype(np.uint8); c[1, np.nonzero(side)[0]] = (~left).astype(np.uint8)
+    c[2, np.nonzero(side)[0]] = left.astype(np.uint8); c[3, np.nonzero(side)[0]] = left.astype(np.uint8)
+    cr = kind == 7
+    st["q"][:, cr] = (np.array([0.0, -1.0, 1.8, 0.0, 1.0, -1.8, 0.0, 1.0, -1.8, 0.0, -1.0, 1.8])[:, None] + 0.1 * (u[cr, 30:42].T - 0.5))
+    st["base_pos"][2, cr] = 0.25
+    ref["contacts"] = np.ascontiguousarray(c)
+    return {k: np.ascontiguousarray(v) for k, v in st.items()}, {k: np.ascontiguousarray(v) for k, v in ref.items()}

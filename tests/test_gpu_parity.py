@@ -76,6 +76,36 @@ def test_against_oracle_on_seeded_batches(wbc, orc, wl, contacts, n, ticks):
     ctl.close()
 
 
+@pytest.mark.parametrize("max_torque", [80.0, 3.0])
+def test_edge_cases_against_oracle(wbc, orc, wl, max_torque):
+    """workloads.stress: flight (no stance foot), one stance foot, saturating references, fast joints, tilted base, far swing targets,
+    one side in the air, deep crouch -- 4 ticks each.  With maxTorque = 3 Nm most QPs are infeasible: the cold start stops at nWSR = 100
+    (rc 64) or fails outright (rc 37, RET_INIT_FAILED_INFEASIBILITY), later hot starts from the unfinished state stop with rc 61
+    (RET_HOTSTART_STOPPED_INFEASIBILITY) and keep being called, like the oracle does.  Return codes must be identical tick by tick;
+    failed robots publish zero torques (what terminate() sends, wbc.cpp:626-635)."""
+    n = 128
+    st, ref = wl.stress(n)
+    prm = wbc.default_params(); prm.maxTorque = max_torque
+    ctl = wbc.WholeBodyController(n, params=prm); ob = orc.OracleBatch(n, params=dict(maxTorque=max_torque))
+    seen = set()
+    for t in range(4):
+        if t:
+            st = wl.advance_state(st)
+        ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.step()
+        ob.set_state(**st); ob.set_reference(**ref); ob.step()
+        got, want = ctl.getOutputs(), ob.outputs()
+        assert (got["rc"] == want["rc"]).all(), (t, got["rc"], want["rc"])
+        ok = want["rc"] == 0
+        assert relerr(got["tau"], want["tau"])[ok].max(initial=0) < RTOL and relerr(got["grf"], want["grf"])[ok].max(initial=0) < RTOL, t
+        assert relerr(got["x"], want["x"])[ok].max(initial=0) < RTOL, t
+        assert not got["tau"][:, ~ok].any()
+        same_ws = (got["ws"] == want["ws"]).all(axis=0)
+        assert same_ws[ok].mean() >= 0.9, (t, same_ws[ok].mean())
+        seen |= set(int(r) for r in want["rc"])
+    assert seen >= ({0, 64} if max_torque == 80.0 else {0, 37, 61, 64}), seen
+    ctl.close()
+
+
 def test_three_methods_equal_step_and_reset_restarts(wbc, wl):
     st, ref = wl.randomised(32, seed=5, contacts="mixed")
     a = wbc.WholeBodyController(32); b = wbc.WholeBodyController(32)

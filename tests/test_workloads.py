@@ -59,3 +59,19 @@ def test_oracle_closed_loop_is_stable(orc, wl):
     z = r["pos"][:, 2, :]
     assert (z > 0.4).all() and (z < 0.7).all()
     assert np.abs(r["tau"]).max() <= 80.0 + 1e-9
+
+
+def test_stress_workload_kinds_and_sharding(wl):
+    st, ref = wl.stress(64)
+    c = ref["contacts"]; kind = np.arange(64) % 8
+    assert (c[:, kind == 0] == 0).all() and (c[:, kind == 1].sum(axis=0) == 1).all() and (c[:, kind == 5].sum(axis=0) == 3).all()
+    assert (c[:, kind == 6].sum(axis=0) == 2).all() and ((c[0] == c[1]) & (c[2] == c[3]))[kind == 6].all()
+    assert np.abs(ref["acc"][:, kind == 2]).max() > 10 and not ref["acc"][:, kind != 2].any()
+    assert np.abs(st["qd"][:, kind == 3]).max() > 3 and np.abs(st["qd"][:, kind != 3]).max() <= 0.5
+    assert np.allclose(np.linalg.norm(st["base_quat"], axis=0), 1.0)
+    assert (st["base_pos"][2, kind == 7] == 0.25).all()
+    s2, r2 = wl.stress(24, first=40)
+    for k in st:
+        assert np.array_equal(s2[k], st[k][:, 40:64]), k
+    for k in ref:
+        assert np.array_equal(r2[k], ref[k][..., 40:64]), k
