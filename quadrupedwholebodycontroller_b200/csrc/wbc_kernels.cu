@@ -69,7 +69,13 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
 #if defined(WBC_QPDATA_GLOBAL)
         if(lane==0) w.qpg=&qpd[r];
 #else
-        { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
+        // all global loads of a robot are issued before the first shared store: the workspace is reached through a generic pointer, so the
+        // compiler will not move a load above a store by itself and every 32-element round would cost a full memory round trip
+        { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; constexpr int K=(QPDATA_DOUBLES+31)/32; double t[K];
+          #pragma unroll
+          for(int k=0;k<K;k++){ const int i=lane+32*k; t[k]=(i<QPDATA_DOUBLES)?__ldg(src+i):0.0; }
+          #pragma unroll
+          for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPDATA_DOUBLES) dst[i]=t[k]; } }
 #endif
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
         for(int k=0;k<8;k++) c.prof[k]=0;
@@ -77,10 +83,20 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         const long long tstart=clock64();
         QPState& S=qs[r];
         if(!isFirst){
-            LANE_FOR(i,42){ w.x[i]=S.x[i]; w.lb[i]=S.lb[i]; w.ub[i]=S.ub[i]; w.bstat[i]=S.bstat[i]; }
-            LANE_FOR(i,112) w.y[i]=S.y[i];
-            LANE_FOR(i,70){ w.Ax_l[i]=S.Ax_l[i]; w.Ax_u[i]=S.Ax_u[i]; w.cstat[i]=S.cstat[i]; }
+            double tx[2],tl[2],tu[2],ty[4],ta[3],tb[3]; signed char sb[2],sc[3];
+            #pragma unroll
+            for(int k=0;k<2;k++){ const int i=lane+32*k; const bool in=i<42; tx[k]=in?S.x[i]:0.0; tl[k]=in?S.lb[i]:0.0; tu[k]=in?S.ub[i]:0.0; sb[k]=in?S.bstat[i]:(signed char)0; }
+            #pragma unroll
+            for(int k=0;k<4;k++){ const int i=lane+32*k; ty[k]=(i<112)?S.y[i]:0.0; }
+            #pragma unroll
+            for(int k=0;k<3;k++){ const int i=lane+32*k; const bool in=i<70; ta[k]=in?S.Ax_l[i]:0.0; tb[k]=in?S.Ax_u[i]:0.0; sc[k]=in?S.cstat[i]:(signed char)0; }
             c.rampOffset=S.rampOffset; c.status=S.status;
+            #pragma unroll
+            for(int k=0;k<2;k++){ const int i=lane+32*k; if(i<42){ w.x[i]=tx[k]; w.lb[i]=tl[k]; w.ub[i]=tu[k]; w.bstat[i]=sb[k]; } }
+            #pragma unroll
+            for(int k=0;k<4;k++){ const int i=lane+32*k; if(i<112) w.y[i]=ty[k]; }
+            #pragma unroll
+            for(int k=0;k<3;k++){ const int i=lane+32*k; if(i<70){ w.Ax_l[i]=ta[k]; w.Ax_u[i]=tb[k]; w.cstat[i]=sc[k]; } }
         }
         WBC_SYNC();
         int nWSR=nWSRmax;
