@@ -56,8 +56,33 @@ __global__ void __launch_bounds__(32,WBC_UPD_MINBLOCKS) wbc_update_state_kernel(
     }
 }
 
+// ---------------------------------------------------------------- kernel 2a: TQ rebuild of the warm start, ahead of the solve
+// The first half of SQProblem::setupNewAuxiliaryQP -- Q = I, then ~20 Givens re-adds of the previous active constraints -- is most of a quiet
+// control tick, needs only Q, T, the index lists and four 42-vectors (QPWORK_TQ_BYTES = 23.8 KB: 9 robots per SM instead of the 5 the whole
+// workspace allows) and is 1.5 k instructions of code.  It runs here for every robot that has a previous solution and leaves Q, T and the
+// lists in HBM (QPPre, 22 KB per robot); wbc_solve_qp_kernel picks them up where the single-kernel path would have built them.  Same
+// functions, same arithmetic, same order.  One robot per CTA (the hardware queue balances: every robot costs about the same here).
+__global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* qpd,const QPState* qs,const unsigned char* first,QPPre* pre){
+    extern __shared__ double smem[];
+    QPWork& w=*reinterpret_cast<QPWork*>(smem);                       // ONLY the first QPWORK_TQ_BYTES exist
+    const int lane=threadIdx.x, r=blockIdx.x;
+    if(r>=N||first[r]!=0) return;
+    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.flops=0.0;
+    const QPState& S=qs[r];
+    signed char* old=reinterpret_cast<signed char*>(w.tmpv);
+    { signed char t[3];
+      #pragma unroll
+      for(int k=0;k<3;k++){ const int i=lane+32*k; t[k]=(i<70)?S.cstat[i]:(signed char)0; }
+      #pragma unroll
+      for(int k=0;k<3;k++){ const int i=lane+32*k; if(i<70) old[i]=t[k]; } }
+    WBC_SYNC();
+    rebuild_TQ(w,c,qpd[r],old);
+    WBC_SYNC();
+    store_prebuilt_TQ(w,c,pre[r]);
+}
+
 // ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart)
-__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int smStride){
+__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int smStride,const QPPre* pre){
     extern __shared__ double smem[];
     if(smStride>1){ unsigned smid; asm volatile("mov.u32 %0, %%smid;":"=r"(smid)); if(smid%(unsigned)smStride) return; }      // DEV experiment: leave SMs idle
     QPWork& w=*reinterpret_cast<QPWork*>(smem);
@@ -100,7 +125,7 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         }
         WBC_SYNC();
         int nWSR=nWSRmax;
-        const int rcv= isFirst? qp_init(w,c,nWSR) : qp_hotstart(w,c,nWSR);
+        const int rcv= isFirst? qp_init(w,c,nWSR) : qp_hotstart(w,c,nWSR,pre?&pre[r]:nullptr);
         WBC_SYNC();
         LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; out.x[i*N+r]=w.x[i]; out.ws[i*N+r]=w.bstat[i]; }
         LANE_FOR(i,112) S.y[i]=w.y[i];
@@ -213,6 +238,7 @@ struct wbc_handle {
     PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
     double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
     int smCount=0, qpBlocksPerSM=1, smStride=1; size_t qpSmem=0;
+    QPPre* pre=nullptr; bool split=true, maybeWarm=false;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     long long launches=0;
     std::string err;
 };
@@ -286,6 +312,9 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     h->qpBlocksPerSM=nb;
     if(const char* e=getenv("WBC_QP_CTAS_PER_SM")){ int v=atoi(e); if(v>=1&&v<nb) h->qpBlocksPerSM=v; }     // tuning knob: fewer resident solver warps per SM
     if(const char* e=getenv("WBC_QP_SM_STRIDE")){ int v=atoi(e); if(v>=1) h->smStride=v; }                              // DEV experiment
+    if(const char* e=getenv("WBC_QP_SPLIT")){ h->split=atoi(e)!=0; }                                                 // 0: rebuild the TQ factorisation inside the solve kernel
+    if(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)QPWORK_TQ_BYTES)!=cudaSuccess){
+        h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
     *out=h;
     int rcode=wbc_reset(h,0,n);
@@ -298,7 +327,7 @@ extern "C" int wbc_destroy(wbc_handle* h){
     cudaSetDevice(h->device);
     if(h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
-                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats};
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre};
     for(void* p:ptrs) if(p) cudaFree(p);
     for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
     if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
@@ -316,7 +345,7 @@ extern "C" int wbc_reset(wbc_handle* h,int first,int count){
     wbc_reset_kernel<<<(count+127)/128,128,0,h->stream>>>(h->N,h->devParams,first,count,h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,
                                                          h->contacts,h->prevc,h->switching,h->first,h->rc,h->nwsr,h->tau,h->grf,h->x);
     h->launches++; CK(cudaGetLastError());
-    if(first==0&&count==h->N) h->tick=0;
+    if(first==0&&count==h->N){ h->tick=0; h->maybeWarm=false; }
     return WBC_OK;
 }
 extern "C" int wbc_set_state(wbc_handle* h,const double* q,const double* qd,const double* pos,const double* quat,const double* twist){
@@ -355,8 +384,15 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     int grid=h->smCount*h->qpBlocksPerSM; if(grid>h->N) grid=h->N;
     CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
     CK(cudaEventRecord(h->ev[1],h->stream));
-    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->smStride);
+    const bool two=h->split&&h->maybeWarm;
+    if(two){
+        if(!h->pre) CK(cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N));
+        wbc_warm_setup_kernel<<<h->N,32,QPWORK_TQ_BYTES,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre);
+        h->launches++; CK(cudaGetLastError());
+    }
+    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->smStride,two?h->pre:nullptr);
     h->launches++; CK(cudaGetLastError());
+    h->maybeWarm=true;
     CK(cudaEventRecord(h->ev[2],h->stream));
     return WBC_OK;
 }

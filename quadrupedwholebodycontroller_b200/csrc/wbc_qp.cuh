@@ -22,6 +22,7 @@
 // If one of these preconditions were ever violated the solver reports QP_RET_UNSUPPORTED_PATH instead of guessing.
 #pragma once
 #include "wbc_common.cuh"
+#include <cstddef>
 #if !defined(__CUDACC__) && (defined(WBC_QP_TRACE) || defined(WBC_LI_STATS))
 #include <cstdio>
 #endif
@@ -77,10 +78,22 @@ struct QPState {
     int rampOffset, status, pad_;
 };
 
-// per-instance shared-memory workspace (40.6 KB -> 5 instances per SM)
+// per-instance shared-memory workspace (40.9 KB -> 5 instances per SM).  The members up to and including `arow` are all the warm-start
+// TQ rebuild touches (rebuild_TQ): the kernel that runs only that phase allocates just this prefix (QPWORK_TQ_BYTES, 9 instances per SM).
 struct QPWork {
     double Q[42*LD];
     double RT[TRI42+1];                         // packed R and T (see RR / TT)
+    signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70], pad_[2];
+    // phase-local scratch, overlaid: Givens / row vectors + {ratio tests | step-direction temporaries} + LI-exchange vectors,
+    // all of it reused as the 12 x nZ block (HZ)_force by the projected Cholesky (which runs when none of them is live)
+    union {
+        struct {
+            double wv[42], cs_c[42], cs_s[42], tmpv[42], arow[42];
+            union { struct { double num[70], den[70], dAx[70]; }; struct { double tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; };
+            double xFRy[42], xFRz[42], Zdz[42], ym[70];
+        };
+        double HZf[12*LD];
+    };
 #if defined(WBC_QPDATA_GLOBAL)
     const QPData* qpg;                          // compact H, A, new g / lbA / ubA stay in global memory (L1/L2): read-only during the solve
 #else
@@ -90,17 +103,17 @@ struct QPWork {
     double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
     double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
     double rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
-    // phase-local scratch, overlaid: {ratio tests | step-direction temporaries} + LI-exchange vectors + Givens / row vectors,
-    // all of it reused as the 12 x nZ block (HZ)_force by the projected Cholesky (which runs when none of them is live)
-    union {
-        struct {
-            union { struct { double num[70], den[70], dAx[70]; }; struct { double tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; };
-            double xFRy[42], xFRz[42], Zdz[42], ym[70];
-            double wv[42], cs_c[42], cs_s[42], tmpv[42], arow[42];
-        };
-        double HZf[12*LD];
-    };
-    signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70];
+};
+constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(double)+408+5*42*sizeof(double);
+static_assert(offsetof(QPWork,wv)+5*42*sizeof(double)==QPWORK_TQ_BYTES,"layout of the TQ-rebuild prefix");
+
+// what the warm-start TQ rebuild hands to the solve kernel (HBM): Q = [Z Y], the nAC rows of T, the index lists
+struct QPPre {
+    double Q[42*LD];
+    double T[TRI42+1];                          // only the first tri(nAC) entries are written / read
+    signed char AC[70], IAC[70], cstat[70], posAC[70];
+    int nAC, nIAC;
+    double flops;
 };
 
 // scalar solver state, replicated in every lane
@@ -915,10 +928,10 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
 // setupAuxiliaryWorkingSet step of the warm start (SQProblem.cpp:340-515 -> QProblem.cpp:2212-2378): cheap LI test
 // (addConstraint_checkLI, QProblem.cpp:3081-3105) and addConstraint without LI exchange.  Both need aFR'Z; it is computed once
 // (the first nZ entries of aFR'[Z Y] are the very same sums).
-WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,int number,int C_status){
+WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,const QPData& qd,int number,int C_status){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_SYNC();
-    LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
+    LANE_FOR(j,42) w.arow[j]=Ael_dev(qd,number,j);
     WBC_SYNC();
     double l2=0.0;
     if(c.frIdentity){
@@ -1098,9 +1111,70 @@ WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     if(rv!=QP_OK&&rv!=QP_RET_MAX_NWSR_REACHED) return QP_RET_INIT_FAILED_HOTSTART;
     return rv;
 }
+// The TQ part of SQProblem::setupNewAuxiliaryQP (SQProblem.cpp:340-515 -> setupAuxiliaryWorkingSet, QProblem.cpp:2212-2378): everything
+// free / inactive again, Q = I, T empty, then the old active constraints (`old` = their statuses) re-added in ascending order with the
+// cheap LI test and no LI exchange.  Touches only the prefix of the workspace (Q, T, lists, Givens vectors, arow) and reads the QP
+// data through `qd`, so it also runs as a kernel of its own with 9 robots per SM (wbc_warm_setup_kernel).
+WBC_FN void rebuild_TQ(QPWork& w,QPCtx& c,const QPData& qd,const signed char* old){
+    const int lane=c.lane;
+    LANE_FOR(i,42){ w.FR[i]=(signed char)i; }
+    LANE_FOR(i,70){ w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; }
+    WBC_SYNC();
+    c.nFR=42; c.nFX=0; c.nAC=0; c.nIAC=70; c.frIdentity=1;
+    setupTQfactorisation(w,c);
+    for(int i=0;i<70;i++){
+        const int os=(int)old[i];
+        if(os==ST_INACTIVE) continue;
+        setup_readd_constraint(w,c,qd,i,os);
+    }
+}
+// store / load of the rebuilt factorisation (HBM, coalesced: consecutive lanes, consecutive doubles).  Loads are issued in batches ahead of the
+// shared stores (see the prologue of wbc_solve_qp_kernel).
+WBC_DEV void store_prebuilt_TQ(const QPWork& w,const QPCtx& c,QPPre& p){
+    const int lane=c.lane, nT=tri(c.nAC);
+    LANE_FOR(i,42*LD) p.Q[i]=w.Q[i];
+    LANE_FOR(i,nT) p.T[i]=w.RT[i];
+    LANE_FOR(i,70){ p.AC[i]=w.AC[i]; p.IAC[i]=w.IAC[i]; p.cstat[i]=w.cstat[i]; p.posAC[i]=w.posAC[i]; }
+    if(lane==0){ p.nAC=c.nAC; p.nIAC=c.nIAC; p.flops=c.flops; }
+}
+WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
+    const int lane=c.lane;
+    c.nFR=42; c.nFX=0; c.nAC=p.nAC; c.nIAC=p.nIAC; c.frIdentity=1; c.flops+=p.flops;
+    const int nT=tri(c.nAC);
+#if WBC_NL==1
+    LANE_FOR(i,70){ w.AC[i]=p.AC[i]; w.IAC[i]=p.IAC[i]; w.cstat[i]=p.cstat[i]; w.posAC[i]=p.posAC[i]; }
+#else
+    signed char l0[3],l1[3],l2[3],l3[3];
+    #pragma unroll
+    for(int k=0;k<3;k++){ const int i=lane+WBC_NL*k; const bool in=i<70; l0[k]=in?p.AC[i]:(signed char)0; l1[k]=in?p.IAC[i]:(signed char)0; l2[k]=in?p.cstat[i]:(signed char)0; l3[k]=in?p.posAC[i]:(signed char)0; }
+#endif
+    constexpr int KB=19;                                                        // 3 batches of 19 x 32 doubles cover Q (1806)
+    #pragma unroll 1
+    for(int base=0;base<42*LD;base+=KB*WBC_NL){
+        double t[KB];
+        #pragma unroll
+        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<42*LD)?p.Q[i]:0.0; }
+        #pragma unroll
+        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; if(i<42*LD) w.Q[i]=t[k]; }
+    }
+    #pragma unroll 1
+    for(int base=0;base<nT;base+=KB*WBC_NL){
+        double t[KB];
+        #pragma unroll
+        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<nT)?p.T[i]:0.0; }
+        #pragma unroll
+        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; if(i<nT) w.RT[i]=t[k]; }
+    }
+#if WBC_NL>1
+    #pragma unroll
+    for(int k=0;k<3;k++){ const int i=lane+WBC_NL*k; if(i<70){ w.AC[i]=l0[k]; w.IAC[i]=l1[k]; w.cstat[i]=l2[k]; w.posAC[i]=l3[k]; } }
+#endif
+    LANE_FOR(i,42) w.FR[i]=(signed char)i;
+    WBC_SYNC();
+}
 // SQProblem::hotstart -> setupNewAuxiliaryQP (SQProblem.cpp:153-197, 340-515) then QProblem::hotstart.
 // On entry w.x, w.y, w.lb, w.ub, w.Ax_l, w.Ax_u, w.bstat, w.cstat hold the previous tick's solver state.
-WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
+WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
     const int lane=c.lane;
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
@@ -1110,18 +1184,12 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR){
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;
     if(wbc_ballot(anyFixed)!=0u) return QP_RET_SETUP_AUXILIARYQP_FAILED;     // addBound on an ST_UNBOUNDED-typed variable: RET_ALL_BOUNDS_ACTIVE
-    LANE_FOR(i,42){ w.FR[i]=(signed char)i; }
-    LANE_FOR(i,70){ w.IAC[i]=(signed char)i; w.num[i]=(double)w.cstat[i]; }      // park the old statuses in w.num
-    WBC_SYNC();
-    LANE_FOR(i,70) w.cstat[i]=ST_INACTIVE;
-    c.nFR=42; c.nFX=0; c.nAC=0; c.nIAC=70; c.frIdentity=1;
-    setupTQfactorisation(w,c);
-    // setupAuxiliaryWorkingSet(old, setupAfresh): re-add the old active constraints in ascending order, cheap LI test, no LI exchange
-    for(int i=0;i<70;i++){
-        const int os=(int)w.num[i];
-        if(os==ST_INACTIVE) continue;
-        setup_readd_constraint(w,c,i,os);
-    }
+    if(!pre){
+        signed char* old=reinterpret_cast<signed char*>(w.tmpv);                 // park the old statuses (nothing in the rebuild touches tmpv)
+        LANE_FOR(i,70) old[i]=w.cstat[i];
+        WBC_SYNC();
+        rebuild_TQ(w,c,WQP,old);
+    } else load_prebuilt_TQ(w,c,*pre);                                         // the same, done beforehand by wbc_warm_setup_kernel
     int rv=computeProjectedCholesky(w,c);
     if(rv!=QP_OK) return QP_RET_UNSUPPORTED_PATH;
     c.status=QPS_AUXILIARYQPSOLVED;

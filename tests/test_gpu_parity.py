@@ -125,6 +125,29 @@ def test_three_methods_equal_step_and_reset_restarts(wbc, wl):
     a.close(); b.close()
 
 
+def test_two_kernel_warm_start_is_bit_identical_to_the_single_kernel_path(wbc, wl, monkeypatch):
+    """The TQ rebuild of the warm start runs as a kernel of its own ahead of the solve (wbc_warm_setup_kernel); WBC_QP_SPLIT=0 keeps it
+    inside the solve kernel.  Same functions, same arithmetic: every output of every tick must be bit-identical, also for robots that are
+    reset (cold) in the middle of the sequence while the others stay warm."""
+    n = 192
+    st, ref = wl.randomised(n, seed=7, contacts="mixed", switching_frac=0.1)
+    outs = []
+    for split in ("1", "0"):
+        monkeypatch.setenv("WBC_QP_SPLIT", split)
+        ctl = wbc.WholeBodyController(n); s = st; rec = []
+        for t in range(4):
+            if t:
+                s = wl.advance_state(s)
+            if t == 2:
+                ctl.setInitialState(first=40, count=50)              # these 50 robots start cold again, the rest hot-start
+            ctl.setJointAndBaseState(**s); ctl.setReference(**ref); ctl.step(); rec.append(ctl.getOutputs())
+        ctl.close(); outs.append(rec)
+    for t in range(4):
+        for k in outs[0][t]:
+            assert np.array_equal(outs[0][t][k], outs[1][t][k]), (t, k)
+    assert (outs[0][2]["nwsr"][40:90] >= 40).all()                    # the reset robots did cold-start at tick 2
+
+
 def test_sharding_does_not_change_results(wbc, wl):
     n = 96
     st, ref = wl.randomised(n, seed=1234, contacts="mixed")

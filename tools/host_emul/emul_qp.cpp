@@ -1,6 +1,7 @@
 // DEVELOPMENT AID ONLY -- not part of the shipped library (see emul_rbd.cpp).  One emulated lane.
 #include "../../quadrupedwholebodycontroller_b200/csrc/wbc_qp.cuh"
 #include <cstring>
+#include <cstdlib>
 #include <cstdio>
 using namespace wbc;
 
@@ -10,7 +11,14 @@ extern "C" void emulqp_destroy(void* h){ delete (EmulQP*)h; }
 // first != 0: init (cold), else hotstart.  outputs: x[42], y[112], ws[112], returns rc; *nwsr in/out
 extern "C" int emulqp_solve(void* h,const double* qpdata,int first,int* nwsr,double* x,double* y,signed char* ws){
     EmulQP* e=(EmulQP*)h; memcpy(&e->w.qp,qpdata,sizeof(QPData));
-    int n=*nwsr; int rc= first? qp_init(e->w,e->c,n) : qp_hotstart(e->w,e->c,n);
+    int n=*nwsr; int rc;
+    if(first) rc=qp_init(e->w,e->c,n);
+    else if(getenv("EMUL_SPLIT")){          // the two-kernel warm start: rebuild in a second workspace, hand over through QPPre
+        static EmulQP a; static QPPre pre; memset(&a,0,sizeof(a)); memset(&pre,0,sizeof(pre)); a.c.lane=0;
+        signed char old[70]; memcpy(old,e->w.cstat,70);
+        rebuild_TQ(a.w,a.c,e->w.qp,old); store_prebuilt_TQ(a.w,a.c,pre);
+        rc=qp_hotstart(e->w,e->c,n,&pre);
+    } else rc=qp_hotstart(e->w,e->c,n,nullptr);
     *nwsr=n;
     memcpy(x,e->w.x,42*8); memcpy(y,e->w.y,112*8);
     for(int i=0;i<42;i++) ws[i]=e->w.bstat[i]; for(int i=0;i<70;i++) ws[42+i]=e->w.cstat[i];
