@@ -384,9 +384,10 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     int grid=h->smCount*h->qpBlocksPerSM; if(grid>h->N) grid=h->N;
     CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
     CK(cudaEventRecord(h->ev[1],h->stream));
-    const bool two=h->split&&h->maybeWarm;
+    bool two=h->split&&h->maybeWarm;
+    if(two&&!h->pre&&cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N)!=cudaSuccess){      // 22 KB per robot; without it the solve kernel rebuilds the factorisation itself
+        cudaGetLastError(); h->pre=nullptr; h->split=false; two=false; }
     if(two){
-        if(!h->pre) CK(cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N));
         wbc_warm_setup_kernel<<<h->N,32,QPWORK_TQ_BYTES,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre);
         h->launches++; CK(cudaGetLastError());
     }
