@@ -62,11 +62,16 @@ __global__ void __launch_bounds__(32,WBC_UPD_MINBLOCKS) wbc_update_state_kernel(
 // workspace allows) and is 1.5 k instructions of code.  It runs here for every robot that has a previous solution and leaves Q, T and the
 // lists in HBM (QPPre, 22 KB per robot); wbc_solve_qp_kernel picks them up where the single-kernel path would have built them.  Same
 // functions, same arithmetic, same order.  One robot per CTA (the hardware queue balances: every robot costs about the same here).
-__global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* qpd,const QPState* qs,const unsigned char* first,QPPre* pre){
+__global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* qpd,const QPState* qs,const unsigned char* first,QPPre* pre,int canary){
     extern __shared__ double smem[];
     QPWork& w=*reinterpret_cast<QPWork*>(smem);                       // ONLY the first QPWORK_TQ_BYTES exist
     const int lane=threadIdx.x, r=blockIdx.x;
     if(r>=N||first[r]!=0) return;
+    // self-check (WBC_QP_SETUP_CANARY=1, tests): launched with the WHOLE workspace, everything past the prefix is filled with a NaN pattern first and
+    // must still hold it at the end; a read from there poisons the result, a write is reported by poisoning it on purpose (see the end)
+    unsigned long long* guard=reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(smem)+QPWORK_TQ_BYTES);
+    constexpr int NGUARD=(int)((sizeof(QPWork)-QPWORK_TQ_BYTES)/8);
+    if(canary){ LANE_FOR(i,NGUARD) guard[i]=0xFFFFFFFFFFFFFFFFull; WBC_SYNC(); }
     QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.flops=0.0;
     const QPState& S=qs[r];
     signed char* old=reinterpret_cast<signed char*>(w.tmpv);
@@ -79,6 +84,8 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
     rebuild_TQ(w,c,qpd[r],old);
     WBC_SYNC();
     store_prebuilt_TQ(w,c,pre[r]);
+    if(canary){ bool bad=false; LANE_FOR(i,NGUARD) if(guard[i]!=0xFFFFFFFFFFFFFFFFull) bad=true;
+                if(wbc_ballot(bad)!=0u){ WBC_SYNC(); LANE_FOR(i,42*LD) pre[r].Q[i]=__longlong_as_double(-1ll); } }
 }
 
 // ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart)
@@ -238,7 +245,7 @@ struct wbc_handle {
     PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
     double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
     int smCount=0, qpBlocksPerSM=1, smStride=1; size_t qpSmem=0;
-    QPPre* pre=nullptr; bool split=true, maybeWarm=false;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
+    QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     long long launches=0;
     std::string err;
 };
@@ -313,7 +320,8 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     if(const char* e=getenv("WBC_QP_CTAS_PER_SM")){ int v=atoi(e); if(v>=1&&v<nb) h->qpBlocksPerSM=v; }     // tuning knob: fewer resident solver warps per SM
     if(const char* e=getenv("WBC_QP_SM_STRIDE")){ int v=atoi(e); if(v>=1) h->smStride=v; }                              // DEV experiment
     if(const char* e=getenv("WBC_QP_SPLIT")){ h->split=atoi(e)!=0; }                                                 // 0: rebuild the TQ factorisation inside the solve kernel
-    if(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)QPWORK_TQ_BYTES)!=cudaSuccess){
+    if(const char* e=getenv("WBC_QP_SETUP_CANARY")){ h->setupCanary=atoi(e)!=0; }                                    // tests: guard the prefix allocation of kernel 2a
+    if(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)(h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES))!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
     *out=h;
@@ -388,7 +396,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     if(two&&!h->pre&&cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N)!=cudaSuccess){      // 22 KB per robot; without it the solve kernel rebuilds the factorisation itself
         cudaGetLastError(); h->pre=nullptr; h->split=false; two=false; }
     if(two){
-        wbc_warm_setup_kernel<<<h->N,32,QPWORK_TQ_BYTES,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre);
+        wbc_warm_setup_kernel<<<h->N,32,h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre,h->setupCanary?1:0);
         h->launches++; CK(cudaGetLastError());
     }
     wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->smStride,two?h->pre:nullptr);

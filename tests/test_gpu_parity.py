@@ -148,6 +148,27 @@ def test_two_kernel_warm_start_is_bit_identical_to_the_single_kernel_path(wbc, w
     assert (outs[0][2]["nwsr"][40:90] >= 40).all()                    # the reset robots did cold-start at tick 2
 
 
+def test_warm_setup_kernel_stays_inside_its_workspace_prefix(wbc, wl, monkeypatch):
+    """wbc_warm_setup_kernel allocates only the first QPWORK_TQ_BYTES of the solver workspace.  With WBC_QP_SETUP_CANARY=1 it is launched with the whole
+    workspace, the part past the prefix is filled with a NaN pattern and checked at the end: a read from there poisons the factorisation, a write
+    makes the kernel poison it on purpose -- either way the outputs would differ from the normal run (compute-sanitizer is not available on the pool)."""
+    n = 256
+    st, ref = wl.stress(n)
+    outs = []
+    for canary in ("0", "1"):
+        monkeypatch.setenv("WBC_QP_SETUP_CANARY", canary)
+        ctl = wbc.WholeBodyController(n); s = st; rec = []
+        for t in range(3):
+            if t:
+                s = wl.advance_state(s)
+            ctl.setJointAndBaseState(**s); ctl.setReference(**ref); ctl.step(); rec.append(ctl.getOutputs())
+        ctl.close(); outs.append(rec)
+    for t in range(3):
+        assert np.isfinite(outs[1][t]["x"]).all(), t
+        for k in outs[0][t]:
+            assert np.array_equal(outs[0][t][k], outs[1][t][k]), (t, k)
+
+
 def test_sharding_does_not_change_results(wbc, wl):
     n = 96
     st, ref = wl.randomised(n, seed=1234, contacts="mixed")
