@@ -245,7 +245,7 @@ struct wbc_handle {
     PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
     double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
     int smCount=0, qpBlocksPerSM=1, smStride=1; size_t qpSmem=0;
-    QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
+    QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false; size_t setupPad=0;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     long long launches=0;
     std::string err;
 };
@@ -321,7 +321,8 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     if(const char* e=getenv("WBC_QP_SM_STRIDE")){ int v=atoi(e); if(v>=1) h->smStride=v; }                              // DEV experiment
     if(const char* e=getenv("WBC_QP_SPLIT")){ h->split=atoi(e)!=0; }                                                 // 0: rebuild the TQ factorisation inside the solve kernel
     if(const char* e=getenv("WBC_QP_SETUP_CANARY")){ h->setupCanary=atoi(e)!=0; }                                    // tests: guard the prefix allocation of kernel 2a
-    if(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)(h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES))!=cudaSuccess){
+    if(const char* e=getenv("WBC_QP_SETUP_PAD")){ int v=atoi(e); if(v>0&&v<100000) h->setupPad=(size_t)v; }          // DEV: extra bytes of shared memory per CTA of kernel 2a = fewer robots per SM (occupancy scan)
+    if(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)((h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad))!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
     *out=h;
@@ -396,7 +397,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     if(two&&!h->pre&&cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N)!=cudaSuccess){      // 22 KB per robot; without it the solve kernel rebuilds the factorisation itself
         cudaGetLastError(); h->pre=nullptr; h->split=false; two=false; }
     if(two){
-        wbc_warm_setup_kernel<<<h->N,32,h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre,h->setupCanary?1:0);
+        wbc_warm_setup_kernel<<<h->N,32,(h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre,h->setupCanary?1:0);
         h->launches++; CK(cudaGetLastError());
     }
     wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->smStride,two?h->pre:nullptr);
