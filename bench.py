@@ -254,7 +254,8 @@ def main():
                 e2e=dict(value=e2e, unit=UNIT, h2d_bytes_per_step=IN_BYTES_PER_ROBOT * n, d2h_bytes_per_step=OUT_BYTES_PER_ROBOT * n, ms_per_step=float(ms_e2e.mean())),
                 gpu_launches=int(launches), clocks=clocks,
                 kernels_ms=dict(update_state=rbd_ms, solve_qp=qp_ms, solve_qp_share=qp_ms * max(1, ro) / float(ms_dev.mean()),
-                                note="per launch; rollout: mean over the ticks of one extra step replayed tick by tick" if ro else "per launch, mean over the timed steps"),
+                                note=("per launch; rollout: mean over the ticks of one extra step replayed tick by tick" if ro else "per launch, mean over the timed steps")
+                                + "; solve_qp = wbc_warm_setup_kernel (hot-started robots only) + wbc_solve_qp_kernel, one event pair"),
                 roofline=dict(bound="hbm", achieved=alg_bytes / (qp_ms * 1e-3) / 1e9, peak=hbm_peak, unit="GB/s", frac=alg_bytes / (qp_ms * 1e-3) / 1e9 / hbm_peak,
                               traffic=traffic, traffic_source="profiles/r01a_ncu_summary.md (cold launch) / profiles/r01f_ncu_summary.md (hot-started launch), 4096 robots" if traffic else None, kernel="wbc_solve_qp_kernel", peak_source="MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                               note="solver is FP64-latency / shared-memory bound, not HBM bound: see fp64_roofline and DESIGN.md section 4"),
