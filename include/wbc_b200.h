@@ -8,7 +8,10 @@
  *
  * Array convention: structure-of-arrays, instance index fastest -- element k of robot i is a[k*N + i]; fp64; flags are
  * bytes.  Pointers may be HOST or DEVICE pointers (detected with cudaPointerGetAttributes); host buffers are copied
- * with cudaMemcpyAsync on the handle's stream.  The caller owns its buffers, the library owns all per-robot
+ * with cudaMemcpyAsync on the handle's stream.  BUFFER LIFETIME: input copies are asynchronous -- from PINNED host memory and
+ * from device memory the caller's buffer is read when the stream reaches the copy, so it must stay valid and unmodified until
+ * then (wbc_synchronize, or any later call that returns results to a host pointer); pageable host memory is staged by the
+ * driver before the call returns.  Output copies to host pointers are complete when the getter returns.  The caller owns its buffers, the library owns all per-robot
  * persistent state (finite-difference history, integral error, QP warm-start state) in device memory.
  * Threading: one handle = one host thread at a time; handles are independent.
  *
@@ -52,6 +55,8 @@ void wbc_default_params(wbc_params* p);
  * table compiled from urdf/anymal.urdf is baked into the library), SQProblem(42,70) construction, loadParameters,
  * setInitialState.  device = CUDA ordinal.  stream = a cudaStream_t (as void*) to run on, or NULL for a private stream. */
 int wbc_create(int n_robots, int device, const wbc_params* params, void* stream, wbc_handle** out);
+/* (params->slackWeight < 1 is refused with WBC_ERR_ARG: the solver leaves out qpOASES' flipping-bound and zero-curvature branches,
+ * QProblem.cpp:3938-3963, 4278-4511, which cannot fire while H >= I -- see the header of csrc/wbc_qp.cuh.) */
 int wbc_destroy(wbc_handle* h);                                   /* ~WholeBodyController (whole_body_controller.cpp:61-63) */
 
 /* Replaces setInitialState() (whole_body_controller.cpp:65-120) for robots [first, first+count): contacts 1111, nominal joint
@@ -76,7 +81,7 @@ int wbc_set_reference(wbc_handle* h, const double* pose, const double* vel, cons
  * hot-starts it again exactly like the SQProblem object would -- halting the loop (:654-659) is the caller's decision. */
 int wbc_update_state(wbc_handle* h);
 int wbc_solve_qp(wbc_handle* h);
-int wbc_compute_joint_torques(wbc_handle* h);
+int wbc_compute_joint_torques(wbc_handle* h);   /* the recovery itself runs as the epilogue of the solve kernel (x is still on chip); this call orders after it */
 int wbc_step(wbc_handle* h);                                     /* the three calls above, asynchronous on the stream */
 int wbc_synchronize(wbc_handle* h);
 
@@ -85,6 +90,17 @@ int wbc_synchronize(wbc_handle* h);
  * ws[112] in {-1,0,+1} (QProblem::getWorkingSet: 42 bounds then 70 constraints), CoM position com[3].  Any pointer may be NULL.
  * Synchronises the stream when a HOST pointer is given. */
 int wbc_get_outputs(wbc_handle* h, double* tau, double* grf, double* x, int* rc, int* nwsr, signed char* ws, double* com);
+
+/* QProblem::getDualSolution of every robot's SQProblem (lib/qpOASES/src/QProblemB.cpp:800-823): y[112] = 42 bound multipliers then 70
+ * constraint multipliers, qpOASES sign convention (>= 0 at an active lower side, <= 0 at an active upper side).  Host or device. */
+int wbc_get_duals(wbc_handle* h, double* y);
+/* 1 while hot-started ticks run the TQ rebuild as a kernel of its own (needs 22 KB of device memory per robot); 0 after that
+ * allocation failed and the rebuild moved inside the solve kernel (identical results, slower) -- wbc_last_error says so once. */
+int wbc_warm_start_split(const wbc_handle* h);
+/* Explicit switches for tests and measurements; every setting gives bit-identical results.  Keys: "warm_start_split" (0 = rebuild the
+ * TQ factorisation inside the solve kernel), "cohort" (-1 auto, 0 never, 1 always: gang scheduling of the solve kernel),
+ * "setup_canary" (1 = guard the workspace prefix of the warm-start kernel). */
+int wbc_set_option(wbc_handle* h, const char* key, int value);
 
 /* Test / inspection hook: the dense QP of robot i as the reference would hand it to qpOASES (row-major H[42*42], g[42],
  * A[70*42], lbA[70], ubA[70]; whole_body_controller.cpp:479-515), expanded on the host from the compact device form. */
@@ -141,7 +157,8 @@ long long wbc_launch_count(const wbc_handle* h);
 int wbc_last_kernel_ms(wbc_handle* h, float* rbd_ms, float* qp_ms, float* torque_ms);
 /* measurement hook: per-robot record of the last solve, 10 int64 per robot: clock64 ticks in data shift, step direction, step,
  * active-set change, projected Cholesky, ramp/drift, whole solve; iterations; ALGORITHMIC flops of the qpOASES method on dense
- * data (formulas of SURVEY.md section 8d, the numerator of the FP64 roofline); cold-start flag.  enable != 0 allocates the buffer */
+ * data (formulas of SURVEY.md section 8d, the numerator of the FP64 roofline); cold-start flag.  enable != 0 allocates the buffer.
+ * Only in the profiling build of the same library (libwbc_b200_prof.so, -DWBC_PROFILE); the product build returns WBC_ERR_ARG. */
 int wbc_profile(wbc_handle* h, int enable, long long* host_out);
 /* measured FP64 FMA peak of the device in GFLOP/s (8 independent DFMA chains per thread, all SMs) -- the FP64 roofline denominator */
 int wbc_measure_fp64_peak(wbc_handle* h, double* gflops);

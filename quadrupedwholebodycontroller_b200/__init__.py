@@ -9,15 +9,15 @@ import os
 
 import numpy as np
 
-from .build import build_library, LIB_PATH
+from .build import build_library, LIB_PATH, PROF_LIB_PATH
 
 NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC = 12, 4, 42, 70          # whole_body_controller.hpp:27-32 of the reference
-_lib = None
+_libs = {}
 
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
            "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
            "wbc_planner_default_params", "wbc_planner_create", "wbc_planner_reset", "wbc_planner_set_cmd_vel", "wbc_planner_tick", "wbc_get_reference",
-           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error"]
+           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option"]
 
 
 class WbcParams(C.Structure):
@@ -32,14 +32,14 @@ class WbcPlannerParams(C.Structure):
                                           "body_final_velocity", "dt")]
 
 
-def load_library():
-    """dlopen the CUDA library; raises if it has not been built (no fallback of any kind)."""
-    global _lib
-    if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
+def load_library(profiling=False):
+    """dlopen the CUDA library (profiling=True: the -DWBC_PROFILE build of the same sources); raises if it has not been built (no fallback of any kind)."""
+    path = PROF_LIB_PATH if profiling else LIB_PATH
+    if path not in _libs:
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
                                "The controller has no CPU fallback.")
-        lib = C.CDLL(LIB_PATH)
+        lib = C.CDLL(path)
         lib.wbc_create.argtypes = [C.c_int, C.c_int, C.POINTER(WbcParams), C.c_void_p, C.POINTER(C.c_void_p)]
         for name in ("wbc_destroy", "wbc_update_state", "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize"):
             getattr(lib, name).argtypes = [C.c_void_p]
@@ -64,9 +64,12 @@ def load_library():
         for name in ("wbc_planner_tick", "wbc_plant_enable", "wbc_plant_step"):
             getattr(lib, name).argtypes = [C.c_void_p]
         lib.wbc_rollout.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        lib.wbc_get_duals.argtypes = [C.c_void_p, C.c_void_p]
+        lib.wbc_warm_start_split.argtypes = [C.c_void_p]
         lib.wbc_rollout_stats.argtypes = [C.c_void_p] + [C.c_void_p] * 4 + [C.c_int]
-        _lib = lib
-    return _lib
+        lib.wbc_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        _libs[path] = lib
+    return _libs[path]
 
 
 def default_params():
@@ -97,8 +100,8 @@ class WholeBodyController:
 
     numberOfJoints, numberOfLegs, qpNumberOfVariables, qpNumberOfConstraints = NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC
 
-    def __init__(self, n_robots, device=0, params=None, stream=None):
-        lib = load_library()
+    def __init__(self, n_robots, device=0, params=None, stream=None, profiling=False):
+        lib = self._lib = load_library(profiling)
         self.N = int(n_robots)
         self._h = C.c_void_p()
         p = params if params is not None else default_params()
@@ -109,38 +112,38 @@ class WholeBodyController:
 
     def _ck(self, rc):
         if rc != 0:
-            raise RuntimeError(f"wbc error {rc}: {load_library().wbc_last_error(self._h).decode()}")
+            raise RuntimeError(f"wbc error {rc}: {self._lib.wbc_last_error(self._h).decode()}")
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
-            load_library().wbc_destroy(self._h); self._h = C.c_void_p()
+            self._lib.wbc_destroy(self._h); self._h = C.c_void_p()
 
     __del__ = close
 
     def setInitialState(self, first=0, count=None):
-        self._ck(load_library().wbc_reset(self._h, first, self.N - first if count is None else count))
+        self._ck(self._lib.wbc_reset(self._h, first, self.N - first if count is None else count))
 
     def setJointAndBaseState(self, q, qd, base_pos, base_quat, base_twist):
-        self._ck(load_library().wbc_set_state(self._h, _ptr(q), _ptr(qd), _ptr(base_pos), _ptr(base_quat), _ptr(base_twist)))
+        self._ck(self._lib.wbc_set_state(self._h, _ptr(q), _ptr(qd), _ptr(base_pos), _ptr(base_quat), _ptr(base_twist)))
 
     def setReference(self, pose, vel, acc, sw_pos, sw_vel, sw_acc, contacts, switching=None):
-        self._ck(load_library().wbc_set_reference(self._h, _ptr(pose), _ptr(vel), _ptr(acc), _ptr(sw_pos), _ptr(sw_vel), _ptr(sw_acc),
+        self._ck(self._lib.wbc_set_reference(self._h, _ptr(pose), _ptr(vel), _ptr(acc), _ptr(sw_pos), _ptr(sw_vel), _ptr(sw_acc),
                                                   _ptr(contacts), _ptr(switching)))
 
     def updateState(self):
-        self._ck(load_library().wbc_update_state(self._h))
+        self._ck(self._lib.wbc_update_state(self._h))
 
     def solveQP(self):
-        self._ck(load_library().wbc_solve_qp(self._h))
+        self._ck(self._lib.wbc_solve_qp(self._h))
 
     def computeJointTorques(self):
-        self._ck(load_library().wbc_compute_joint_torques(self._h))
+        self._ck(self._lib.wbc_compute_joint_torques(self._h))
 
     def step(self):
-        self._ck(load_library().wbc_step(self._h))
+        self._ck(self._lib.wbc_step(self._h))
 
     def synchronize(self):
-        self._ck(load_library().wbc_synchronize(self._h))
+        self._ck(self._lib.wbc_synchronize(self._h))
 
     def getOutputs(self, tau=None, grf=None, x=None, rc=None, nwsr=None, ws=None, com=None):
         """copies into the given buffers (host or device); with no argument returns fresh numpy arrays of everything."""
@@ -148,54 +151,67 @@ class WholeBodyController:
             N = self.N
             o = dict(tau=np.zeros((12, N)), grf=np.zeros((12, N)), x=np.zeros((42, N)), rc=np.zeros(N, np.int32), nwsr=np.zeros(N, np.int32),
                      ws=np.zeros((112, N), np.int8), com=np.zeros((3, N)))
-            self._ck(load_library().wbc_get_outputs(self._h, *[_ptr(o[k]) for k in ("tau", "grf", "x", "rc", "nwsr", "ws", "com")]))
+            self._ck(self._lib.wbc_get_outputs(self._h, *[_ptr(o[k]) for k in ("tau", "grf", "x", "rc", "nwsr", "ws", "com")]))
             return o
-        self._ck(load_library().wbc_get_outputs(self._h, _ptr(tau), _ptr(grf), _ptr(x), _ptr(rc), _ptr(nwsr), _ptr(ws), _ptr(com)))
+        self._ck(self._lib.wbc_get_outputs(self._h, _ptr(tau), _ptr(grf), _ptr(x), _ptr(rc), _ptr(nwsr), _ptr(ws), _ptr(com)))
+
+    def getDuals(self, y=None):
+        """QProblem::getDualSolution of every robot, (112, N): 42 bound multipliers then 70 constraint multipliers"""
+        out = np.zeros((112, self.N)) if y is None else y
+        self._ck(self._lib.wbc_get_duals(self._h, _ptr(out)))
+        return out
+
+    def setOption(self, key, value):
+        """explicit switches for tests / measurements (wbc_set_option): warm_start_split, cohort, setup_canary"""
+        self._ck(self._lib.wbc_set_option(self._h, key.encode(), int(value)))
+
+    def warmStartSplit(self):
+        return bool(self._lib.wbc_warm_start_split(self._h))
 
     def denseQP(self, robot):
         o = dict(H=np.zeros((42, 42)), g=np.zeros(42), A=np.zeros((70, 42)), lbA=np.zeros(70), ubA=np.zeros(70))
-        self._ck(load_library().wbc_get_dense_qp(self._h, robot, *[_ptr(o[k]) for k in ("H", "g", "A", "lbA", "ubA")]))
+        self._ck(self._lib.wbc_get_dense_qp(self._h, robot, *[_ptr(o[k]) for k in ("H", "g", "A", "lbA", "ubA")]))
         return o
 
     def launchCount(self):
-        return int(load_library().wbc_launch_count(self._h))
+        return int(self._lib.wbc_launch_count(self._h))
 
     def profile(self, enable=True, fetch=False):
         """per-robot clock64 breakdown of the last solve, shape (N, 10) int64: 7 clock64 phase counters, iterations, algorithmic flops, cold flag"""
         out = np.zeros((self.N, 10), np.int64) if fetch else None
-        self._ck(load_library().wbc_profile(self._h, int(enable), _ptr(out)))
+        self._ck(self._lib.wbc_profile(self._h, int(enable), _ptr(out)))
         return out
 
     def measureFp64Peak(self):
-        g = C.c_double(); self._ck(load_library().wbc_measure_fp64_peak(self._h, C.byref(g))); return g.value
+        g = C.c_double(); self._ck(self._lib.wbc_measure_fp64_peak(self._h, C.byref(g))); return g.value
 
     def lastKernelMs(self):
         a, b, c = C.c_float(), C.c_float(), C.c_float()
-        self._ck(load_library().wbc_last_kernel_ms(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        self._ck(self._lib.wbc_last_kernel_ms(self._h, C.byref(a), C.byref(b), C.byref(c)))
         return dict(update_state=a.value, solve_qp=b.value, compute_joint_torques=c.value)
 
     # ---- planner, plant, closed-loop rollout (SURVEY 8f; reference src/motion_planner.cpp) ----
     def plannerCreate(self, params=None):
         p = params
         if p is None:
-            p = WbcPlannerParams(); load_library().wbc_planner_default_params(C.byref(p))
-        self._ck(load_library().wbc_planner_create(self._h, C.byref(p)))
+            p = WbcPlannerParams(); self._lib.wbc_planner_default_params(C.byref(p))
+        self._ck(self._lib.wbc_planner_create(self._h, C.byref(p)))
 
     def plannerReset(self, first=0, count=None):
-        self._ck(load_library().wbc_planner_reset(self._h, first, self.N - first if count is None else count))
+        self._ck(self._lib.wbc_planner_reset(self._h, first, self.N - first if count is None else count))
 
     def plannerSetCmdVel(self, vx=None, vy=None, yaw_rate=None):
-        self._ck(load_library().wbc_planner_set_cmd_vel(self._h, _ptr(vx), _ptr(vy), _ptr(yaw_rate)))
+        self._ck(self._lib.wbc_planner_set_cmd_vel(self._h, _ptr(vx), _ptr(vy), _ptr(yaw_rate)))
 
     def plannerTick(self):
-        self._ck(load_library().wbc_planner_tick(self._h))
+        self._ck(self._lib.wbc_planner_tick(self._h))
 
     def getReference(self, with_published=True):
         N = self.N
         o = dict(pose=np.zeros((6, N)), vel=np.zeros((6, N)), acc=np.zeros((6, N)), sw_pos=np.zeros((12, N)), sw_vel=np.zeros((12, N)), sw_acc=np.zeros((12, N)),
                  contacts=np.zeros((4, N), np.uint8), switching=np.zeros(N, np.uint8))
         pub = np.zeros(N, np.uint8) if with_published else None
-        self._ck(load_library().wbc_get_reference(self._h, *[_ptr(o[k]) for k in ("pose", "vel", "acc", "sw_pos", "sw_vel", "sw_acc", "contacts", "switching")], _ptr(pub)))
+        self._ck(self._lib.wbc_get_reference(self._h, *[_ptr(o[k]) for k in ("pose", "vel", "acc", "sw_pos", "sw_vel", "sw_acc", "contacts", "switching")], _ptr(pub)))
         if with_published:
             o["published"] = pub
         return o
@@ -203,20 +219,20 @@ class WholeBodyController:
     def getState(self):
         N = self.N
         o = dict(q=np.zeros((12, N)), qd=np.zeros((12, N)), base_pos=np.zeros((3, N)), base_quat=np.zeros((4, N)), base_twist=np.zeros((6, N)))
-        self._ck(load_library().wbc_get_state(self._h, *[_ptr(o[k]) for k in ("q", "qd", "base_pos", "base_quat", "base_twist")]))
+        self._ck(self._lib.wbc_get_state(self._h, *[_ptr(o[k]) for k in ("q", "qd", "base_pos", "base_quat", "base_twist")]))
         return o
 
     def plantEnable(self):
-        self._ck(load_library().wbc_plant_enable(self._h))
+        self._ck(self._lib.wbc_plant_enable(self._h))
 
     def plantStep(self):
-        self._ck(load_library().wbc_plant_step(self._h))
+        self._ck(self._lib.wbc_plant_step(self._h))
 
     def rollout(self, ticks, planner_every=4):
-        self._ck(load_library().wbc_rollout(self._h, int(ticks), int(planner_every)))
+        self._ck(self._lib.wbc_rollout(self._h, int(ticks), int(planner_every)))
 
     def rolloutStats(self, reset=False):
         N = self.N
         o = dict(ticks=np.zeros(N, np.int32), failed_ticks=np.zeros(N, np.int32), nwsr_sum=np.zeros(N, np.int32), nwsr_max=np.zeros(N, np.int32))
-        self._ck(load_library().wbc_rollout_stats(self._h, *[_ptr(o[k]) for k in ("ticks", "failed_ticks", "nwsr_sum", "nwsr_max")], int(reset)))
+        self._ck(self._lib.wbc_rollout_stats(self._h, *[_ptr(o[k]) for k in ("ticks", "failed_ticks", "nwsr_sum", "nwsr_max")], int(reset)))
         return o

@@ -5,13 +5,15 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.environ.get("WBC_B200_LIB") or os.path.join(HERE, "libwbc_b200.so")     # override = DEV experiments with another build of the same CUDA library
+PROF_LIB_PATH = os.path.join(HERE, "libwbc_b200_prof.so")     # same sources with -DWBC_PROFILE: clock64 phase timers + algorithmic-flop counter (measurement only)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
 
 
-def _stale():
-    if not os.path.exists(LIB_PATH):
+def _stale(path=None):
+    path = path or LIB_PATH
+    if not os.path.exists(path):
         return True
-    t = os.path.getmtime(LIB_PATH)
+    t = os.path.getmtime(path)
     srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "wbc_b200.h")]
     return any(os.path.getmtime(s) > t for s in srcs)
 
@@ -26,9 +28,14 @@ def build_variant(out_path, defines=(), verbose=False):
 
 def build_library(force=False, verbose=False):
     """nvcc -gencode arch=compute_100a,code=sm_100a ... csrc/wbc_kernels.cu -> libwbc_b200.so (cross-compiles without a GPU)."""
-    if not force and not _stale():
-        return LIB_PATH
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "wbc_kernels.cu"), "-o", LIB_PATH]
-    subprocess.check_call(cmd)
+    default = os.path.join(HERE, "libwbc_b200.so")
+    jobs = []
+    if force or _stale(default):
+        jobs.append(subprocess.Popen([nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "wbc_kernels.cu"), "-o", default]))
+    if force or _stale(PROF_LIB_PATH):
+        jobs.append(subprocess.Popen([nvcc] + NVCC_FLAGS + ["-DWBC_PROFILE", os.path.join(CSRC, "wbc_kernels.cu"), "-o", PROF_LIB_PATH]))
+    for j in jobs:
+        if j.wait() != 0:
+            raise RuntimeError("nvcc failed building the CUDA library")
     return LIB_PATH

@@ -45,7 +45,11 @@
 #endif
 
 // element loops are NOT unrolled: the solver is instruction-cache bound (453 KB of code vs a 32 KB L1.5), not issue bound
-#if defined(__CUDACC__)
+#if defined(__CUDACC__) && defined(WBC_LANE_UNROLL)
+  #define WBC_PRAGMA_(x) _Pragma(#x)
+  #define WBC_PRAGMA(x) WBC_PRAGMA_(x)
+  #define LANE_FOR(i,n) WBC_PRAGMA(unroll WBC_LANE_UNROLL) for(int i=lane;i<(n);i+=WBC_NL)
+#elif defined(__CUDACC__)
   #define LANE_FOR(i,n) _Pragma("unroll 1") for(int i=lane;i<(n);i+=WBC_NL)
 #else
   #define LANE_FOR(i,n) for(int i=lane;i<(n);i+=WBC_NL)

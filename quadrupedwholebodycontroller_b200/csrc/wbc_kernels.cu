@@ -10,6 +10,9 @@
 #include <string>
 #include <vector>
 #include "../../include/wbc_b200.h"
+#ifndef WBC_GANG
+#define WBC_GANG 5              /* solver warps (= robots in flight) per CTA, one CTA per SM: 5 x 41.5 KB of shared memory */
+#endif
 #include "wbc_assembly.cuh"
 #include "wbc_qp.cuh"
 #include "wbc_planner.cuh"
@@ -72,7 +75,10 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
     unsigned long long* guard=reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(smem)+QPWORK_TQ_BYTES);
     constexpr int NGUARD=(int)((sizeof(QPWork)-QPWORK_TQ_BYTES)/8);
     if(canary){ LANE_FOR(i,NGUARD) guard[i]=0xFFFFFFFFFFFFFFFFull; WBC_SYNC(); }
-    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.flops=0.0;
+    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+#if defined(WBC_PROFILE)
+    c.flops=0.0;
+#endif
     const QPState& S=qs[r];
     signed char* old=reinterpret_cast<signed char*>(w.tmpv);
     { signed char t[3];
@@ -88,15 +94,20 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
                 if(wbc_ballot(bad)!=0u){ WBC_SYNC(); LANE_FOR(i,42*LD) pre[r].Q[i]=__longlong_as_double(-1ll); } }
 }
 
-// ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart)
-__global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int smStride,const QPPre* pre){
+// ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart) + torque recovery
+// One robot per warp; WBC_GANG warps per CTA (one CTA per SM: WBC_GANG x 41.5 KB of shared memory) walk the iterations of their robots in
+// step (wbc_qp.cuh "gang mode").  Robots are pulled from an atomic work counter.  cohort = 0: a warp fetches its next robot as soon as
+// it is done (hot-started ticks: iteration counts 0..100); cohort = 1: the gang fetches together and waits for its slowest member (cold
+// batches: all members then sit at the same iteration index with matrices of the same size, which keeps the barrier waits short).
+#define WBC_QP_THREADS (32*WBC_GANG)
+__global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int cohort,const QPPre* pre,int* stats){
     extern __shared__ double smem[];
-    if(smStride>1){ unsigned smid; asm volatile("mov.u32 %0, %%smid;":"=r"(smid)); if(smid%(unsigned)smStride) return; }      // DEV experiment: leave SMs idle
-    QPWork& w=*reinterpret_cast<QPWork*>(smem);
-    const int lane=threadIdx.x;
+    QPWork& w=*reinterpret_cast<QPWork*>(reinterpret_cast<char*>(smem)+(size_t)(threadIdx.x>>5)*sizeof(QPWork));
+    const int lane=threadIdx.x&31;
     for(;;){
         int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
-        if(r>=N) break;
+        if(cohort){ if(gang_bar(r>=N)) break; }                      // the whole gang is out of work
+        if(r>=N){ while(!gang_bar(1)){} if(cohort) continue; break; }     // keep the others' barriers complete until every warp is done
         const bool isFirst=first[r]!=0;
 #if defined(WBC_QPDATA_GLOBAL)
         if(lane==0) w.qpg=&qpd[r];
@@ -110,9 +121,11 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
           for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPDATA_DOUBLES) dst[i]=t[k]; } }
 #endif
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+#if defined(WBC_PROFILE)
         for(int k=0;k<8;k++) c.prof[k]=0;
         c.flops=0.0;
         const long long tstart=clock64();
+#endif
         QPState& S=qs[r];
         if(!isFirst){
             double tx[2],tl[2],tu[2],ty[4],ta[3],tb[3]; signed char sb[2],sc[3];
@@ -134,32 +147,39 @@ __global__ void __launch_bounds__(32) wbc_solve_qp_kernel(int N,const QPData* qp
         int nWSR=nWSRmax;
         const int rcv= isFirst? qp_init(w,c,nWSR) : qp_hotstart(w,c,nWSR,pre?&pre[r]:nullptr);
         WBC_SYNC();
-        LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; out.x[i*N+r]=w.x[i]; out.ws[i*N+r]=w.bstat[i]; }
+        // QProblemB::getPrimalSolution (QProblemB.cpp:774-793) hands x out only in these three states; otherwise the caller's qpSolution_ keeps
+        // its previous value (wbc.cpp:536) -- and so does out.x.  The solver's own iterate S.x is stored regardless (it IS the SQProblem member).
+        const bool haveSol=(c.status==QPS_AUXILIARYQPSOLVED||c.status==QPS_HOMOTOPYQPSOLVED||c.status==QPS_SOLVED);
+        LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; if(haveSol) out.x[i*N+r]=w.x[i]; else w.x[i]=out.x[i*N+r]; out.ws[i*N+r]=w.bstat[i]; }
         LANE_FOR(i,112) S.y[i]=w.y[i];
         LANE_FOR(i,70){ S.Ax_l[i]=w.Ax_l[i]; S.Ax_u[i]=w.Ax_u[i]; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; }
-        if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
-                     if(prof){ c.prof[6]=clock64()-tstart; for(int k=0;k<8;k++) prof[10*(size_t)r+k]=c.prof[k]; prof[10*(size_t)r+8]=(long long)c.flops; prof[10*(size_t)r+9]=isFirst?1:0; } }
         WBC_SYNC();
+        // computeJointTorques (wbc.cpp:553-577) on the solution still in shared memory: tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*, f* = x[18:30];
+        // a robot whose solve did not return 0 publishes zero torques (terminate(), :626-635).  w.x = qpSolution_ here (see above).
+        if(lane<12){ const int i=lane; const QPData& q=WQP;
+            double s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*w.x[6+j];
+            double t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*w.x[18+j];
+            out.tau[i*N+r]= (rcv==0)? (s+q.biasj[i]-t) : 0.0;
+            out.grf[i*N+r]= w.x[18+i]; }
+        if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
+                     if(stats){ stats[r]+=1; if(rcv!=0) stats[N+r]+=1; stats[2*N+r]+=nWSR; if(nWSR>stats[3*N+r]) stats[3*N+r]=nWSR; }   // ticks, failed ticks, sum / max of nWSR
+#if defined(WBC_PROFILE)
+                     if(prof){ c.prof[6]=clock64()-tstart; for(int k=0;k<8;k++) prof[10*(size_t)r+k]=c.prof[k]; prof[10*(size_t)r+8]=(long long)c.flops; prof[10*(size_t)r+9]=isFirst?1:0; }
+#endif
+        }
+        WBC_SYNC();
+        if(cohort){ while(!gang_bar(1)){} }                           // drain until every member of the gang is done
     }
 }
 
-// ---------------------------------------------------------------- kernel 3: torque recovery (wbc.cpp:553-577)
-// tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*;  a robot whose QP failed publishes zero torques (terminate(), :626-635)
-__global__ void wbc_compute_torques_kernel(int N,const QPData* qpd,BatchOut out,int* stats){
+// ---------------------------------------------------------------- kernel 3 (torque recovery, wbc.cpp:553-577) is the epilogue of kernel 2:
+// x and the compact QP are still in shared memory there; a separate kernel re-read the 5.7 KB AoS QPData record per thread.
+// gather of the dual solution (QProblem::getDualSolution) from the AoS solver state into the SoA output layout: inspection only
+__global__ void wbc_gather_duals_kernel(int N,const QPState* qs,double* y){
     const int r=blockIdx.x*blockDim.x+threadIdx.x;
     if(r>=N) return;
-    if(stats){ const int nw=out.nwsr[r]; stats[r]+=1; if(out.rc[r]!=0) stats[N+r]+=1; stats[2*N+r]+=nw; if(nw>stats[3*N+r]) stats[3*N+r]=nw; }   // ticks, failed ticks, sum / max of nWSR
-    const QPData& q=qpd[r];
-    const bool ok=out.rc[r]==0;
-    double xs[24]; for(int k=0;k<24;k++) xs[k]=out.x[(6+k)*N+r];
-    for(int i=0;i<12;i++){
-        double s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*xs[j];
-        double t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*xs[12+j];
-        out.tau[i*N+r]= ok? (s+q.biasj[i]-t) : 0.0;
-        out.grf[i*N+r]= xs[12+i];
-    }
+    for(int k=0;k<112;k++) y[(size_t)k*N+r]=qs[r].y[k];
 }
-
 
 // ---------------------------------------------------------------- batched MotionPlanner (wbc_planner.cuh), one planner per thread
 // mode 0: one planner period + hand-over of a published message (referenceCallback, wbc.cpp:150-185); mode 1: constructor state
@@ -244,7 +264,8 @@ struct wbc_handle {
     // planner / plant / rollout
     PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
     double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
-    int smCount=0, qpBlocksPerSM=1, smStride=1; size_t qpSmem=0;
+    int smCount=0, qpBlocksPerSM=1, cohortMode=-1; size_t qpSmem=0;
+    double* duals=nullptr;
     QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false; size_t setupPad=0;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     long long launches=0;
     std::string err;
@@ -282,6 +303,10 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     *out=nullptr;
     wbc_handle* h=new wbc_handle; h->N=n; h->device=device;
     if(params) h->params=*params; else wbc_default_params(&h->params);
+    // The solver omits qpOASES' flipping-bound and zero-curvature branches; they cannot fire while H = blkdiag(I, I, I + Jst Jst', slackWeight I) >= I
+    // (wbc_qp.cuh header).  slackWeight < 1 breaks that premise (H's smallest eigenvalue becomes slackWeight), so it is refused here, loudly.
+    if(!(h->params.slackWeight>=1.0)||!(h->params.loopRate>0.0)){
+        fprintf(stderr,"wbc_create failed: slackWeight must be >= 1 (the solver's omitted qpOASES branches rely on H >= I) and loopRate > 0\n"); delete h; return WBC_ERR_ARG; }
     auto fail=[&](int code){ fprintf(stderr,"wbc_create failed: %s\n",h->err.c_str()); wbc_destroy(h); return code; };
     cudaError_t e=cudaSetDevice(device);
     if(e!=cudaSuccess){ h->err=std::string("cudaSetDevice: ")+cudaGetErrorString(e)+" (no CPU fallback exists)"; int c=WBC_ERR_CUDA; fprintf(stderr,"wbc_create failed: %s\n",h->err.c_str()); delete h; return c; }
@@ -297,8 +322,9 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     ok=ok&&dalloc(h->tau,12*N)==cudaSuccess&&dalloc(h->grf,12*N)==cudaSuccess&&dalloc(h->x,42*N)==cudaSuccess&&dalloc(h->com,3*N)==cudaSuccess;
     ok=ok&&dalloc(h->rc,N)==cudaSuccess&&dalloc(h->nwsr,N)==cudaSuccess&&dalloc(h->ws,112*N)==cudaSuccess;
     if(!ok){ h->err=std::string("cudaMalloc: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_NOMEM); }
-    cudaMemsetAsync(h->ctrl,0,N*sizeof(CtrlState),h->stream); cudaMemsetAsync(h->qpd,0,N*sizeof(QPData),h->stream); cudaMemsetAsync(h->qps,0,N*sizeof(QPState),h->stream);
-    cudaMemsetAsync(h->ws,0,112*N,h->stream); cudaMemsetAsync(h->com,0,3*N*sizeof(double),h->stream);
+    if(cudaMemsetAsync(h->ctrl,0,N*sizeof(CtrlState),h->stream)!=cudaSuccess||cudaMemsetAsync(h->qpd,0,N*sizeof(QPData),h->stream)!=cudaSuccess
+       ||cudaMemsetAsync(h->qps,0,N*sizeof(QPState),h->stream)!=cudaSuccess||cudaMemsetAsync(h->ws,0,112*N,h->stream)!=cudaSuccess
+       ||cudaMemsetAsync(h->com,0,3*N*sizeof(double),h->stream)!=cudaSuccess){ h->err=std::string("cudaMemsetAsync: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     // constants: 13-body model table and gains
     ModelConst mc; memcpy(mc.restR,ANYMAL_restR,sizeof(mc.restR)); memcpy(mc.restP,ANYMAL_restP,sizeof(mc.restP)); memcpy(mc.axis,ANYMAL_axis,sizeof(mc.axis));
     memcpy(mc.mass,ANYMAL_mass,sizeof(mc.mass)); memcpy(mc.mcom,ANYMAL_mcom,sizeof(mc.mcom)); memcpy(mc.inertia,ANYMAL_inertia,sizeof(mc.inertia));
@@ -311,17 +337,15 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     if(cudaMemcpyToSymbol(c_model,&mc,sizeof(mc))!=cudaSuccess){
         h->err=std::string("cudaMemcpyToSymbol: ")+cudaGetErrorString(cudaGetLastError())+" (library built for sm_100a only)"; return fail(WBC_ERR_CUDA); }
     // solver launch geometry: one warp per CTA, as many CTAs per SM as shared memory allows
-    h->qpSmem=sizeof(QPWork);
+    h->qpSmem=sizeof(QPWork)*WBC_GANG;
     if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
-    int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,32,h->qpSmem)!=cudaSuccess||nb<1){
+    int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,WBC_QP_THREADS,h->qpSmem)!=cudaSuccess||nb<1){
         h->err=std::string("occupancy query: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     h->qpBlocksPerSM=nb;
-    if(const char* e=getenv("WBC_QP_CTAS_PER_SM")){ int v=atoi(e); if(v>=1&&v<nb) h->qpBlocksPerSM=v; }     // tuning knob: fewer resident solver warps per SM
-    if(const char* e=getenv("WBC_QP_SM_STRIDE")){ int v=atoi(e); if(v>=1) h->smStride=v; }                              // DEV experiment
-    if(const char* e=getenv("WBC_QP_SPLIT")){ h->split=atoi(e)!=0; }                                                 // 0: rebuild the TQ factorisation inside the solve kernel
-    if(const char* e=getenv("WBC_QP_SETUP_CANARY")){ h->setupCanary=atoi(e)!=0; }                                    // tests: guard the prefix allocation of kernel 2a
-    if(const char* e=getenv("WBC_QP_SETUP_PAD")){ int v=atoi(e); if(v>0&&v<100000) h->setupPad=(size_t)v; }          // DEV: extra bytes of shared memory per CTA of kernel 2a = fewer robots per SM (occupancy scan)
+#if defined(WBC_DEV_KNOBS)                                                                                        // measurement builds only (tools/): never in the shipped library
+    if(const char* e=getenv("WBC_QP_SETUP_PAD")){ int v=atoi(e); if(v>0&&v<100000) h->setupPad=(size_t)v; }          // extra shared memory per CTA of kernel 2a = fewer robots per SM (occupancy scan)
+#endif
     if(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)((h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad))!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     for(int i=0;i<4;i++) if(cudaEventCreate(&h->ev[i])!=cudaSuccess){ h->err="cudaEventCreate failed"; return fail(WBC_ERR_CUDA); }
@@ -336,7 +360,7 @@ extern "C" int wbc_destroy(wbc_handle* h){
     cudaSetDevice(h->device);
     if(h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
-                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre};
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre,h->duals};
     for(void* p:ptrs) if(p) cudaFree(p);
     for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
     if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
@@ -348,7 +372,8 @@ static BatchIn batch_in(const wbc_handle* h){ BatchIn b; b.q=h->q; b.qd=h->qd; b
 static BatchOut batch_out(const wbc_handle* h){ BatchOut o; o.tau=h->tau; o.grf=h->grf; o.x=h->x; o.com=h->com; o.rc=h->rc; o.nwsr=h->nwsr; o.ws=h->ws; return o; }
 
 extern "C" int wbc_reset(wbc_handle* h,int first,int count){
-    if(!h||first<0||count<0||first+count>h->N) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(first<0||count<0||first+count>h->N){ h->err="wbc_reset: robot range outside [0, n_robots)"; return WBC_ERR_ARG; }
     if(count==0) return WBC_OK;
     CK(cudaSetDevice(h->device));
     wbc_reset_kernel<<<(count+127)/128,128,0,h->stream>>>(h->N,h->devParams,first,count,h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,
@@ -390,17 +415,21 @@ extern "C" int wbc_update_state(wbc_handle* h){
 extern "C" int wbc_solve_qp(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
-    int grid=h->smCount*h->qpBlocksPerSM; if(grid>h->N) grid=h->N;
+    int grid=h->smCount*h->qpBlocksPerSM;
+    if(grid>(h->N+WBC_GANG-1)/WBC_GANG) grid=(h->N+WBC_GANG-1)/WBC_GANG;
+    // cohort scheduling only when every robot of the batch cold-starts (nothing solved since the last full reset)
+    const int cohort= h->cohortMode<0 ? (h->maybeWarm?0:1) : h->cohortMode;
     CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
     CK(cudaEventRecord(h->ev[1],h->stream));
     bool two=h->split&&h->maybeWarm;
     if(two&&!h->pre&&cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N)!=cudaSuccess){      // 22 KB per robot; without it the solve kernel rebuilds the factorisation itself
-        cudaGetLastError(); h->pre=nullptr; h->split=false; two=false; }
+        cudaGetLastError(); h->pre=nullptr; h->split=false; two=false;
+        h->err="warm-start workspace (22 KB per robot) could not be allocated: the TQ rebuild runs inside the solve kernel (same results, slower); see wbc_warm_start_split"; }
     if(two){
         wbc_warm_setup_kernel<<<h->N,32,(h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre,h->setupCanary?1:0);
         h->launches++; CK(cudaGetLastError());
     }
-    wbc_solve_qp_kernel<<<grid,32,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->smStride,two?h->pre:nullptr);
+    wbc_solve_qp_kernel<<<grid,WBC_QP_THREADS,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,cohort,two?h->pre:nullptr,h->stats);
     h->launches++; CK(cudaGetLastError());
     h->maybeWarm=true;
     CK(cudaEventRecord(h->ev[2],h->stream));
@@ -409,8 +438,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
 extern "C" int wbc_compute_joint_torques(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
-    wbc_compute_torques_kernel<<<(h->N+63)/64,64,0,h->stream>>>(h->N,h->qpd,batch_out(h),h->stats);
-    h->launches++; CK(cudaGetLastError());
+    // tau and f* were written by the epilogue of wbc_solve_qp_kernel from the solution in shared memory; nothing is left to launch
     CK(cudaEventRecord(h->ev[3],h->stream));
     return WBC_OK;
 }
@@ -426,8 +454,19 @@ extern "C" int wbc_get_outputs(wbc_handle* h,double* tau,double* grf,double* x,i
     if(host) CK(cudaStreamSynchronize(h->stream));
     return WBC_OK;
 }
+extern "C" int wbc_get_duals(wbc_handle* h,double* y){
+    if(!h||!y){ if(h) h->err="wbc_get_duals: null argument"; return WBC_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    const size_t N=(size_t)h->N;
+    if(!h->duals){ if(dalloc(h->duals,112*N)!=cudaSuccess){ h->err="cudaMalloc (duals)"; cudaGetLastError(); return WBC_ERR_NOMEM; } }
+    wbc_gather_duals_kernel<<<(h->N+127)/128,128,0,h->stream>>>(h->N,h->qps,h->duals); h->launches++; CK(cudaGetLastError());
+    bool host=false; int r; if((r=copy_out(h,y,h->duals,112*N*sizeof(double),host))) return r;
+    if(host) CK(cudaStreamSynchronize(h->stream));
+    return WBC_OK;
+}
 extern "C" int wbc_get_dense_qp(wbc_handle* h,int robot,double* H,double* g,double* A,double* lbA,double* ubA){
-    if(!h||robot<0||robot>=h->N) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(robot<0||robot>=h->N){ h->err="wbc_get_dense_qp: robot index outside [0, n_robots)"; return WBC_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     QPData q; CK(cudaMemcpyAsync(&q,h->qpd+robot,sizeof(QPData),cudaMemcpyDeviceToHost,h->stream)); CK(cudaStreamSynchronize(h->stream));
     if(H) for(int i=0;i<42;i++) for(int j=0;j<42;j++) H[i*42+j]=Hel(q,i,j);
@@ -449,7 +488,8 @@ extern "C" void wbc_planner_default_params(wbc_planner_params* p){
 static RefOut ref_out(const wbc_handle* h){ RefOut o; o.pose=h->pose; o.vel=h->vel; o.acc=h->acc; o.swp=h->swp; o.swv=h->swv; o.swa=h->swa; o.contacts=h->contacts; o.prevc=h->prevc;
     o.switching=h->switching; o.published=h->published; return o; }
 extern "C" int wbc_planner_reset(wbc_handle* h,int first,int count){
-    if(!h||!h->planner||first<0||count<0||first+count>h->N) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(!h->planner||first<0||count<0||first+count>h->N){ h->err="wbc_planner_reset: needs wbc_planner_create and a robot range inside [0, n_robots)"; return WBC_ERR_ARG; }
     if(count==0) return WBC_OK;
     CK(cudaSetDevice(h->device));
     wbc_planner_kernel<<<(count+127)/128,128,0,h->stream>>>(h->N,h->plannerParams,h->planner,h->plannerCmd,ref_out(h),1,first,count);
@@ -473,14 +513,16 @@ extern "C" int wbc_planner_create(wbc_handle* h,const wbc_planner_params* p){
     return wbc_planner_reset(h,0,h->N);
 }
 extern "C" int wbc_planner_set_cmd_vel(wbc_handle* h,const double* vx,const double* vy,const double* yaw_rate){
-    if(!h||!h->planner) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(!h->planner){ h->err="planner call before wbc_planner_create"; return WBC_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     const size_t N=(size_t)h->N, D=sizeof(double); int r;
     if((r=copy_in(h,h->plannerCmd,vx,N*D))||(r=copy_in(h,h->plannerCmd+N,vy,N*D))||(r=copy_in(h,h->plannerCmd+2*N,yaw_rate,N*D))) return r;
     return WBC_OK;
 }
 extern "C" int wbc_planner_tick(wbc_handle* h){
-    if(!h||!h->planner) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(!h->planner){ h->err="planner call before wbc_planner_create"; return WBC_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     wbc_planner_kernel<<<(h->N+127)/128,128,0,h->stream>>>(h->N,h->plannerParams,h->planner,h->plannerCmd,ref_out(h),0,0,h->N);
     h->launches++; CK(cudaGetLastError());
@@ -515,14 +557,16 @@ extern "C" int wbc_plant_enable(wbc_handle* h){
     return WBC_OK;
 }
 extern "C" int wbc_plant_step(wbc_handle* h){
-    if(!h||!h->plantAux) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(!h->plantAux){ h->err="wbc_plant_step before wbc_plant_enable"; return WBC_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     wbc_plant_step_kernel<<<(h->N+127)/128,128,0,h->stream>>>(h->N,1.0/h->devParams.loopRate,h->plantAux,h->x,h->rc,h->q,h->qd,h->pos,h->quat,h->twist);
     h->launches++; CK(cudaGetLastError());
     return WBC_OK;
 }
 extern "C" int wbc_rollout(wbc_handle* h,int ticks,int planner_every){
-    if(!h||ticks<0||planner_every<1||!h->plantAux||!h->planner) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(ticks<0||planner_every<1||!h->plantAux||!h->planner){ h->err="wbc_rollout: needs wbc_planner_create, wbc_plant_enable, ticks >= 0 and planner_every >= 1"; return WBC_ERR_ARG; }
     int r;
     for(int t=0;t<ticks;t++){
         if(h->tick%planner_every==0) if((r=wbc_planner_tick(h))) return r;
@@ -532,7 +576,8 @@ extern "C" int wbc_rollout(wbc_handle* h,int ticks,int planner_every){
     return WBC_OK;
 }
 extern "C" int wbc_rollout_stats(wbc_handle* h,int* ticks,int* failed_ticks,int* nwsr_sum,int* nwsr_max,int reset){
-    if(!h||!h->stats) return WBC_ERR_ARG;
+    if(!h) return WBC_ERR_ARG;
+    if(!h->stats){ h->err="wbc_rollout_stats before wbc_plant_enable"; return WBC_ERR_ARG; }
     CK(cudaSetDevice(h->device));
     const size_t N=(size_t)h->N; bool host=false; int r;
     if((r=copy_out(h,ticks,h->stats,N*sizeof(int),host))||(r=copy_out(h,failed_ticks,h->stats+N,N*sizeof(int),host))||(r=copy_out(h,nwsr_sum,h->stats+2*N,N*sizeof(int),host))
@@ -542,6 +587,20 @@ extern "C" int wbc_rollout_stats(wbc_handle* h,int* ticks,int* failed_ticks,int*
     return WBC_OK;
 }
 extern "C" int wbc_num_robots(const wbc_handle* h){ return h?h->N:0; }
+extern "C" int wbc_warm_start_split(const wbc_handle* h){ return (h&&h->split)?1:0; }
+// explicit switches (tests, measurements); every setting gives bit-identical results
+extern "C" int wbc_set_option(wbc_handle* h,const char* key,int value){
+    if(!h||!key) return WBC_ERR_ARG;
+    const std::string k(key);
+    if(k=="warm_start_split"){ h->split=value!=0; return WBC_OK; }            // 0: rebuild the TQ factorisation inside the solve kernel
+    if(k=="cohort"){ h->cohortMode=value; return WBC_OK; }                    // -1 auto, 0 never, 1 always (gang scheduling of kernel 2)
+    if(k=="setup_canary"){                                                    // guard the prefix allocation of kernel 2a (tests)
+        h->setupCanary=value!=0;
+        CK(cudaSetDevice(h->device));
+        CK(cudaFuncSetAttribute(wbc_warm_setup_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)((h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad)));
+        return WBC_OK; }
+    h->err="wbc_set_option: unknown key "+k; return WBC_ERR_ARG;
+}
 extern "C" long long wbc_launch_count(const wbc_handle* h){ return h?h->launches:0; }
 extern "C" int wbc_last_kernel_ms(wbc_handle* h,float* rbd_ms,float* qp_ms,float* torque_ms){
     if(!h) return WBC_ERR_ARG;
@@ -555,10 +614,14 @@ extern "C" int wbc_last_kernel_ms(wbc_handle* h,float* rbd_ms,float* qp_ms,float
 // per-robot breakdown of the last solve (10 x int64 per robot: QPCtx::prof[0..7], algorithmic flops, cold flag); enable!=0 allocates the buffer
 extern "C" int wbc_profile(wbc_handle* h,int enable,long long* host_out){
     if(!h) return WBC_ERR_ARG;
+#if !defined(WBC_PROFILE)
+    (void)enable; (void)host_out; h->err="wbc_profile: this is the product build; the phase timers and the flop counter exist only in libwbc_b200_prof.so (-DWBC_PROFILE)"; return WBC_ERR_ARG;
+#else
     CK(cudaSetDevice(h->device));
     if(enable&&!h->prof){ CK(cudaMalloc((void**)&h->prof,10*(size_t)h->N*sizeof(long long))); CK(cudaMemsetAsync(h->prof,0,10*(size_t)h->N*sizeof(long long),h->stream)); }
     if(host_out&&h->prof){ CK(cudaMemcpyAsync(host_out,h->prof,10*(size_t)h->N*sizeof(long long),cudaMemcpyDeviceToHost,h->stream)); CK(cudaStreamSynchronize(h->stream)); }
     return WBC_OK;
+#endif
 }
 // FP64 FMA peak of the device, measured: 8 independent DFMA chains per thread, 1024 threads x 2 CTAs per SM
 __global__ void wbc_fp64_peak_kernel(double* out,int iters){

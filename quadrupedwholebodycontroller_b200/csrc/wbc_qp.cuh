@@ -63,12 +63,20 @@ constexpr int TRI42=42*43/2;
 WBC_HD int tri(int i){ return (i*(i+1))>>1; }
 #define RR(i,j) w.RT[TRI42-1-(tri(j)+(i))]
 #define TT(i,j) w.RT[tri(i)+(SIZET-1-(j))]
-#if defined(__CUDACC__)
+// measurement code (clock64 phase timers, algorithmic-flop counter) exists only in the profiling build (-DWBC_PROFILE -> libwbc_b200_prof.so)
+#if defined(WBC_PROFILE) && defined(__CUDACC__)
   #define WBC_TIC(t) long long t=clock64()
   #define WBC_TOC(t,k) { long long n_=clock64(); c.prof[k]+=n_-t; t=n_; }
 #else
-  #define WBC_TIC(t) long long t=0
-  #define WBC_TOC(t,k) { (void)t; }
+  #define WBC_TIC(t) do{}while(0)
+  #define WBC_TOC(t,k) do{}while(0)
+#endif
+#if defined(WBC_PROFILE)
+  #define WBC_FLOPS(expr) { c.flops+=(expr); }
+  #define WBC_COUNT_ITER() { c.prof[7]++; }
+#else
+  #define WBC_FLOPS(expr) do{}while(0)
+  #define WBC_COUNT_ITER() do{}while(0)
 #endif
 
 // persistent solver state of one instance between ticks (HBM) -- what SQProblem keeps across hotstarts
@@ -125,9 +133,26 @@ struct QPCtx {
     int farRampOffset;   // rampOffset at the last updateFarBounds
     double farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
     double tau;
+#if defined(WBC_PROFILE)
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
     double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
+#endif
 };
+
+// ---------------------------------------------------------------- gang mode (WBC_GANG = warps per CTA, one robot per warp)
+// The solver is instruction-SUPPLY bound when its warps run independently: 193 KB of code, ~90 KB touched per working-set change, a 32 KB
+// L1.5 instruction cache per SM and a GPC-level cache that delivers one line per two cycles to ~18 SMs (ncu, 5 independent warps per SM:
+// sm__icc hit rate 62 %, gcc instruction requests 85 % of peak, 2.5 of 7.6 stall cycles per instruction are `no_instruction`).
+// In gang mode the WBC_GANG warps of a CTA meet at ONE barrier at the top of every working-set iteration, so they walk the phases of the
+// iteration roughly together and share the instruction-cache fills (icc hit rate 91 %, gcc requests 38 % of peak, no_instruction 0.26).
+// More barrier sites per iteration were measured and do not pay (profiles/r02_gang_variants.txt).  The barrier also reduces a predicate
+// (every warp done?) which the drain loops of the kernel use to leave together.
+#if defined(WBC_GANG) && defined(__CUDACC__)
+  WBC_DEV bool gang_bar(int done){ return __syncthreads_and(done)!=0; }
+  #define WBC_GANG_SYNC() gang_bar(0)
+#else
+  #define WBC_GANG_SYNC() do{}while(0)
+#endif
 
 // ---------------------------------------------------------------- structured A and H
 WBC_HD double Ael(const QPData& q,int i,int j){
@@ -452,7 +477,7 @@ WBC_FN void fill_R_with_H(QPWork& w,const QPCtx& c){
 // QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
 WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
-    { const double f=nFR,z=nZ; c.flops+=2*f*f*z+2*f*z*z+z*z*z/3.0; }
+    WBC_FLOPS(2.0*nFR*nFR*nZ+2.0*nFR*nZ*nZ+(double)nZ*nZ*nZ/3.0);
     WBC_SYNC();
     if(nZ==0&&c.nFX+c.nAC!=0) return QP_OK;
     if(c.nAC==0){
@@ -541,7 +566,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         WBC_SYNC();
         if(rnrm<OPT_epsIterRef) break;
     }
-    { const double a=nAC,f=nFR,z=nZ; c.flops+=(1.0+nref)*(2*a*a+4*f*a+4*f*z+4*f*f+4*z*z)+nref*(2*f*f+4*a*42.0); }
+    WBC_FLOPS((1.0+nref)*(2.0*nAC*nAC+4.0*nFR*nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+nref*(2.0*nFR*nFR+4.0*nAC*42.0)); (void)nref;
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
     LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=Acol_times(WQP,ii,w.ym); t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); w.dyFX[ii]=t; }
@@ -617,7 +642,7 @@ WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
 WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_isBound){
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nIAC=c.nIAC;
     c.tau=1.0; BC_idx=-1; BC_status=2 /*ST_UNDEFINED*/; BC_isBound=false; int tmp;
-    c.flops+=2.0*nIAC*42.0+10.0*(42+70);
+    WBC_FLOPS(2.0*nIAC*42.0+10.0*(42+70));
     WBC_SYNC();
     // I.1 active constraints' duals
     LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=-w.dyAC[i]; }
@@ -789,7 +814,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
             mx=wbc_max(mx);
             const double nrm=sqrt(l2);
             const bool sureLI=mx>LI_SURE*nrm, sureLD=mx<=LI_NONE*nrm;
-            if(sureLI||sureLD){ const double a=c.nAC,f=nFR,z=nZ; c.flops+=3.0*(2*a*a+4*f*a+4*f*z+4*f*f+4*z*z)+2.0*(2*f*f+4*a*42.0); return sureLI; }
+            if(sureLI||sureLD){ WBC_FLOPS(3.0*(2.0*c.nAC*c.nAC+4.0*nFR*c.nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+2.0*(2.0*nFR*nFR+4.0*c.nAC*42.0)); return sureLI; }
         }
         int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
         if(rv!=QP_OK) return false;
@@ -821,7 +846,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
             double mx=0.0; LANE_FOR(i,nZ) mx=fmax(mx,fabs(QQ(number,i)));
             mx=wbc_max(mx);
             const bool sureLI=mx>LI_SURE, sureLD=mx<=LI_NONE;
-            if(sureLI||sureLD){ const double a=c.nAC,f=c.nFR,z=nZ; c.flops+=3.0*(2*a*a+4*f*a+4*f*z+4*f*f+4*z*z)+2.0*(2*f*f+4*a*42.0); return sureLI; }
+            if(sureLI||sureLD){ WBC_FLOPS(3.0*(2.0*c.nAC*c.nAC+4.0*c.nFR*c.nAC+4.0*c.nFR*nZ+4.0*c.nFR*c.nFR+4.0*nZ*nZ)+2.0*(2.0*c.nFR*c.nFR+4.0*c.nAC*42.0)); return sureLI; }
         }
         LANE_FOR(j,42) w.tmpv[j]=(j==number)?1.0:0.0;
         WBC_SYNC();
@@ -904,7 +929,7 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
 // QProblem::addConstraint (QProblem.cpp:2819-2975), second half: w.wv = aFR' [Z Y] is given; new row of T, Givens chain on Z, index lists
 WBC_FN void addConstraint_tail(QPWork& w,QPCtx& c,int number,int C_status){
     const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
-    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
+    WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     LANE_FOR(j,nAC) TT(nAC,tcol+j)=w.wv[nZ+j];
     WBC_SYNC();
     if(nZ>0){
@@ -948,7 +973,7 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
     const int lane=c.lane;
     if(updateCholesky&&ensureLI){ int rv=addBound_ensureLI(w,c,number,B_status); if(rv!=QP_OK) return rv; }
     const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
-    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
+    WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
 #if !defined(__CUDACC__) && defined(WBC_QP_TRACE)
     printf("    addBound %2d  nFR %2d nAC %2d\n",number,nFR,nAC);
 #endif
@@ -971,7 +996,7 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
 // QProblem::removeConstraint (QProblem.cpp:3782-4012) without NZC test / flipper / R update (see file header)
 WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
     const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
-    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
+    WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     WBC_SYNC();
     const int number_idx=(int)w.posAC[number];
     if(number_idx<nAC-1){
@@ -994,7 +1019,7 @@ WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
 // QProblem::removeBound (QProblem.cpp:4018-4252) without NZC test / flipper / R update (see file header)
 WBC_FN int removeBound(QPWork& w,QPCtx& c,int number){
     const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
-    { const double f=nFR,z=nZ; c.flops+=6*f*z+3*z*z+2*f*42.0; }
+    WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     moveFixedToFree(w,c,number);
     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; QQ(ii,nFR)=0.0; QQ(number,i)=0.0; }
     WBC_SYNC();
@@ -1038,6 +1063,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
     c.infeasible=0; c.unbounded=0;
     for(int iter=nWSRperformed;iter<nWSR;iter++){
         c.status=QPS_PERFORMINGHOMOTOPY;
+        WBC_GANG_SYNC();
         WBC_TIC(t0);
         bool bCzero,bBzero; determineDataShift(w,c,bCzero,bBzero);
         WBC_TOC(t0,0);
@@ -1047,7 +1073,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
         int BC_idx,BC_status; bool BC_isBound;
         performStep(w,c,BC_idx,BC_status,BC_isBound);
         const bool finished=homotopyFinished(w,c);
-        WBC_TOC(t0,2); c.prof[7]++;
+        WBC_TOC(t0,2); WBC_COUNT_ITER();
         if(finished){ c.status=QPS_SOLVED; nWSR=iter; return QP_OK; }
 #if !defined(__CUDACC__) && defined(WBC_QP_TRACE)
         printf("  it %3d tau %.6e  %s %s %3d  nFX %2d nAC %2d\n",iter,c.tau,BC_status==2?"---":(BC_status==0?"REM":(BC_status<0?"ADL":"ADU")),BC_isBound?"B":"C",BC_idx,c.nFX,c.nAC);
@@ -1135,11 +1161,15 @@ WBC_DEV void store_prebuilt_TQ(const QPWork& w,const QPCtx& c,QPPre& p){
     LANE_FOR(i,42*LD) p.Q[i]=w.Q[i];
     LANE_FOR(i,nT) p.T[i]=w.RT[i];
     LANE_FOR(i,70){ p.AC[i]=w.AC[i]; p.IAC[i]=w.IAC[i]; p.cstat[i]=w.cstat[i]; p.posAC[i]=w.posAC[i]; }
-    if(lane==0){ p.nAC=c.nAC; p.nIAC=c.nIAC; p.flops=c.flops; }
+    if(lane==0){ p.nAC=c.nAC; p.nIAC=c.nIAC;
+#if defined(WBC_PROFILE)
+        p.flops=c.flops;
+#endif
+    }
 }
 WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
     const int lane=c.lane;
-    c.nFR=42; c.nFX=0; c.nAC=p.nAC; c.nIAC=p.nIAC; c.frIdentity=1; c.flops+=p.flops;
+    c.nFR=42; c.nFX=0; c.nAC=p.nAC; c.nIAC=p.nIAC; c.frIdentity=1; WBC_FLOPS(p.flops);
     const int nT=tri(c.nAC);
 #if WBC_NL==1
     LANE_FOR(i,70){ w.AC[i]=p.AC[i]; w.IAC[i]=p.IAC[i]; w.cstat[i]=p.cstat[i]; w.posAC[i]=p.posAC[i]; }
@@ -1178,7 +1208,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
     const int lane=c.lane;
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
-    c.flops+=4.0*42*42+4.0*70*42;
+    WBC_FLOPS(4.0*42*42+4.0*70*42);
     LANE_FOR(i,70){ double ax=Arow_times(WQP,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again

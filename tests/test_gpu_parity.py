@@ -125,16 +125,15 @@ def test_three_methods_equal_step_and_reset_restarts(wbc, wl):
     a.close(); b.close()
 
 
-def test_two_kernel_warm_start_is_bit_identical_to_the_single_kernel_path(wbc, wl, monkeypatch):
-    """The TQ rebuild of the warm start runs as a kernel of its own ahead of the solve (wbc_warm_setup_kernel); WBC_QP_SPLIT=0 keeps it
+def test_two_kernel_warm_start_is_bit_identical_to_the_single_kernel_path(wbc, wl):
+    """The TQ rebuild of the warm start runs as a kernel of its own ahead of the solve (wbc_warm_setup_kernel); wbc_set_option("warm_start_split", 0) keeps it
     inside the solve kernel.  Same functions, same arithmetic: every output of every tick must be bit-identical, also for robots that are
     reset (cold) in the middle of the sequence while the others stay warm."""
     n = 192
     st, ref = wl.randomised(n, seed=7, contacts="mixed", switching_frac=0.1)
     outs = []
-    for split in ("1", "0"):
-        monkeypatch.setenv("WBC_QP_SPLIT", split)
-        ctl = wbc.WholeBodyController(n); s = st; rec = []
+    for split in (1, 0):
+        ctl = wbc.WholeBodyController(n); ctl.setOption("warm_start_split", split); s = st; rec = []
         for t in range(4):
             if t:
                 s = wl.advance_state(s)
@@ -148,16 +147,15 @@ def test_two_kernel_warm_start_is_bit_identical_to_the_single_kernel_path(wbc, w
     assert (outs[0][2]["nwsr"][40:90] >= 40).all()                    # the reset robots did cold-start at tick 2
 
 
-def test_warm_setup_kernel_stays_inside_its_workspace_prefix(wbc, wl, monkeypatch):
-    """wbc_warm_setup_kernel allocates only the first QPWORK_TQ_BYTES of the solver workspace.  With WBC_QP_SETUP_CANARY=1 it is launched with the whole
+def test_warm_setup_kernel_stays_inside_its_workspace_prefix(wbc, wl):
+    """wbc_warm_setup_kernel allocates only the first QPWORK_TQ_BYTES of the solver workspace.  With wbc_set_option("setup_canary", 1) it is launched with the whole
     workspace, the part past the prefix is filled with a NaN pattern and checked at the end: a read from there poisons the factorisation, a write
     makes the kernel poison it on purpose -- either way the outputs would differ from the normal run (compute-sanitizer is not available on the pool)."""
     n = 256
     st, ref = wl.stress(n)
     outs = []
-    for canary in ("0", "1"):
-        monkeypatch.setenv("WBC_QP_SETUP_CANARY", canary)
-        ctl = wbc.WholeBodyController(n); s = st; rec = []
+    for canary in (0, 1):
+        ctl = wbc.WholeBodyController(n); ctl.setOption("setup_canary", canary); s = st; rec = []
         for t in range(3):
             if t:
                 s = wl.advance_state(s)

@@ -7,7 +7,7 @@ from quadrupedwholebodycontroller_b200 import workloads as wl
 
 def run(N, contacts, ticks=2, check=False):
     st, ref = wl.randomised(N, seed=1234, contacts=contacts)
-    ctl = wbc.WholeBodyController(N); ctl.profile(True)
+    ctl = wbc.WholeBodyController(N, profiling=True); ctl.profile(True)
     if check:
         from oracle import oracle as orc
         ob = orc.OracleBatch(N)

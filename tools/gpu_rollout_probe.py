@@ -8,7 +8,7 @@ from quadrupedwholebodycontroller_b200 import workloads as wl
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 400
 st, ref, cmd = wl.rollout_start(N)
-ctl = wbc.WholeBodyController(N); ctl.plannerCreate(); ctl.plantEnable(); ctl.profile(True)
+ctl = wbc.WholeBodyController(N, profiling=True); ctl.plannerCreate(); ctl.plantEnable(); ctl.profile(True)
 ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.plannerSetCmdVel(cmd[0].copy(), cmd[1].copy(), cmd[2].copy())
 ctl.rollout(1); ctl.synchronize(); print("cold tick", ctl.lastKernelMs())
 rows = []
