@@ -150,6 +150,10 @@ int wbc_rollout(wbc_handle* h, int ticks, int planner_every);
 /* per-robot rollout statistics since the last reset: control ticks, ticks whose solve did not return 0, sum and max of nWSR */
 int wbc_rollout_stats(wbc_handle* h, int* ticks, int* failed_ticks, int* nwsr_sum, int* nwsr_max, int reset);
 
+/* Verification build only (libwbc_b200_exact.so, -DWBC_EXACT -fmad=false: qpOASES' arithmetic operation by operation, bit-identical iterates):
+ * out3 = { full linear-independence tests run (QProblem.cpp:2998-3072, 3500-3570), tests inside the undecided band of the product build's shortcut,
+ * tests whose verdict the shortcut would have got wrong }.  Other builds return WBC_ERR_ARG. */
+int wbc_debug_counters(wbc_handle* h, unsigned long long* out3, int reset);
 int wbc_num_robots(const wbc_handle* h);
 /* number of kernel launches issued by this handle so far (bench.py reports it as gpu_launches) */
 long long wbc_launch_count(const wbc_handle* h);

@@ -138,6 +138,22 @@ void orc_qp_sequence(int T,const double* H,const double* g,const double* A,const
     }
 }
 
+// same with an iteration limit PER QP (debugging aid: the iterate after k working-set changes of a hot start is read back after RET_MAX_NWSR_REACHED)
+void orc_qp_sequence_nwsr(int T,const double* H,const double* g,const double* A,const double* lbA,const double* ubA,const int* nWSRmax,
+                          double* x,double* y,signed char* ws,int* rc,int* nwsr){
+    qpOASES::SQProblem qp(42,70);
+    for(int t=0;t<T;t++){
+        qpOASES::int_t nWSR=nWSRmax[t]; qpOASES::Options o; o.setToReliable(); o.printLevel=qpOASES::PL_LOW; qp.setOptions(o);
+        int r = (t==0) ? qp.init(H+t*1764,g+t*42,A+t*2940,nullptr,nullptr,lbA+t*70,ubA+t*70,nWSR,0)
+                       : qp.hotstart(H+t*1764,g+t*42,A+t*2940,nullptr,nullptr,lbA+t*70,ubA+t*70,nWSR,0);
+        rc[t]=r; nwsr[t]=(int)nWSR;
+        double xs[42]={0},ys[112]={0},w[112]={0};
+        qp.getPrimalSolution(xs); qp.getDualSolution(ys); qp.getWorkingSet(w);
+        for(int k=0;k<42;k++) x[t*42+k]=xs[k];
+        for(int k=0;k<112;k++){ y[t*112+k]=ys[k]; ws[t*112+k]=(signed char)w[k]; }
+    }
+}
+
 // ---- restated MotionPlanner (planner_oracle.cpp): K planner periods of ONE planner; cmd[K][3] = (linear.x, linear.y, angular.z) per period.
 // out: published[K] (bytes), msg[K][54] = pose6 vel6 acc6 swPos12 swVel12 swAcc12 (the latched ref_msg_ at the end of the period), contacts[K][4]
 void orc_planner_run(const double* params8,int K,const double* cmd,unsigned char* published,double* msg,unsigned char* contacts){

@@ -9,7 +9,7 @@ import os
 
 import numpy as np
 
-from .build import build_library, LIB_PATH, PROF_LIB_PATH
+from .build import build_library, LIB_PATH, PROF_LIB_PATH, EXACT_LIB_PATH
 
 NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC = 12, 4, 42, 70          # whole_body_controller.hpp:27-32 of the reference
 _libs = {}
@@ -17,7 +17,7 @@ _libs = {}
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
            "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
            "wbc_planner_default_params", "wbc_planner_create", "wbc_planner_reset", "wbc_planner_set_cmd_vel", "wbc_planner_tick", "wbc_get_reference",
-           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option"]
+           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option", "wbc_debug_counters"]
 
 
 class WbcParams(C.Structure):
@@ -32,9 +32,10 @@ class WbcPlannerParams(C.Structure):
                                           "body_final_velocity", "dt")]
 
 
-def load_library(profiling=False):
-    """dlopen the CUDA library (profiling=True: the -DWBC_PROFILE build of the same sources); raises if it has not been built (no fallback of any kind)."""
-    path = PROF_LIB_PATH if profiling else LIB_PATH
+def load_library(profiling=False, exact=False):
+    """dlopen the CUDA library (profiling=True: the -DWBC_PROFILE build of the same sources; exact=True: the -DWBC_EXACT verification build that
+    reproduces qpOASES' arithmetic operation by operation); raises if it has not been built (no fallback of any kind)."""
+    path = EXACT_LIB_PATH if exact else (PROF_LIB_PATH if profiling else LIB_PATH)
     if path not in _libs:
         if not os.path.exists(path):
             raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
@@ -68,6 +69,7 @@ def load_library(profiling=False):
         lib.wbc_warm_start_split.argtypes = [C.c_void_p]
         lib.wbc_rollout_stats.argtypes = [C.c_void_p] + [C.c_void_p] * 4 + [C.c_int]
         lib.wbc_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        lib.wbc_debug_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         _libs[path] = lib
     return _libs[path]
 
@@ -100,8 +102,8 @@ class WholeBodyController:
 
     numberOfJoints, numberOfLegs, qpNumberOfVariables, qpNumberOfConstraints = NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC
 
-    def __init__(self, n_robots, device=0, params=None, stream=None, profiling=False):
-        lib = self._lib = load_library(profiling)
+    def __init__(self, n_robots, device=0, params=None, stream=None, profiling=False, exact=False):
+        lib = self._lib = load_library(profiling, exact)
         self.N = int(n_robots)
         self._h = C.c_void_p()
         p = params if params is not None else default_params()
@@ -164,6 +166,10 @@ class WholeBodyController:
     def setOption(self, key, value):
         """explicit switches for tests / measurements (wbc_set_option): warm_start_split, cohort, setup_canary"""
         self._ck(self._lib.wbc_set_option(self._h, key.encode(), int(value)))
+
+    def debugCounters(self, reset=False):
+        """exact build only: (full LI tests run, inside the shortcut's undecided band, shortcut verdict wrong)"""
+        out = np.zeros(3, np.uint64); self._ck(self._lib.wbc_debug_counters(self._h, _ptr(out), int(reset))); return out
 
     def warmStartSplit(self):
         return bool(self._lib.wbc_warm_start_split(self._h))

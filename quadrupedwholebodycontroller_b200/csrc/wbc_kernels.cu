@@ -586,6 +586,20 @@ extern "C" int wbc_rollout_stats(wbc_handle* h,int* ticks,int* failed_ticks,int*
     if(reset) CK(cudaMemsetAsync(h->stats,0,4*N*sizeof(int),h->stream));
     return WBC_OK;
 }
+// exact build (-DWBC_EXACT): [0] full linear-independence tests run, [1] of them inside the undecided band of the product build's |Z'a| shortcut,
+// [2] tests whose verdict the shortcut would have got wrong (must stay 0).  Other builds: WBC_ERR_ARG.
+extern "C" int wbc_debug_counters(wbc_handle* h,unsigned long long* out3,int reset){
+    if(!h||!out3) return WBC_ERR_ARG;
+#if defined(WBC_EXACT)
+    CK(cudaSetDevice(h->device)); CK(cudaStreamSynchronize(h->stream));
+    unsigned long long v[4]={0,0,0,0}; CK(cudaMemcpyFromSymbol(v,g_wbc_li,sizeof(v)));
+    out3[0]=v[0]; out3[1]=v[1]; out3[2]=v[2];
+    if(reset){ const unsigned long long z[4]={0,0,0,0}; CK(cudaMemcpyToSymbol(g_wbc_li,z,sizeof(z))); }
+    return WBC_OK;
+#else
+    (void)reset; h->err="wbc_debug_counters: only in the exact build (libwbc_b200_exact.so, -DWBC_EXACT)"; return WBC_ERR_ARG;
+#endif
+}
 extern "C" int wbc_num_robots(const wbc_handle* h){ return h?h->N:0; }
 extern "C" int wbc_warm_start_split(const wbc_handle* h){ return (h&&h->split)?1:0; }
 // explicit switches (tests, measurements); every setting gives bit-identical results

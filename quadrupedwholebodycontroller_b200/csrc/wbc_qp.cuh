@@ -23,11 +23,19 @@
 #pragma once
 #include "wbc_common.cuh"
 #include <cstddef>
-#if !defined(__CUDACC__) && (defined(WBC_QP_TRACE) || defined(WBC_LI_STATS))
+#if !defined(__CUDACC__) && (defined(WBC_QP_TRACE) || defined(WBC_LI_STATS) || defined(WBC_QP_DBG))
 #include <cstdio>
+#include <cstdlib>
 #endif
 
 namespace wbc {
+#if !defined(__CUDACC__) && defined(WBC_QP_DBG)      // host emulation only: dump of the step-direction intermediates of one iteration (tools/host_emul)
+static int g_dbg_iter=-1;
+static int dbg_target(){ static int t=-2; if(t==-2){ const char* e=getenv("DBG_ITER"); t=e?atoi(e):-1; } return t; }
+#define WBC_DBG_VEC(name,expr,len) if(g_dbg_iter==dbg_target()){ printf("REF %s",name); for(int i_=0;i_<(len);i_++){ const int i=i_; printf(" %a",(double)(expr)); } printf("\n"); }
+#else
+#define WBC_DBG_VEC(name,expr,len) do{}while(0)
+#endif
 
 // qpOASES returnValue numbering (MessageHandling.hpp) for the codes this path can produce
 enum : int { QP_OK=0, QP_RET_DIV_BY_ZERO=1, QP_RET_INIT_FAILED=33, QP_RET_INIT_FAILED_CHOLESKY=35, QP_RET_INIT_FAILED_HOTSTART=36,
@@ -63,6 +71,38 @@ constexpr int TRI42=42*43/2;
 WBC_HD int tri(int i){ return (i*(i+1))>>1; }
 #define RR(i,j) w.RT[TRI42-1-(tri(j)+(i))]
 #define TT(i,j) w.RT[tri(i)+(SIZET-1-(j))]
+// Arithmetic deviations from qpOASES, all at the level of one rounding: triangular solves and DPOTRF multiply by a
+// precomputed reciprocal of the diagonal where the reference divides (a divide is ~10 multiplies of latency on the critical path of every
+// substitution step), the Givens chains of addConstraint / addBound come from prefix sums of squares instead of the serial hypot recurrence,
+// and nvcc contracts a*b+c into FMAs.  -DWBC_EXACT (libwbc_b200_exact.so, built with -fmad=false) removes all three: that build walks the
+// SAME iteration path as the reference library on every tick, including the zero-length steps whose ramping / drift-correction branch is
+// decided by rounding noise (tests/test_gpu_pinned_parity.py requires 100 % equal nWSR and working sets from it).
+#if defined(WBC_EXACT)
+  #define WBC_EXACT_DIV
+  #define WBC_EXACT_GIVENS
+  #define WBC_EXACT_BACKSUB
+#endif
+#if defined(WBC_EXACT_DIV)
+  #define WBC_RDIAG(d) (d)
+  #define WBC_BYDIAG(s,r) ((s)/(r))
+#else
+  #define WBC_RDIAG(d) (1.0/(d))
+  #define WBC_BYDIAG(s,r) ((s)*(r))
+#endif
+#if defined(WBC_EXACT)
+  #define WBC_FNMA(l,a,s) ((s)-(l)*(a))
+#else
+  #define WBC_FNMA(l,a,s) fma(-(l),(a),(s))
+#endif
+// Exact build only: the reference's full linear-independence test (a whole step-direction solve) is run on EVERY add, next to the |Z'a|
+// shortcut of the product build, and the two verdicts are compared: [0] tests, [1] tests inside the shortcut's undecided band, [2] disagreements.
+#if defined(WBC_EXACT) && defined(__CUDACC__)
+  __device__ unsigned long long g_wbc_li[4];
+  #define WBC_LI_COUNT(k) { if(lane==0) atomicAdd(&g_wbc_li[k],1ull); }
+#elif defined(WBC_EXACT)
+  static unsigned long long g_wbc_li[4];
+  #define WBC_LI_COUNT(k) { g_wbc_li[k]++; }
+#endif
 // measurement code (clock64 phase timers, algorithmic-flop counter) exists only in the profiling build (-DWBC_PROFILE -> libwbc_b200_prof.so)
 #if defined(WBC_PROFILE) && defined(__CUDACC__)
   #define WBC_TIC(t) long long t=clock64()
@@ -169,34 +209,40 @@ WBC_HD double Hel(const QPData& q,int i,int j){
 }
 WBC_FN double Ael_dev(const QPData& q,int i,int j){ return Ael(q,i,j); }       // ONE device copy of the element decoder
 // Structured products with A (whole_body_controller.cpp:492-497): no per-element decoding, only the non-zero blocks.
-// Arow_times: (A v)_i for a 42-vector v (callers mask v to the free / fixed columns beforehand, 0-entries add exactly 0).
-WBC_FN double Arow_times(const QPData& q,int i,const double* v){
-    double s=0;
-    if(i<6){ for(int j=0;j<6;j++) s+=q.Mbb[6*i+j]*v[j]; for(int f=0;f<12;f++) s-=(q.cmask[f/3]*q.Jc[18*f+i])*v[18+f]; return s; }
-    if(i<18){ const int r=i-6; const double c=q.cmask[r/3]; if(c==0.0) return 0.0; for(int j=0;j<18;j++) s+=q.Jc[18*r+j]*v[j]; return s; }
-    if(i<34){ const int r=i-18,l=r>>2,k=r&3; const double c=q.cmask[l]; if(c==0.0) return 0.0; const double* f=v+18+3*l;
-              return ((k&1)?-f[k>>1]:f[k>>1])-q.mu*f[2]; }
-    if(i<46){ const int r=i-34; for(int j=0;j<12;j++) s+=q.Mjj[12*r+j]*v[6+j]; for(int f=0;f<12;f++) s-=(q.cmask[f/3]*q.Jc[18*f+6+r])*v[18+f]; return s; }
-    { const int r=(i<58)?i-46:i-58; const double c=1.0-q.cmask[r/3]; if(c!=0.0) for(int j=0;j<18;j++) s+=q.Jc[18*r+j]*v[j]; return (i<58)? s-v[30+r] : s+v[30+r]; }
+// All of them ACCUMULATE ONTO THE GIVEN VALUE term by term, y <- y + sgn*a_ij*v_j in ascending j, which is what the reference's dense
+// loops do (DenseMatrix::times / transTimes with index lists, Matrices.cpp:332-590, and the DGEMM replacement, BLASReplacement.cpp:36-92:
+// `y[.] += val*x` / `y[.] -= val*x` onto the existing y; zero entries of the dense row add exactly 0).  sgn is +1.0 or -1.0 exactly,
+// so (sgn*a)*v == +-(a*v) bit for bit.
+// Arow_acc: y + sgn*(A v)_i for a 42-vector v (callers mask v to the free / fixed columns beforehand: the reference visits the selected columns only).
+WBC_FN double Arow_acc(const QPData& q,int i,const double* v,double y,double sgn){
+    if(i<6){ for(int j=0;j<6;j++) y+=(sgn*q.Mbb[6*i+j])*v[j]; for(int f=0;f<12;f++) y-=(sgn*(q.cmask[f/3]*q.Jc[18*f+i]))*v[18+f]; return y; }
+    if(i<18){ const int r=i-6; const double c=q.cmask[r/3]; if(c==0.0) return y; for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return y; }
+    if(i<34){ const int r=i-18,l=r>>2,k=r&3; const double c=q.cmask[l]; if(c==0.0) return y; const double* f=v+18+3*l;
+              const double d=(k&1)?-sgn:sgn;
+              if(k<2){ y+=d*f[0]; } else { y+=d*f[1]; }
+              return y-(sgn*q.mu)*f[2]; }
+    if(i<46){ const int r=i-34; for(int j=0;j<12;j++) y+=(sgn*q.Mjj[12*r+j])*v[6+j]; for(int f=0;f<12;f++) y-=(sgn*(q.cmask[f/3]*q.Jc[18*f+6+r]))*v[18+f]; return y; }
+    { const int r=(i<58)?i-46:i-58; const double c=1.0-q.cmask[r/3]; if(c!=0.0) for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return (i<58)? y-sgn*v[30+r] : y+sgn*v[30+r]; }
 }
-// Acol_times: (A' y)_j for a 70-vector y by constraint number (0 for inactive constraints), rows visited in ascending order
-WBC_FN double Acol_times(const QPData& q,int j,const double* y){
-    double s=0;
+// Acol_acc: y + sgn*(A' yv)_j for a 70-vector yv by constraint number (0 for inactive constraints), rows visited in ascending order
+WBC_FN double Acol_acc(const QPData& q,int j,const double* yv,double y,double sgn){
     if(j<18){
-        if(j<6) for(int i=0;i<6;i++) s+=q.Mbb[6*i+j]*y[i];
-        for(int r=0;r<12;r++) s+=(q.cmask[r/3]*q.Jc[18*r+j])*y[6+r];
-        if(j>=6) for(int r=0;r<12;r++) s+=q.Mjj[12*r+(j-6)]*y[34+r];
-        for(int r=0;r<12;r++) s+=((1.0-q.cmask[r/3])*q.Jc[18*r+j])*y[46+r];
-        for(int r=0;r<12;r++) s+=((1.0-q.cmask[r/3])*q.Jc[18*r+j])*y[58+r];
-        return s;
+        if(j<6) for(int i=0;i<6;i++) y+=(sgn*q.Mbb[6*i+j])*yv[i];
+        for(int r=0;r<12;r++) y+=(sgn*(q.cmask[r/3]*q.Jc[18*r+j]))*yv[6+r];
+        if(j>=6) for(int r=0;r<12;r++) y+=(sgn*q.Mjj[12*r+(j-6)])*yv[34+r];
+        for(int r=0;r<12;r++) y+=(sgn*((1.0-q.cmask[r/3])*q.Jc[18*r+j]))*yv[46+r];
+        for(int r=0;r<12;r++) y+=(sgn*((1.0-q.cmask[r/3])*q.Jc[18*r+j]))*yv[58+r];
+        return y;
     }
     if(j<30){ const int f=j-18,l=f/3,c=f-3*l; const double cf=q.cmask[l];
-        for(int i=0;i<6;i++) s-=(cf*q.Jc[18*f+i])*y[i];
-        const double* yf=y+18+4*l;
-        if(c==2) s+=cf*(-q.mu)*(yf[0]+yf[1]+yf[2]+yf[3]); else s+=cf*(yf[2*c]-yf[2*c+1]);
-        for(int r=0;r<12;r++) s-=(cf*q.Jc[18*f+6+r])*y[34+r];
-        return s; }
-    return y[58+(j-30)]-y[46+(j-30)];
+        for(int i=0;i<6;i++) y-=(sgn*(cf*q.Jc[18*f+i]))*yv[i];
+        const double* yf=yv+18+4*l;
+        if(c==2){ const double m=sgn*(cf*q.mu); y-=m*yf[0]; y-=m*yf[1]; y-=m*yf[2]; y-=m*yf[3]; }
+        else { const double d=sgn*cf; y+=d*yf[2*c]; y-=d*yf[2*c+1]; }
+        for(int r=0;r<12;r++) y-=(sgn*(cf*q.Jc[18*f+6+r]))*yv[34+r];
+        return y; }
+    y-=sgn*yv[46+(j-30)];
+    return y+sgn*yv[58+(j-30)];
 }
 // (H v)_i over the free (sel 0), fixed (sel 1) or all (sel 2) variables.  H = blkdiag(I6, I12, Hff, rho I12): only the 12 force rows
 // have off-diagonal terms; `fm` = bit mask of the force variables selected by `sel` (force_mask), terms are added in ascending
@@ -208,13 +254,13 @@ WBC_DEV unsigned force_mask(const QPWork& w,const QPCtx& c,int sel){
     return wbc_ballot(c.lane<12&&(sel==2||((w.bstat[18+(c.lane<12?c.lane:0)]!=0)==(sel==1))));
 #endif
 }
-WBC_FN double Hrow_dot(const QPWork& w,int i,const double* v,int sel,unsigned fm){
-    if(i>=18&&i<30){ const double* h=&WQP.Hff[i-18]; double s=0.0;
+WBC_FN double Hrow_acc(const QPWork& w,int i,const double* v,int sel,unsigned fm,double y,double sgn){
+    if(i>=18&&i<30){ const double* h=&WQP.Hff[i-18];
         #pragma unroll
-        for(int u=0;u<12;u++) if((fm>>u)&1u) s+=h[12*u]*v[18+u];
-        return s; }
-    if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return 0.0;
-    return ((i>=30)?WQP.rho:1.0)*v[i];
+        for(int u=0;u<12;u++) if((fm>>u)&1u) y+=(sgn*h[12*u])*v[18+u];
+        return y; }
+    if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return y;
+    return y+(sgn*((i>=30)?WQP.rho:1.0))*v[i];
 }
 // masked copies: vm = v restricted to free (sel 0) / fixed (sel 1) variables; ym = yAC scattered to constraint numbers
 WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
@@ -323,40 +369,40 @@ WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,in
     (void)lane; double u[42];
     for(int k=0;k<n;k++){ double sum=b[k*bs]; int off=trisolve_row0(kind,n,k), d=d0;
         for(int j=0;j<k;j++){ sum-=RT[off]*u[j]; off+=d; d+=dd; }
-        u[k]=sum*rd[k*rs]; }
+        u[k]=WBC_BYDIAG(sum,rd[k*rs]); }
     for(int k=0;k<n;k++) a[k*as]=u[k];
 #else
     const bool in0=lane<n, in1=lane+32<n;
     const unsigned L=wbc_saddr(RT);                           // 32-bit shared address of the packed R/T buffer (read-only here)
     int o0=in0?trisolve_row0(kind,n,lane):0, d=d0;
-    double s0=in0?b[lane*bs]:0.0, r0=in0?rd[lane*rs]:0.0, l0=(in0&&lane>0)?wbc_lds(L+8u*o0):0.0;
+    double s0=in0?b[lane*bs]:0.0, r0=in0?rd[lane*rs]:1.0, l0=(in0&&lane>0)?wbc_lds(L+8u*o0):0.0;
     WBC_SYNC();                                              // a may alias b
     // l0 is loaded as 0 for lanes <= k, so the update needs no predicate and a finished lane keeps its final sum: u_k = s0*r0 is
     // formed for the broadcast at step k and once more, from the same operands, for the store after the loop.
     if(n<=32){
         #pragma unroll 2
         for(int k=0;k<n;k++){
-            const double ak=__shfl_sync(0xffffffffu,s0*r0,k);
+            const double ak=__shfl_sync(0xffffffffu,WBC_BYDIAG(s0,r0),k);
             o0+=d; d+=dd;
             const double nl=(lane>k+1&&in0)?wbc_lds(L+8u*o0):0.0;   // next column's entry, independent of the chain
-            s0=fma(-l0,ak,s0);
+            s0=WBC_FNMA(l0,ak,s0);
             l0=nl;
         }
-        if(in0) a[lane*as]=s0*r0;
+        if(in0) a[lane*as]=WBC_BYDIAG(s0,r0);
     } else {
         int o1=in1?trisolve_row0(kind,n,lane+32):0;
-        double s1=in1?b[(lane+32)*bs]:0.0, r1=in1?rd[(lane+32)*rs]:0.0, l1=in1?wbc_lds(L+8u*o1):0.0;
+        double s1=in1?b[(lane+32)*bs]:0.0, r1=in1?rd[(lane+32)*rs]:1.0, l1=in1?wbc_lds(L+8u*o1):0.0;
         #pragma unroll 2
         for(int k=0;k<n;k++){
-            const double mine=(k<32)?s0*r0:s1*r1;
+            const double mine=(k<32)?WBC_BYDIAG(s0,r0):WBC_BYDIAG(s1,r1);
             const double ak=__shfl_sync(0xffffffffu,mine,k&31);
             o0+=d; o1+=d; d+=dd;
             const double nl0=(lane>k+1&&in0)?wbc_lds(L+8u*o0):0.0, nl1=(lane+32>k+1&&in1)?wbc_lds(L+8u*o1):0.0;
-            s0=fma(-l0,ak,s0); s1=fma(-l1,ak,s1);
+            s0=WBC_FNMA(l0,ak,s0); s1=WBC_FNMA(l1,ak,s1);
             l0=nl0; l1=nl1;
         }
-        a[lane*as]=s0*r0;
-        if(in1) a[(lane+32)*as]=s1*r1;
+        a[lane*as]=WBC_BYDIAG(s0,r0);
+        if(in1) a[(lane+32)*as]=WBC_BYDIAG(s1,r1);
     }
 #endif
     WBC_SYNC();
@@ -364,7 +410,7 @@ WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,in
 // reciprocals of T's diagonal TT(k, sizeT-1-k); false if a pivot fails the |.| > EPS test of QProblem::backsolveT
 WBC_FN bool prepare_T(QPWork& w,const QPCtx& c){
     const int lane=c.lane; bool bad=false; WBC_SYNC();
-    LANE_FOR(k,c.nAC){ const double d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=1.0/d; }
+    LANE_FOR(k,c.nAC){ const double d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=WBC_RDIAG(d); }
     WBC_SYNC();
     return wbc_ballot(bad)==0u;
 }
@@ -379,8 +425,16 @@ WBC_DEV void backsolveT(QPWork& w,const QPCtx& c,const double* b,bool transposed
 // QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b.  w.rdR = 1/diag(R).
 WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a,int nR){
     if(nR<=0) return;
-    if(transposed) trisolve(c.lane,2,nR,w.RT,b,1,a,1,w.rdR,1);
-    else           trisolve(c.lane,3,nR,w.RT,b+nR-1,-1,a+nR-1,-1,w.rdR+nR-1,-1);
+    if(transposed){ trisolve(c.lane,2,nR,w.RT,b,1,a,1,w.rdR,1); return; }
+#if defined(WBC_EXACT_BACKSUB)
+    // The reference's back substitution subtracts the terms of row i in ASCENDING column order j = i+1 .. nR-1, i.e. starting with the unknown
+    // it has only just computed: a serial chain of nR^2/2 operations that the streaming form below (terms in the order the unknowns become
+    // available: j = nR-1 down to i+1) re-orders.  Exact build: the serial form, every lane redundantly, lane 0 stores.
+    { const int lane=c.lane; WBC_SYNC();
+      for(int i=nR-1;i>=0;--i){ double sum=b[i]; for(int j=i+1;j<nR;++j) sum-=RR(i,j)*a[j]; const double v=WBC_BYDIAG(sum,w.rdR[i]); WBC_SYNC(); if(lane==0) a[i]=v; WBC_SYNC(); } }
+#else
+    trisolve(c.lane,3,nR,w.RT,b+nR-1,-1,a+nR-1,-1,w.rdR+nR-1,-1);
+#endif
 }
 
 // ---------------------------------------------------------------- factorisations
@@ -402,8 +456,8 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
     for(int i=0;i<n;i++){
         double sum=RR(i,i); for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);
         if(!(sum>0.0)) return false;
-        const double d=sqrt(sum), rd=1.0/d; RR(i,i)=d; w.rdR[i]=rd;
-        for(int j=i+1;j<n;j++){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=s2*rd; }
+        const double d=sqrt(sum), rd=WBC_RDIAG(d); RR(i,i)=d; w.rdR[i]=rd;
+        for(int j=i+1;j<n;j++){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=WBC_BYDIAG(s2,rd); }
     }
 #else
     // lane t owns columns t and t+32 for the whole factorisation (fixed pointers, no per-row index arithmetic); packed column j lives
@@ -424,10 +478,10 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
         }
         const double sum=wbc_bcast((i<32)?s0:s1,i&31);
         if(!(sum>0.0)) return false;
-        const double d=sqrt(sum), rd=1.0/d;
+        const double d=sqrt(sum), rd=WBC_RDIAG(d);
         if(lane==(i&31)){ if(i<32) c0[-i]=d; else c1[-i]=d; w.rdR[i]=rd; }
-        if(own0&&lane>i) c0[-i]=s0*rd;
-        if(own1&&lane+32>i) c1[-i]=s1*rd;
+        if(own0&&lane>i) c0[-i]=WBC_BYDIAG(s0,rd);
+        if(own1&&lane+32>i) c1[-i]=WBC_BYDIAG(s1,rd);
         ci-=i+1;                                                // tri(i+1)-tri(i)
         WBC_SYNC();
     }
@@ -527,15 +581,15 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
             if(nAC>0){
                 if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=0.0; WBC_SYNC(); }
                 else {
-                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]-=Arow_times(WQP,(int)w.AC[i],w.vm); WBC_SYNC(); }
+                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-1.0); WBC_SYNC(); }
                     backsolveT(w,c,w.tB,false,w.xFRy);
                     Q_times(w,c,nZ,nAC,w.xFRy,w.xTMP,nullptr);
                 }
             }
             LANE_FOR(i,nZ) w.xFRz[i]=0.0;
             // HMX*delta_xFX and HFR*delta_xFRy into tempA
-            if(!bBzero&&r==0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.dx,1,fxm); } WBC_SYNC(); }
-            if(nAC>0&&(!bCzero||!bBzero)){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.xTMP,0,ffm); } }
+            if(!bBzero&&r==0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.dx,1,fxm,w.tA[ii],1.0); } WBC_SYNC(); }
+            if(nAC>0&&(!bCzero||!bBzero)){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.xTMP,0,ffm,w.tA[ii],1.0); } }
             WBC_SYNC();
             if(nZ>0){
                 Qt_times(w,c,0,nZ,w.tA,-1.0,w.xFRz);
@@ -546,7 +600,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         }
         // III) delta_yAC
         if(nAC>0){
-            if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]+=Hrow_dot(w,ii,w.Zdz,0,ffm); } WBC_SYNC(); }
+            if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.Zdz,0,ffm,w.tA[ii],1.0); } WBC_SYNC(); }
             Qt_times(w,c,nZ,nAC,w.tA,1.0,w.tB);
             backsolveT(w,c,w.tB,true,w.yTMP);
         }
@@ -559,18 +613,28 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         // residuals for the next refinement pass
         double rnrm=0.0;
         scatter_yAC(w,c,w.dyAC);
-        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); t-=Acol_times(WQP,ii,w.ym); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,1.0); t=Hrow_acc(w,ii,w.dx,1,fxm,t,1.0); t=Acol_acc(WQP,ii,w.ym,t,-1.0); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        // bA - A_FR dx_FR - A_FX dx_FX: the free columns first, then the fixed ones, each accumulated onto tempB (QProblem.cpp:4934-4935)
+        mask_vars(w,c,w.dx,0);
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= (bCzero||!dlbA)?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
-            t-=Arow_times(WQP,ii,w.dx); w.tB[i]=t; rnrm=fmax(rnrm,fabs(t)); }
+            w.tB[i]=Arow_acc(WQP,ii,w.vm,t,-1.0); }
+        if(!bBzero&&dlb){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-1.0); }
+        LANE_FOR(i,nAC) rnrm=fmax(rnrm,fabs(w.tB[i]));
         rnrm=wbc_max(rnrm);
+#if !defined(__CUDACC__) && defined(WBC_QP_DBG)
+        if(g_dbg_iter==dbg_target()) printf("REF pass %d rnrm %a\n",r,rnrm);
+#endif
+        WBC_DBG_VEC("tmpxFR",w.xTMP[(int)w.FR[i]],nFR); WBC_DBG_VEC("xFRz",w.xFRz[i],nZ); WBC_DBG_VEC("xFRy",w.xFRy[i],nAC);
+        WBC_DBG_VEC("resA",w.tA[(int)w.FR[i]],nFR); WBC_DBG_VEC("resB",w.tB[i],nAC);
         WBC_SYNC();
         if(rnrm<OPT_epsIterRef) break;
     }
     WBC_FLOPS((1.0+nref)*(2.0*nAC*nAC+4.0*nFR*nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+nref*(2.0*nFR*nFR+4.0*nAC*42.0)); (void)nref;
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t-=Acol_times(WQP,ii,w.ym); t+=Hrow_dot(w,ii,w.dx,0,ffm); t+=Hrow_dot(w,ii,w.dx,1,fxm); w.dyFX[ii]=t; }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t=Acol_acc(WQP,ii,w.ym,t,-1.0); t=Hrow_acc(w,ii,w.dx,0,ffm,t,1.0); t=Hrow_acc(w,ii,w.dx,1,fxm,t,1.0); w.dyFX[ii]=t; }
     WBC_SYNC();
+    WBC_DBG_VEC("dxFR",w.dx[(int)w.FR[i]],nFR); WBC_DBG_VEC("dyAC",w.dyAC[i],nAC); WBC_DBG_VEC("dyFX",w.dyFX[(int)w.FX[i]],nFX); WBC_DBG_VEC("dxFX",w.dx[(int)w.FX[i]],nFX);
     return QP_OK;
 }
 
@@ -634,8 +698,8 @@ WBC_FN bool homotopyFinished(const QPWork& w,const QPCtx& c){
 // QProblem::setupAuxiliaryQPgradient (QProblem.cpp:2602-2641): g = y_B - H x + A' y_C
 WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ double t=w.y[i]; t-=Hrow_dot(w,i,w.x,2,0xfffu);
-        w.g[i]=t+Acol_times(WQP,i,w.y+42); }
+    LANE_FOR(i,42){ double t=w.y[i]; t=Hrow_acc(w,i,w.x,2,0xfffu,t,-1.0);
+        w.g[i]=Acol_acc(WQP,i,w.y+42,t,1.0); }
     WBC_SYNC();
 }
 // QProblem::performStep (QProblem.cpp:4981-5278)
@@ -655,7 +719,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
     WBC_SYNC();
     // II.1 inactive constraints
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_times(WQP,ii,w.dx); }
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_acc(WQP,ii,w.dx,0.0,1.0); }
     WBC_SYNC();
     LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],0.0); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
@@ -683,7 +747,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
         LANE_FOR(i,42){ w.g[i]+=tau*w.dg[i]; w.lb[i]+=tau*w.dlb[i]; w.ub[i]+=tau*w.dub[i]; }
         LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
         WBC_SYNC();
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_times(WQP,ii,w.x); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_acc(WQP,ii,w.x,0.0,1.0); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
         LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; double da=w.dAx[ii];
             w.Ax[ii]+=tau*da; w.Ax_l[ii]+=tau*(da-w.dlbA[ii]); w.Ax_u[ii]+=tau*(w.dubA[ii]-da); }
         WBC_SYNC();
@@ -744,6 +808,17 @@ WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
     // The recurrence t_j = hypot(w[j+1], t_{j-1}) of the reference's loop is t_j = sgn(w[j+1]) |w[0..j+1]|_2, so every
     // rotation follows from prefix sums of squares: one lane per rotation, no serial sqrt/divide chain.
     const int lane=c.lane; WBC_SYNC();
+#if defined(WBC_EXACT_GIVENS)
+    { // the reference's serial recurrence (QProblem.cpp:2909-2925, 3401-3450): rotation j is computed from (wv[j+1], result of rotation j-1); every lane
+      // evaluates it redundantly, lane 0 stores
+        double prev=(nrot>0)?w.wv[0]:0.0;
+        for(int j=0;j<nrot;j++){ double xn,yn,cc,ss; computeGivens(w.wv[j+1],prev,xn,yn,cc,ss); if(lane==0){ w.cs_c[j]=cc; w.cs_s[j]=ss; } prev=xn; }
+        WBC_SYNC();
+        if(nrot>0&&lane==0) w.wv[nrot]=prev;
+        WBC_SYNC();
+        return;
+    }
+#endif
     double tlast=w.wv[0];
     LANE_FOR(j,nrot){
         double P=0.0; for(int k=0;k<=j;k++) P+=w.wv[k]*w.wv[k];      // sequential on purpose: a warp scan re-associates the sum and moved one degenerate working set
@@ -803,6 +878,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_SYNC();
     if(fullTest){
+        int shortcut=-1; (void)shortcut;
         LANE_FOR(j,42) w.tmpv[j]=Ael_dev(WQP,number,j);
         WBC_SYNC();
         { // The full test costs a whole step-direction solve and only its verdict is used.  |Z'a| decides it beforehand in all but
@@ -814,7 +890,11 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
             mx=wbc_max(mx);
             const double nrm=sqrt(l2);
             const bool sureLI=mx>LI_SURE*nrm, sureLD=mx<=LI_NONE*nrm;
+#if defined(WBC_EXACT)
+            shortcut= sureLI?1:(sureLD?0:-1);
+#else
             if(sureLI||sureLD){ WBC_FLOPS(3.0*(2.0*c.nAC*c.nAC+4.0*nFR*c.nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+2.0*(2.0*nFR*nFR+4.0*c.nAC*42.0)); return sureLI; }
+#endif
         }
         int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
         if(rv!=QP_OK) return false;
@@ -827,6 +907,9 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         { double l2=0.0,mx=0.0,amax=0.0; for(int i=0;i<nFR;i++){ double a=w.tmpv[(int)w.FR[i]]; l2+=a*a; amax=fmax(amax,fabs(a)); }
           for(int j=0;j<nZ;j++){ double sum=0.0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=w.tmpv[ii]*QQ(ii,j); } mx=fmax(mx,fabs(sum)); }
           printf("LISTAT C %d %.3e %.3e %.3e %.3e %.3e\n",(int)(zero>OPT_epsLITests*weight),mx,l2,amax,zero,weight); }
+#endif
+#if defined(WBC_EXACT)
+        { const bool full=zero>OPT_epsLITests*weight; WBC_LI_COUNT(0); if(shortcut<0) WBC_LI_COUNT(1) else if((shortcut==1)!=full) WBC_LI_COUNT(2) }
 #endif
         return zero>OPT_epsLITests*weight;
     }
@@ -842,11 +925,16 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     const int lane=c.lane, nZ=c.nFR-c.nAC;
     WBC_SYNC();
     if(fullTest){
+        int shortcut=-1; (void)shortcut;
         { // same shortcut as addConstraint_checkLI with a = e_number
             double mx=0.0; LANE_FOR(i,nZ) mx=fmax(mx,fabs(QQ(number,i)));
             mx=wbc_max(mx);
             const bool sureLI=mx>LI_SURE, sureLD=mx<=LI_NONE;
+#if defined(WBC_EXACT)
+            shortcut= sureLI?1:(sureLD?0:-1);
+#else
             if(sureLI||sureLD){ WBC_FLOPS(3.0*(2.0*c.nAC*c.nAC+4.0*c.nFR*c.nAC+4.0*c.nFR*nZ+4.0*c.nFR*c.nFR+4.0*nZ*nZ)+2.0*(2.0*c.nFR*c.nFR+4.0*c.nAC*42.0)); return sureLI; }
+#endif
         }
         LANE_FOR(j,42) w.tmpv[j]=(j==number)?1.0:0.0;
         WBC_SYNC();
@@ -859,6 +947,9 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         weight=wbc_max(weight); zero=wbc_max(zero);
 #if !defined(__CUDACC__) && defined(WBC_LI_STATS)
         { double mx=0.0; for(int i=0;i<nZ;i++) mx=fmax(mx,fabs(QQ(number,i))); printf("LISTAT B %d %.3e 1 1 %.3e %.3e\n",(int)(zero>OPT_epsLITests*weight),mx,zero,weight); }
+#endif
+#if defined(WBC_EXACT)
+        { const bool full=zero>OPT_epsLITests*weight; WBC_LI_COUNT(0); if(shortcut<0) WBC_LI_COUNT(1) else if((shortcut==1)!=full) WBC_LI_COUNT(2) }
 #endif
         return zero>OPT_epsLITests*weight;
     }
@@ -906,7 +997,7 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=sg*Ael_dev(WQP,number,ii)-Acol_times(WQP,ii,w.ym); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=Acol_acc(WQP,ii,w.ym,sg*Ael_dev(WQP,number,ii),-1.0); }
     return ensureLI_exchange(w,c,number,C_status,false);
 }
 // QProblem::addBound_ensureLI (QProblem.cpp:3596-3780)
@@ -922,7 +1013,7 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=0.0-Acol_times(WQP,ii,w.ym); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=Acol_acc(WQP,ii,w.ym,0.0,-1.0); }
     return ensureLI_exchange(w,c,number,B_status,true);
 }
 
@@ -1063,6 +1154,9 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
     c.infeasible=0; c.unbounded=0;
     for(int iter=nWSRperformed;iter<nWSR;iter++){
         c.status=QPS_PERFORMINGHOMOTOPY;
+#if !defined(__CUDACC__) && defined(WBC_QP_DBG)
+        g_dbg_iter=iter;
+#endif
         WBC_GANG_SYNC();
         WBC_TIC(t0);
         bool bCzero,bBzero; determineDataShift(w,c,bCzero,bBzero);
@@ -1209,7 +1303,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
     WBC_FLOPS(4.0*42*42+4.0*70*42);
-    LANE_FOR(i,70){ double ax=Arow_times(WQP,i,w.x); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    LANE_FOR(i,70){ double ax=Arow_acc(WQP,i,w.x,0.0,1.0); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;

@@ -10,7 +10,7 @@ rbd = C.CDLL("/tmp/libemul_rbd.so"); qp = C.CDLL("/tmp/libemul_qp_trace.so"); qp
 NS, NQ = rbd.emul_sizes(0), rbd.emul_sizes(1); P = lambda a: a.ctypes.data_as(C.c_void_p)
 mode, seed, inst, T = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
 N = inst + 1
-st, ref = wl.randomised(N, seed=seed, contacts=mode); pp = orc.pack_params()
+st, ref = wl.randomised(N, seed=seed, contacts=mode, switching_frac=0.1); pp = orc.pack_params()
 state = np.zeros(NS); h = C.c_void_p(qp.emulqp_create())
 Hs, gs, As, ls, us = [], [], [], [], []
 for t in range(T):
