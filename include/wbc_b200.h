@@ -166,6 +166,9 @@ int wbc_last_kernel_ms(wbc_handle* h, float* rbd_ms, float* qp_ms, float* torque
 int wbc_profile(wbc_handle* h, int enable, long long* host_out);
 /* measured FP64 FMA peak of the device in GFLOP/s (8 independent DFMA chains per thread, all SMs) -- the FP64 roofline denominator */
 int wbc_measure_fp64_peak(wbc_handle* h, double* gflops);
+/* measured shared-memory load bandwidth of the device in GB/s (conflict-free 64-bit loads, all SMs) -- the denominator for the solver's
+ * shared-memory traffic (SURVEY.md section 8d asks for a measured figure, not a datasheet one) */
+int wbc_measure_smem_peak(wbc_handle* h, double* gbytes_per_s);
 const char* wbc_last_error(const wbc_handle* h);
 
 #ifdef __cplusplus

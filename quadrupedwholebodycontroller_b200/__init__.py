@@ -17,7 +17,7 @@ _libs = {}
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
            "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
            "wbc_planner_default_params", "wbc_planner_create", "wbc_planner_reset", "wbc_planner_set_cmd_vel", "wbc_planner_tick", "wbc_get_reference",
-           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option", "wbc_debug_counters"]
+           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option", "wbc_debug_counters", "wbc_measure_smem_peak"]
 
 
 class WbcParams(C.Structure):
@@ -56,6 +56,7 @@ def load_library(profiling=False, exact=False):
         lib.wbc_default_params.argtypes = [C.POINTER(WbcParams)]
         lib.wbc_profile.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.wbc_measure_fp64_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        lib.wbc_measure_smem_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         lib.wbc_planner_default_params.argtypes = [C.POINTER(WbcPlannerParams)]
         lib.wbc_planner_create.argtypes = [C.c_void_p, C.POINTER(WbcPlannerParams)]
         lib.wbc_planner_reset.argtypes = [C.c_void_p, C.c_int, C.c_int]
@@ -190,6 +191,9 @@ class WholeBodyController:
 
     def measureFp64Peak(self):
         g = C.c_double(); self._ck(self._lib.wbc_measure_fp64_peak(self._h, C.byref(g))); return g.value
+
+    def measureSmemPeak(self):
+        g = C.c_double(); self._ck(self._lib.wbc_measure_smem_peak(self._h, C.byref(g))); return g.value
 
     def lastKernelMs(self):
         a, b, c = C.c_float(), C.c_float(), C.c_float()

@@ -655,4 +655,26 @@ extern "C" int wbc_measure_fp64_peak(wbc_handle* h,double* gflops){
         const double gf=2.0*8.0*iters*(double)grid*block/(ms*1e-3)/1e9; if(gf>best) best=gf; }
     cudaEventDestroy(e0); cudaEventDestroy(e1); *gflops=best; return WBC_OK;
 }
+// shared-memory bandwidth of the device, measured: conflict-free 64-bit loads (what the solver issues), 1024 threads x 2 CTAs per SM
+__global__ void wbc_smem_peak_kernel(unsigned long long* out,int iters){
+    __shared__ unsigned long long s[4096];
+    for(int i=threadIdx.x;i<4096;i+=blockDim.x) s[i]=(unsigned long long)i*0x9E3779B97F4A7C15ull;
+    __syncthreads();
+    unsigned long long a0=0,a1=0,a2=0,a3=0; int idx=threadIdx.x;
+    #pragma unroll 4
+    for(int it=0;it<iters;it++){ a0^=s[idx]; a1^=s[(idx+1024)&4095]; a2^=s[(idx+2048)&4095]; a3^=s[(idx+3072)&4095]; idx=(idx+32)&4095; }
+    if((a0^a1^a2^a3)==0x1234567ull) out[0]=a0;
+}
+extern "C" int wbc_measure_smem_peak(wbc_handle* h,double* gbytes_per_s){
+    if(!h||!gbytes_per_s) return WBC_ERR_ARG;
+    CK(cudaSetDevice(h->device));
+    const int iters=1<<14, grid=h->smCount*2, block=1024; cudaEvent_t e0,e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    wbc_smem_peak_kernel<<<grid,block,0,h->stream>>>((unsigned long long*)h->com,64); h->launches++;
+    double best=0;
+    for(int rep=0;rep<3;rep++){
+        CK(cudaEventRecord(e0,h->stream)); wbc_smem_peak_kernel<<<grid,block,0,h->stream>>>((unsigned long long*)h->com,iters); h->launches++; CK(cudaEventRecord(e1,h->stream));
+        CK(cudaEventSynchronize(e1)); float ms=0; CK(cudaEventElapsedTime(&ms,e0,e1));
+        const double gb=8.0*4.0*iters*(double)grid*block/(ms*1e-3)/1e9; if(gb>best) best=gb; }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); *gbytes_per_s=best; return WBC_OK;
+}
 extern "C" const char* wbc_last_error(const wbc_handle* h){ return h?h->err.c_str():"null handle"; }
