@@ -171,6 +171,33 @@ int wbc_measure_fp64_peak(wbc_handle* h, double* gflops);
 int wbc_measure_smem_peak(wbc_handle* h, double* gbytes_per_s);
 const char* wbc_last_error(const wbc_handle* h);
 
+/* ------------------------------------------------------------------------------------------------------------------------------
+ * One batch over several GPUs of the box.  The batch shards by robot index with no exchange on the hot path:
+ * device k owns the contiguous range [first_k, first_k + count_k) (remainder to the lowest shards) for the lifetime of the object, with its
+ * own stream; every call below is issued from the calling host thread and is asynchronous on those streams unless it says otherwise.
+ * Arrays are structure-of-arrays over the WHOLE batch (a[j*n_robots + i]), in host memory or in device memory of any GPU of the box.
+ * ------------------------------------------------------------------------------------------------------------------------------ */
+typedef struct wbc_multi wbc_multi;
+/* Replaces N x WholeBodyController::WholeBodyController() (whole_body_controller.cpp:22-59) spread over n_devices GPUs. */
+int wbc_multi_create(int n_robots, const int* device_ids, int n_devices, const wbc_params* params, wbc_multi** out);
+int wbc_multi_destroy(wbc_multi* m);
+int wbc_multi_num_devices(const wbc_multi* m);
+int wbc_multi_num_robots(const wbc_multi* m);
+int wbc_multi_shard(const wbc_multi* m, int k, int* device, int* first, int* count);
+wbc_handle* wbc_multi_handle(wbc_multi* m, int k);               /* the shard's own handle, for everything not wrapped here (planner, plant, rollout) */
+int wbc_multi_reset(wbc_multi* m);                                /* setInitialState (whole_body_controller.cpp:65-120) for every robot */
+/* The three callbacks (whole_body_controller.cpp:150-254) for the whole batch: one strided copy per array and device. */
+int wbc_multi_set_state(wbc_multi* m, const double* q, const double* qd, const double* base_pos, const double* base_quat_wxyz, const double* base_twist);
+int wbc_multi_set_reference(wbc_multi* m, const double* pose, const double* vel, const double* acc, const double* sw_pos, const double* sw_vel,
+                            const double* sw_acc, const unsigned char* contacts, const unsigned char* switching);
+int wbc_multi_step(wbc_multi* m);                                 /* updateState; solveQP; computeJointTorques (whole_body_controller.cpp:650-652) on every device */
+int wbc_multi_synchronize(wbc_multi* m);
+/* Publishers (whole_body_controller.cpp:558-576, 666-670) of every shard into global arrays.  With DEVICE pointers of one GPU this is the optional
+ * single gather of the results over NVLink (about 200 B per robot; peer-to-peer where the topology allows).  Blocks until the copies are done. */
+int wbc_multi_get_outputs(wbc_multi* m, double* tau, double* grf, double* x, int* rc, int* nwsr, signed char* ws, double* com);
+int wbc_multi_last_gather_ms(wbc_multi* m, float* ms);            /* device time of those copies, max over the GPUs */
+const char* wbc_multi_last_error(const wbc_multi* m);
+
 #ifdef __cplusplus
 }
 #endif

@@ -112,6 +112,40 @@ private:
     int n_ = 0;
 };
 
+// The same batch spread over several GPUs of the box from ONE host thread (wbc_multi_*): device k owns a contiguous range of robots with its own
+// stream, no exchange on the hot path.  Pointers are arrays over the WHOLE batch, host memory or device memory of any GPU; getOutputs
+// into device memory of one GPU is the optional single gather of the results over NVLink (lastGatherMilliseconds() = its device time).
+class MultiGpuWholeBodyController {
+public:
+    MultiGpuWholeBodyController(int nRobots, const std::vector<int>& devices, const WholeBodyController::Params& params = WholeBodyController::Params()) : n_(nRobots) {
+        const int rc = wbc_multi_create(nRobots, devices.data(), (int)devices.size(), &params, &m_);
+        if (rc != WBC_OK) throw std::runtime_error("MultiGpuWholeBodyController: wbc_multi_create failed with code " + std::to_string(rc));
+    }
+    ~MultiGpuWholeBodyController() { if (m_) wbc_multi_destroy(m_); }
+    MultiGpuWholeBodyController(const MultiGpuWholeBodyController&) = delete;
+    MultiGpuWholeBodyController& operator=(const MultiGpuWholeBodyController&) = delete;
+    int numberOfRobots() const { return n_; }
+    int numberOfDevices() const { return wbc_multi_num_devices(m_); }
+    void shard(int k, int& device, int& first, int& count) const { check(wbc_multi_shard(m_, k, &device, &first, &count)); }
+    void setInitialState() { check(wbc_multi_reset(m_)); }
+    void jointStateCallback(const double* jointPos, const double* jointVel) { check(wbc_multi_set_state(m_, jointPos, jointVel, nullptr, nullptr, nullptr)); }
+    void floatingBaseStateCallback(const double* basePos, const double* baseQuatWXYZ, const double* baseTwist) { check(wbc_multi_set_state(m_, nullptr, nullptr, basePos, baseQuatWXYZ, baseTwist)); }
+    void referenceCallback(const double* pose, const double* vel, const double* acc, const double* swPos, const double* swVel, const double* swAcc,
+                           const unsigned char* footContacts, const unsigned char* isSwitchingFootState = nullptr) {
+        check(wbc_multi_set_reference(m_, pose, vel, acc, swPos, swVel, swAcc, footContacts, isSwitchingFootState));
+    }
+    void step() { check(wbc_multi_step(m_)); }               // updateState(); solveQP(); computeJointTorques(); on every device
+    void synchronize() { check(wbc_multi_synchronize(m_)); }
+    void getOutputs(double* tau, double* grf, double* x, int* rc, int* nWSR, signed char* ws, double* com) { check(wbc_multi_get_outputs(m_, tau, grf, x, rc, nWSR, ws, com)); }
+    float lastGatherMilliseconds() { float t = 0; check(wbc_multi_last_gather_ms(m_, &t)); return t; }
+    wbc_handle* shardHandle(int k) { return wbc_multi_handle(m_, k); }
+
+private:
+    void check(int rc) const { if (rc != WBC_OK) throw std::runtime_error(std::string("MultiGpuWholeBodyController: ") + wbc_multi_last_error(m_) + " (code " + std::to_string(rc) + ")"); }
+    wbc_multi* m_ = nullptr;
+    int n_ = 0;
+};
+
 // Batched mirror of the reference's MotionPlanner (include/anymal_wbc/motion_planner.hpp:10-52, src/motion_planner.cpp): one planner
 // per robot of a WholeBodyController, living on the same GPU.  plannerLoop() is a blocking loop paced by ros::Rate in the
 // reference; here one call of plannerPeriod() is one period (params.dt) of that loop for the whole batch, and a published

@@ -17,7 +17,9 @@ _libs = {}
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
            "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
            "wbc_planner_default_params", "wbc_planner_create", "wbc_planner_reset", "wbc_planner_set_cmd_vel", "wbc_planner_tick", "wbc_get_reference",
-           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option", "wbc_debug_counters", "wbc_measure_smem_peak"]
+           "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option", "wbc_debug_counters", "wbc_measure_smem_peak",
+           "wbc_multi_create", "wbc_multi_destroy", "wbc_multi_num_devices", "wbc_multi_num_robots", "wbc_multi_shard", "wbc_multi_handle", "wbc_multi_reset", "wbc_multi_set_state",
+           "wbc_multi_set_reference", "wbc_multi_step", "wbc_multi_synchronize", "wbc_multi_get_outputs", "wbc_multi_last_gather_ms", "wbc_multi_last_error"]
 
 
 class WbcParams(C.Structure):
@@ -71,6 +73,16 @@ def load_library(profiling=False, exact=False):
         lib.wbc_rollout_stats.argtypes = [C.c_void_p] + [C.c_void_p] * 4 + [C.c_int]
         lib.wbc_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         lib.wbc_debug_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        lib.wbc_multi_create.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(WbcParams), C.POINTER(C.c_void_p)]
+        for name in ("wbc_multi_destroy", "wbc_multi_num_devices", "wbc_multi_num_robots", "wbc_multi_reset", "wbc_multi_step", "wbc_multi_synchronize"):
+            getattr(lib, name).argtypes = [C.c_void_p]
+        lib.wbc_multi_shard.argtypes = [C.c_void_p, C.c_int] + [C.POINTER(C.c_int)] * 3
+        lib.wbc_multi_handle.argtypes = [C.c_void_p, C.c_int]; lib.wbc_multi_handle.restype = C.c_void_p
+        lib.wbc_multi_set_state.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        lib.wbc_multi_set_reference.argtypes = [C.c_void_p] + [C.c_void_p] * 8
+        lib.wbc_multi_get_outputs.argtypes = [C.c_void_p] + [C.c_void_p] * 7
+        lib.wbc_multi_last_gather_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        lib.wbc_multi_last_error.argtypes = [C.c_void_p]; lib.wbc_multi_last_error.restype = C.c_char_p
         _libs[path] = lib
     return _libs[path]
 
@@ -246,3 +258,64 @@ class WholeBodyController:
         o = dict(ticks=np.zeros(N, np.int32), failed_ticks=np.zeros(N, np.int32), nwsr_sum=np.zeros(N, np.int32), nwsr_max=np.zeros(N, np.int32))
         self._ck(self._lib.wbc_rollout_stats(self._h, *[_ptr(o[k]) for k in ("ticks", "failed_ticks", "nwsr_sum", "nwsr_max")], int(reset)))
         return o
+
+
+class MultiGpuController:
+    """One batch of N robots sharded by robot index over several GPUs of the box inside ONE process (wbc_multi_*, include/wbc_b200.h): device k
+    owns a contiguous range with its own stream, no exchange on the hot path; getOutputs into device memory of one GPU is the optional single
+    gather of the results.  Arrays are (K, N) over the WHOLE batch: numpy (host) or torch CUDA tensors of any device."""
+
+    def __init__(self, n_robots, devices, params=None):
+        lib = self._lib = load_library()
+        self.N = int(n_robots); self.devices = [int(d) for d in devices]
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        p = params if params is not None else default_params()
+        self._m = C.c_void_p()
+        rc = lib.wbc_multi_create(self.N, arr, len(self.devices), C.byref(p), C.byref(self._m))
+        if rc != 0:
+            self._m = C.c_void_p()
+            raise RuntimeError(f"wbc_multi_create failed with {rc} (devices {self.devices}; there is no CPU fallback)")
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError(f"wbc error {rc}: {self._lib.wbc_multi_last_error(self._m).decode()}")
+
+    def close(self):
+        if getattr(self, "_m", None) and self._m.value:
+            self._lib.wbc_multi_destroy(self._m); self._m = C.c_void_p()
+
+    __del__ = close
+
+    def shards(self):
+        out = []
+        for k in range(self._lib.wbc_multi_num_devices(self._m)):
+            d, f, c = C.c_int(), C.c_int(), C.c_int()
+            self._ck(self._lib.wbc_multi_shard(self._m, k, C.byref(d), C.byref(f), C.byref(c))); out.append((d.value, f.value, c.value))
+        return out
+
+    def setInitialState(self):
+        self._ck(self._lib.wbc_multi_reset(self._m))
+
+    def setJointAndBaseState(self, q, qd, base_pos, base_quat, base_twist):
+        self._ck(self._lib.wbc_multi_set_state(self._m, _ptr(q), _ptr(qd), _ptr(base_pos), _ptr(base_quat), _ptr(base_twist)))
+
+    def setReference(self, pose, vel, acc, sw_pos, sw_vel, sw_acc, contacts, switching=None):
+        self._ck(self._lib.wbc_multi_set_reference(self._m, _ptr(pose), _ptr(vel), _ptr(acc), _ptr(sw_pos), _ptr(sw_vel), _ptr(sw_acc), _ptr(contacts), _ptr(switching)))
+
+    def step(self):
+        self._ck(self._lib.wbc_multi_step(self._m))
+
+    def synchronize(self):
+        self._ck(self._lib.wbc_multi_synchronize(self._m))
+
+    def getOutputs(self, tau=None, grf=None, x=None, rc=None, nwsr=None, ws=None, com=None):
+        if all(v is None for v in (tau, grf, x, rc, nwsr, ws, com)):
+            N = self.N
+            o = dict(tau=np.zeros((12, N)), grf=np.zeros((12, N)), x=np.zeros((42, N)), rc=np.zeros(N, np.int32), nwsr=np.zeros(N, np.int32),
+                     ws=np.zeros((112, N), np.int8), com=np.zeros((3, N)))
+            self._ck(self._lib.wbc_multi_get_outputs(self._m, *[_ptr(o[k]) for k in ("tau", "grf", "x", "rc", "nwsr", "ws", "com")]))
+            return o
+        self._ck(self._lib.wbc_multi_get_outputs(self._m, _ptr(tau), _ptr(grf), _ptr(x), _ptr(rc), _ptr(nwsr), _ptr(ws), _ptr(com)))
+
+    def lastGatherMs(self):
+        t = C.c_float(); self._ck(self._lib.wbc_multi_last_gather_ms(self._m, C.byref(t))); return t.value

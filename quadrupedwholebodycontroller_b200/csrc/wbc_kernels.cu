@@ -678,3 +678,99 @@ extern "C" int wbc_measure_smem_peak(wbc_handle* h,double* gbytes_per_s){
     cudaEventDestroy(e0); cudaEventDestroy(e1); *gbytes_per_s=best; return WBC_OK;
 }
 extern "C" const char* wbc_last_error(const wbc_handle* h){ return h?h->err.c_str():"null handle"; }
+
+// ================================================================= one batch over several GPUs of the box (include/wbc_b200.h, "multi-GPU")
+// The path shards by robot index with no exchange: device k owns the contiguous range [first_k, first_k + count_k) for the lifetime
+// of the object -- one wbc_handle, one stream per device, all issued from the calling host thread.  Global arrays are structure-of-arrays over the
+// WHOLE batch, a[j*N + i]; a shard's slice of one array is a strided block, moved with ONE cudaMemcpy2DAsync per array and device.
+struct wbc_multi {
+    int N=0, nDev=0;
+    std::vector<wbc_handle*> h; std::vector<int> first, count, device;
+    std::vector<cudaEvent_t> g0, g1;            // brackets of the last output copy per device (gather timing)
+    std::string err;
+};
+#define MCK(call) do{ cudaError_t e_=(call); if(e_!=cudaSuccess){ m->err=std::string(#call)+": "+cudaGetErrorString(e_); return WBC_ERR_CUDA; } }while(0)
+
+extern "C" int wbc_multi_destroy(wbc_multi* m){
+    if(!m) return WBC_ERR_ARG;
+    for(size_t k=0;k<m->h.size();k++){ if(m->h[k]){ cudaSetDevice(m->device[k]); if(k<m->g0.size()&&m->g0[k]) cudaEventDestroy(m->g0[k]); if(k<m->g1.size()&&m->g1[k]) cudaEventDestroy(m->g1[k]); wbc_destroy(m->h[k]); } }
+    delete m; return WBC_OK;
+}
+extern "C" int wbc_multi_create(int n_robots,const int* device_ids,int n_devices,const wbc_params* params,wbc_multi** out){
+    if(!out||n_robots<=0||n_devices<=0||!device_ids||n_devices>n_robots) return WBC_ERR_ARG;
+    *out=nullptr;
+    wbc_multi* m=new wbc_multi; m->N=n_robots; m->nDev=n_devices;
+    const int base=n_robots/n_devices, rem=n_robots%n_devices;            // same split as workloads.shard_range: the remainder goes to the lowest shards
+    for(int k=0;k<n_devices;k++){
+        const int cnt=base+(k<rem?1:0), fst=k*base+(k<rem?k:rem);
+        wbc_handle* h=nullptr; const int rc=wbc_create(cnt,device_ids[k],params,nullptr,&h);
+        if(rc!=WBC_OK){ fprintf(stderr,"wbc_multi_create: shard %d on device %d failed with %d\n",k,device_ids[k],rc); wbc_multi_destroy(m); return rc; }
+        m->h.push_back(h); m->first.push_back(fst); m->count.push_back(cnt); m->device.push_back(device_ids[k]);
+        cudaEvent_t a=nullptr,b=nullptr; cudaSetDevice(device_ids[k]); cudaEventCreate(&a); cudaEventCreate(&b); m->g0.push_back(a); m->g1.push_back(b);
+    }
+    // direct peer copies for the gather where the topology allows them (NVLink / NVSwitch); without peer access the runtime stages through the host
+    for(int a=0;a<n_devices;a++) for(int b=0;b<n_devices;b++) if(a!=b){ int can=0; cudaDeviceCanAccessPeer(&can,device_ids[a],device_ids[b]);
+        if(can){ cudaSetDevice(device_ids[a]); if(cudaDeviceEnablePeerAccess(device_ids[b],0)!=cudaSuccess) cudaGetLastError(); } }
+    *out=m; return WBC_OK;
+}
+extern "C" int wbc_multi_num_devices(const wbc_multi* m){ return m?m->nDev:0; }
+extern "C" int wbc_multi_num_robots(const wbc_multi* m){ return m?m->N:0; }
+extern "C" int wbc_multi_shard(const wbc_multi* m,int k,int* device,int* first,int* count){
+    if(!m||k<0||k>=m->nDev) return WBC_ERR_ARG;
+    if(device) *device=m->device[k]; if(first) *first=m->first[k]; if(count) *count=m->count[k]; return WBC_OK;
+}
+extern "C" wbc_handle* wbc_multi_handle(wbc_multi* m,int k){ return (m&&k>=0&&k<m->nDev)?m->h[k]:nullptr; }
+extern "C" const char* wbc_multi_last_error(const wbc_multi* m){
+    if(!m) return "null handle";
+    if(!m->err.empty()) return m->err.c_str();
+    for(auto* h:m->h) if(h&&!h->err.empty()) return h->err.c_str();
+    return "";
+}
+// slice [first, first+count) of a global (rows x N) array <-> the shard's own (rows x count) array: one strided copy
+static int multi_in(wbc_multi* m,int k,void* dst,const void* src,int rows,size_t elem){
+    if(!src) return WBC_OK;
+    const wbc_handle* h=m->h[k];
+    MCK(cudaMemcpy2DAsync(dst,(size_t)m->count[k]*elem,(const char*)src+(size_t)m->first[k]*elem,(size_t)m->N*elem,(size_t)m->count[k]*elem,rows,cudaMemcpyDefault,h->stream));
+    return WBC_OK;
+}
+static int multi_out(wbc_multi* m,int k,void* dst,const void* src,int rows,size_t elem){
+    if(!dst) return WBC_OK;
+    const wbc_handle* h=m->h[k];
+    MCK(cudaMemcpy2DAsync((char*)dst+(size_t)m->first[k]*elem,(size_t)m->N*elem,src,(size_t)m->count[k]*elem,(size_t)m->count[k]*elem,rows,cudaMemcpyDefault,h->stream));
+    return WBC_OK;
+}
+extern "C" int wbc_multi_reset(wbc_multi* m){ if(!m) return WBC_ERR_ARG; for(int k=0;k<m->nDev;k++){ int r=wbc_reset(m->h[k],0,m->count[k]); if(r) return r; } return WBC_OK; }
+extern "C" int wbc_multi_set_state(wbc_multi* m,const double* q,const double* qd,const double* pos,const double* quat,const double* twist){
+    if(!m) return WBC_ERR_ARG;
+    for(int k=0;k<m->nDev;k++){ wbc_handle* h=m->h[k]; MCK(cudaSetDevice(h->device)); int r; const size_t D=sizeof(double);
+        if((r=multi_in(m,k,h->q,q,12,D))||(r=multi_in(m,k,h->qd,qd,12,D))||(r=multi_in(m,k,h->pos,pos,3,D))||(r=multi_in(m,k,h->quat,quat,4,D))||(r=multi_in(m,k,h->twist,twist,6,D))) return r; }
+    return WBC_OK;
+}
+extern "C" int wbc_multi_set_reference(wbc_multi* m,const double* pose,const double* vel,const double* acc,const double* swp,const double* swv,const double* swa,
+                                       const unsigned char* contacts,const unsigned char* switching){
+    if(!m) return WBC_ERR_ARG;
+    for(int k=0;k<m->nDev;k++){ wbc_handle* h=m->h[k]; MCK(cudaSetDevice(h->device)); int r; const size_t D=sizeof(double);
+        if((r=multi_in(m,k,h->pose,pose,6,D))||(r=multi_in(m,k,h->vel,vel,6,D))||(r=multi_in(m,k,h->acc,acc,6,D))||(r=multi_in(m,k,h->swp,swp,12,D))||(r=multi_in(m,k,h->swv,swv,12,D))
+           ||(r=multi_in(m,k,h->swa,swa,12,D))||(r=multi_in(m,k,h->contacts,contacts,4,1))||(r=multi_in(m,k,h->switching,switching,1,1))) return r;
+        if(contacts&&(r=wbc_set_reference(h,nullptr,nullptr,nullptr,nullptr,nullptr,nullptr,h->contacts,switching?h->switching:nullptr))) return r; }   // derives / rolls the switching flag like the single-device call
+    return WBC_OK;
+}
+extern "C" int wbc_multi_step(wbc_multi* m){ if(!m) return WBC_ERR_ARG; for(int k=0;k<m->nDev;k++){ int r=wbc_step(m->h[k]); if(r) return r; } return WBC_OK; }
+extern "C" int wbc_multi_synchronize(wbc_multi* m){ if(!m) return WBC_ERR_ARG; for(int k=0;k<m->nDev;k++){ int r=wbc_synchronize(m->h[k]); if(r) return r; } return WBC_OK; }
+// results of every shard into global (rows x N) arrays: host memory, or device memory of ANY device of the box -- the latter is the optional
+// single gather of SURVEY 8e (about 200 B per robot over NVLink; peer copies where enabled).  Returns after all copies have completed.
+extern "C" int wbc_multi_get_outputs(wbc_multi* m,double* tau,double* grf,double* x,int* rc,int* nwsr,signed char* ws,double* com){
+    if(!m) return WBC_ERR_ARG;
+    for(int k=0;k<m->nDev;k++){ wbc_handle* h=m->h[k]; MCK(cudaSetDevice(h->device)); int r; const size_t D=sizeof(double);
+        MCK(cudaEventRecord(m->g0[k],h->stream));
+        if((r=multi_out(m,k,tau,h->tau,12,D))||(r=multi_out(m,k,grf,h->grf,12,D))||(r=multi_out(m,k,x,h->x,42,D))||(r=multi_out(m,k,rc,h->rc,1,sizeof(int)))
+           ||(r=multi_out(m,k,nwsr,h->nwsr,1,sizeof(int)))||(r=multi_out(m,k,ws,h->ws,112,1))||(r=multi_out(m,k,com,h->com,3,D))) return r;
+        MCK(cudaEventRecord(m->g1[k],h->stream)); }
+    return wbc_multi_synchronize(m);
+}
+// duration [ms] of the output copies of the last wbc_multi_get_outputs, max over the devices (each measured with CUDA events on its own stream)
+extern "C" int wbc_multi_last_gather_ms(wbc_multi* m,float* ms){
+    if(!m||!ms) return WBC_ERR_ARG;
+    float worst=0; for(int k=0;k<m->nDev;k++){ MCK(cudaSetDevice(m->device[k])); float t=0; if(cudaEventElapsedTime(&t,m->g0[k],m->g1[k])!=cudaSuccess){ cudaGetLastError(); t=-1; } if(t>worst) worst=t; }
+    *ms=worst; return WBC_OK;
+}
