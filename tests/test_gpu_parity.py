@@ -207,3 +207,20 @@ def test_full_size_properties(wbc, wl, contacts, n):
     ctl.setInitialState(); ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.step(); o2 = ctl.getOutputs()
     assert all(np.array_equal(o[k], o2[k]) for k in o)             # deterministic whatever the work-queue order was
     ctl.close()
+
+
+def test_device_qp_blocks_against_the_independent_urdf_model(wbc):
+    """The device's centroidal mass matrix and foot Jacobians (as they appear in the QP's A, wbc.cpp:492-497) against tests/golden/rbd_independent.npz:
+    an independent xml.etree read of the URDF + geometric-Jacobian mass matrix + numpy controller algebra (tests/urdf_independent.py) -- nothing shared
+    with tools/urdf_compiler.py, from which both the device table and the oracle tree come."""
+    import urdf_independent as ui
+    gold = np.load(os.path.join(HERE, "golden", "rbd_independent.npz")); st, ref = ui.fixture_states(); n = st["q"].shape[1]
+    ctl = wbc.WholeBodyController(n); ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.step(); o = ctl.getOutputs()
+    rel = lambda a, b: np.abs(a - b).max() / max(1.0, np.abs(b).max())
+    for i in range(n):
+        A = ctl.denseQP(i)["A"]; Mc = gold[f"Mc_{i}"]
+        assert rel(A[0:6, 0:6], Mc[0:6, 0:6]) < 1e-9 and rel(A[34:46, 6:18], Mc[6:18, 6:18]) < 1e-9, i
+        assert rel(A[6:18, 0:18], gold[f"Jst_c_{i}"]) < 1e-9 and rel(A[46:58, 0:18], gold[f"Jsw_c_{i}"]) < 1e-9, i
+        assert rel(A[0:6, 18:30], -gold[f"Jst_c_{i}"][:, 0:6].T) < 1e-9, i
+        assert rel(o["com"][:, i], gold[f"com_{i}"]) < 1e-9, i
+    ctl.close()
