@@ -558,6 +558,48 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
     if(!potrf_R(w,c,nZ)) return QP_RET_HESSIAN_NOT_SPD;
     return QP_OK;
 }
+// The same factor after a REMOVAL (removeBound / removeConstraint) without recomputing what cannot have changed.  A removal appends ONE column to Z
+// (index n = nZ-1; the Givens sweeps of QProblem.cpp:3846-3870, 4099-4121 touch columns >= n only) and leaves the first n columns bit for bit alone; a freed
+// variable joins the END of the free list with zeros in those columns, so its terms add exactly 0 to every old entry of Z'HZ.  DPOTRF "U" computes R row by
+// row from the rows above, hence the leading n x n block of the new R is bitwise the old one and only column n is new:
+//     A(i,n) = sum_ii Z(ii,n) (HZ)(ii,i)            (the reference's order: SymDenseMat::bilinear, free-list order)
+//     R(i,n) = (A(i,n) - sum_{k=i-1..0} R(k,i) R(k,n)) / R(i,i),   R(n,n) = sqrt(A(n,n) - sum_{k=n-1..0} R(k,n)^2)      (LAPACKReplacement.cpp:39-77)
+// The inner sums start with the entry computed last, so the column is one serial chain; every lane runs it redundantly on broadcast loads and stores the
+// same values (a lane only ever reads back what it wrote itself: no synchronisation inside the chain).  Saves the (nZ^2/2) x nFR tile products of Z'HZ and
+// nZ-1 square roots / divisions on more than half of the iterations of a cold start.  Needs nAC > 0 (with nAC == 0 the reference re-trivialises Z).
+WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
+    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC, n=nZ-1;
+    WBC_FLOPS(2.0*nFR*nFR*nZ+2.0*nFR*nZ*nZ+(double)nZ*nZ*nZ/3.0);      // algorithmic count of the reference, which recomputes everything
+    WBC_SYNC();
+    int nff=0; int* ffl=reinterpret_cast<int*>(w.rdT);
+    for(int base=0;base<nFR;base+=WBC_NL){ const int i=base+lane; const int v=(i<nFR)?(int)w.FR[i]:0; const bool isf=(i<nFR)&&v>=18&&v<30;
+        const unsigned m=wbc_ballot(isf); if(isf) ffl[nff+wbc_rank(m,lane)]=v-18; nff+=wbc_popc(m); }
+    WBC_SYNC();
+    LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; double s=0;
+        for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
+        w.HZf[a*LD+k]=s; }
+    WBC_SYNC();
+    double* col=w.ym;                                           // behind the 12 x LD block of (HZ)_force inside the scratch union
+    LANE_FOR(i,nZ){ double s=0.0;
+        for(int ii=0;ii<nFR;ii++){ const int v=(int)w.FR[ii]; const double z=QQ(v,n);
+            const double hk=(v>=18&&v<30)? w.HZf[(v-18)*LD+i] : ((v>=30)?WQP.rho:1.0)*QQ(v,i);
+            s+=z*hk; }
+        col[i]=s; }
+    WBC_SYNC();
+    const double* rn=&RR(0,n);                                  // packed column n: RR(k,n) = rn[-k]
+    for(int i=0;i<n;i++){
+        double s=col[i]; const double* ri=&RR(0,i);
+        for(int k=i-1;k>=0;k--) s-=ri[-k]*rn[-k];
+        RR(i,n)=WBC_BYDIAG(s,w.rdR[i]);
+    }
+    double sum=col[n];
+    for(int k=n-1;k>=0;k--) sum-=rn[-k]*rn[-k];
+    if(!(sum>0.0)) return QP_RET_HESSIAN_NOT_SPD;
+    const double d=sqrt(sum);
+    RR(n,n)=d; w.rdR[n]=WBC_RDIAG(d);
+    WBC_SYNC();
+    return QP_OK;
+}
 
 // ---------------------------------------------------------------- step direction
 // QProblem::determineStepDirection (QProblem.cpp:4637-4975), HST_POSDEF branch.
@@ -1175,7 +1217,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
         rv=changeActiveSet(w,c,BC_idx,BC_status,BC_isBound);
         WBC_TOC(t0,3);
         if(rv!=QP_OK){ nWSR=iter; if(c.infeasible){ c.status=QPS_HOMOTOPYQPSOLVED; return QP_RET_HOTSTART_STOPPED_INFEASIBILITY; } return rv; }
-        rv=computeProjectedCholesky(w,c);
+        rv=(BC_status==ST_INACTIVE&&c.nAC>0&&c.nFR>c.nAC)? extendProjectedCholesky(w,c) : computeProjectedCholesky(w,c);
         WBC_TOC(t0,4);
         if(rv!=QP_OK) return rv;
         c.status=QPS_HOMOTOPYQPSOLVED;
