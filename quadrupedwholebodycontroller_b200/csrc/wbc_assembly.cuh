@@ -11,6 +11,20 @@
 #pragma once
 #include "wbc_rbd.cuh"
 
+// The dense phase runs with WBC_ASM_NL lanes per robot (16: two robots share a warp).  Most of its loops have 6, 12 or 36 elements and its first block
+// is serial, so a whole warp per robot kept 12 of 32 lanes busy (ncu, r02); `lane` below is the lane index INSIDE the robot's group.  Measured for
+// 16384 robots (profiles/r02_update_state.txt): 32 lanes per robot 0.408 ms, 16 lanes 0.401 ms, 8 lanes 0.739 ms (57 KB of shared memory per warp leave
+// 3 warps per SM: the kernel is latency bound and wants warps in flight more than it wants full lanes).
+#if WBC_NL==1
+  #define WBC_ASM_NL 1
+  #define ASM_FOR(i,n) for(int i=lane;i<(n);i+=1)
+#else
+  #ifndef WBC_ASM_NL
+  #define WBC_ASM_NL 16
+  #endif
+  #define ASM_FOR(i,n) _Pragma("unroll 1") for(int i=lane;i<(n);i+=WBC_ASM_NL)
+#endif
+
 namespace wbc {
 
 // wbc.cpp:12-20
@@ -60,32 +74,43 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     }
     WBC_SYNC();
     // ---- D2: Mbj (MIXED) column j = [R F.lin ; R F.ang]; foot world offsets/velocities; B = Mbb^-1 Mbj ----
-    LANE_FOR(j,12){
+    ASM_FOR(j,12){
         double a[3],b[3]; mv3(R,s.Fraw[j],a); mv3(R,s.Fraw[j]+3,b);
         double y[6]={a[0],a[1],a[2],b[0],b[1],b[2]};
+        #pragma unroll
         for(int i=0;i<6;i++) s.Mbj[12*i+j]=y[i];
-        for(int i=0;i<6;i++){ double v=y[i]; for(int k=0;k<i;k++) v-=s.L[6*i+k]*y[k]; y[i]=v/s.L[6*i+i]; }
-        for(int i=5;i>=0;i--){ double v=y[i]; for(int k=i+1;k<6;k++) v-=s.L[6*k+i]*y[k]; y[i]=v/s.L[6*i+i]; }
+        #pragma unroll
+        for(int i=0;i<6;i++){ double v=y[i];
+            #pragma unroll
+            for(int k=0;k<6;k++) if(k<i) v-=s.L[6*i+k]*y[k];
+            y[i]=v/s.L[6*i+i]; }
+        #pragma unroll
+        for(int i=5;i>=0;i--){ double v=y[i];
+            #pragma unroll
+            for(int k=0;k<6;k++) if(k>i) v-=s.L[6*k+i]*y[k];
+            y[i]=v/s.L[6*i+i]; }
+        #pragma unroll
         for(int i=0;i<6;i++) s.B[12*i+j]=y[i];
     }
-    LANE_FOR(l,4){
+    ASM_FOR(l,4){
         double a[3],b[3]; mv3(R,s.footp[l],a); mv3(R,s.footv[l],b);
         for(int i=0;i<3;i++){ s.footpw[3*l+i]=a[i]+s.pb[i]; s.footvw[3*l+i]=b[i]; }
     }
     WBC_SYNC();
     // ---- D3: centroidal blocks ----
     // M_c,bb = X^T Mbb X
-    LANE_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.Mbb[6*i+k]*s.X[6*k+j]; s.tmp66[e]=v; }
+    ASM_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.Mbb[6*i+k]*s.X[6*k+j]; s.tmp66[e]=v; }
     WBC_SYNC();
-    LANE_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.X[6*k+i]*s.tmp66[6*k+j]; out.Mbb[e]=v; }
+    ASM_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.X[6*k+i]*s.tmp66[6*k+j]; out.Mbb[e]=v; }
     // M_c,jj = Mjj - Mjb B   (Mjj is block diagonal per leg)
-    LANE_FOR(e,144){ int i=e/12,j=e%12; double v=(i/3==j/3)?s.Hleg[i/3][3*(i%3)+(j%3)]:0.0;
+    ASM_FOR(e,144){ int i=e/12,j=e%12; double v=(i/3==j/3)?s.Hleg[i/3][3*(i%3)+(j%3)]:0.0;
         for(int k=0;k<6;k++) v-=s.Mbj[12*k+i]*s.B[12*k+j]; out.Mjj[e]=v; }
     // J_c = [Jb X, Jj - Jb B],  Jb(foot l) = [1, -S(r_l)], r_l = p_foot - p_base (world)   (Jacobians.cpp:16-52)
-    LANE_FOR(e,216){ int i=e/18,j=e%18,l=i/3,r=i%3;
+    ASM_FOR(e,216){ int i=e/18,j=e%18,l=i/3,r=i%3;
         double rl[3]={s.footpw[3*l]-s.pb[0],s.footpw[3*l+1]-s.pb[1],s.footpw[3*l+2]-s.pb[2]};
-        const double Sr[9]={0,-rl[2],rl[1], rl[2],0,-rl[0], -rl[1],rl[0],0};
-        double jb[6]; for(int k=0;k<3;k++){ jb[k]=(k==r)?1.0:0.0; jb[3+k]=-Sr[3*r+k]; }
+        // row r of [1, -S(r_l)] without a dynamically indexed local array
+        const double jb[6]={ (r==0)?1.0:0.0, (r==1)?1.0:0.0, (r==2)?1.0:0.0,
+                             (r==0)?-0.0:((r==1)?-rl[2]:rl[1]), (r==0)?rl[2]:((r==1)?-0.0:-rl[0]), (r==0)?-rl[1]:((r==1)?rl[0]:-0.0) };
         double v;
         if(j<6){ v=0; for(int k=0;k<6;k++) v+=jb[k]*s.X[6*k+j]; }
         else { int jj=j-6; v=0;
@@ -93,20 +118,20 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
             for(int k=0;k<6;k++) v-=jb[k]*s.B[12*k+jj]; }
         out.Jc[e]=v; }
     // T top rows = [Xi, Xi B], Xi = [[1,-S(d)],[0,1]]
-    LANE_FOR(e,108){ int i=e/18,j=e%18; double v;
+    ASM_FOR(e,108){ int i=e/18,j=e%18; double v;
         if(j<6) v=(i==j)?1.0:((i<3&&j>=3)?-s.X[6*i+j]:0.0);
         else { int jj=j-6; v=s.B[12*i+jj]; if(i<3) for(int k=0;k<3;k++) v-=s.X[6*i+3+k]*s.B[12*(3+k)+jj]; }
         s.Ttop[e]=v; }
     // w6 = (Tdot^-1)_prev nu  (only its top 6 rows are non-zero)
-    LANE_FOR(i,6){ double v=0; if(!first){ for(int k=0;k<6;k++) v+=st.TdotInv[18*i+k]*s.twist[k]; for(int k=0;k<12;k++) v+=st.TdotInv[18*i+6+k]*s.qd[k]; } s.w6[i]=v; }
+    ASM_FOR(i,6){ double v=0; if(!first){ for(int k=0;k<6;k++) v+=st.TdotInv[18*i+k]*s.twist[k]; for(int k=0;k<12;k++) v+=st.TdotInv[18*i+6+k]*s.qd[k]; } s.w6[i]=v; }
     WBC_SYNC();
     // ---- D4: bias_c (joint part) = v_j - B^T v_b,  v = C nu + M w   (wbc.cpp:289) ----
-    LANE_FOR(i,6){ double v=s.Cb[i]; for(int k=0;k<6;k++) v+=s.Mbb[6*i+k]*s.w6[k]; s.vb6[i]=v; }
+    ASM_FOR(i,6){ double v=s.Cb[i]; for(int k=0;k<6;k++) v+=s.Mbb[6*i+k]*s.w6[k]; s.vb6[i]=v; }
     WBC_SYNC();
-    LANE_FOR(j,12){ double v=s.tauC[j]; for(int k=0;k<6;k++) v+=s.Mbj[12*k+j]*s.w6[k]; for(int k=0;k<6;k++) v-=s.B[12*k+j]*s.vb6[k]; out.biasj[j]=v; }
+    ASM_FOR(j,12){ double v=s.tauC[j]; for(int k=0;k<6;k++) v+=s.Mbj[12*k+j]*s.w6[k]; for(int k=0;k<6;k++) v-=s.B[12*k+j]*s.vb6[k]; out.biasj[j]=v; }
     // ---- D5: finite-difference terms -Jdot [v_c; qd] (wbc.cpp:384-402,504,507), then roll old <- current ----
     const double timeStep=1.0/P.loopRate;
-    LANE_FOR(i,12){
+    ASM_FOR(i,12){
         const double c=s.cmask[i/3]; double a=0,b=0;
         if(!switching){
             for(int k=0;k<18;k++){
@@ -118,24 +143,24 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     }
     WBC_SYNC();
     // Tdot^-1 (top rows) for the NEXT tick = -X [Tdot_b X, Tdot_j - Tdot_b B]   (wbc.cpp:293)
-    LANE_FOR(e,108){ int i=e/18,j=e%18; double v=0;
+    ASM_FOR(e,108){ int i=e/18,j=e%18; double v=0;
         if(!switching){ double told=first?((i==j)?1.0:0.0):st.Told[e]; v=(s.Ttop[e]-told)/timeStep; }
         s.Tdot[e]=v; }
     WBC_SYNC();
     if(plant){
-        LANE_FOR(i,3) plant[(size_t)i*N]=s.d[i];
-        LANE_FOR(e,72) plant[(size_t)(3+e)*N]=s.B[e];
-        LANE_FOR(i,6){ double v=0; for(int k=0;k<6;k++) v+=s.Tdot[18*i+k]*s.twist[k]; for(int k=0;k<12;k++) v+=s.Tdot[18*i+6+k]*s.qd[k]; plant[(size_t)(75+i)*N]=v; }
+        ASM_FOR(i,3) plant[(size_t)i*N]=s.d[i];
+        ASM_FOR(e,72) plant[(size_t)(3+e)*N]=s.B[e];
+        ASM_FOR(i,6){ double v=0; for(int k=0;k<6;k++) v+=s.Tdot[18*i+k]*s.twist[k]; for(int k=0;k<12;k++) v+=s.Tdot[18*i+6+k]*s.qd[k]; plant[(size_t)(75+i)*N]=v; }
     }
-    LANE_FOR(e,108){ int i=e/18,j=e%18; double v=0;
+    ASM_FOR(e,108){ int i=e/18,j=e%18; double v=0;
         if(j<6){ for(int k=0;k<6;k++) v+=s.Tdot[18*i+k]*s.X[6*k+j]; }
         else { v=s.Tdot[18*i+j]; for(int k=0;k<6;k++) v-=s.Tdot[18*i+k]*s.B[12*k+(j-6)]; }
         s.Y[e]=v; }
     WBC_SYNC();
-    LANE_FOR(e,108){ int i=e/18,j=e%18; double v=0; for(int k=0;k<6;k++) v+=s.X[6*i+k]*s.Y[18*k+j]; st.TdotInv[e]=-v; st.Told[e]=s.Ttop[e]; }
-    LANE_FOR(e,216){ const double c=s.cmask[e/54]; double jc=out.Jc[e]; st.Jstold[e]=c*jc; st.Jswold[e]=(1.0-c)*jc; }
+    ASM_FOR(e,108){ int i=e/18,j=e%18; double v=0; for(int k=0;k<6;k++) v+=s.X[6*i+k]*s.Y[18*k+j]; st.TdotInv[e]=-v; st.Told[e]=s.Ttop[e]; }
+    ASM_FOR(e,216){ const double c=s.cmask[e/54]; double jc=out.Jc[e]; st.Jstold[e]=c*jc; st.Jswold[e]=(1.0-c)*jc; }
     // ---- D6: desired wrench (wbc.cpp:426-445), swing command (wbc.cpp:447-464) ----
-    LANE_FOR(i,6){
+    ASM_FOR(i,6){
         const double kp=(i==2)?P.kpValueZ:P.kpValue;
         double mcb=0; for(int k=0;k<6;k++) mcb+=out.Mbb[6*i+k]*s.acc_d[k];     // needs out.Mbb: written before the D3 barrier
         const double gw=(i==2)?mc_.total_mass*GRAV:0.0;
@@ -143,18 +168,18 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
         s.W[i]=-kp*(s.pose[i]-s.pose_d[i])-P.kdValue*(s.vcom[i]-s.vel_d[i])-P.kiValue*integ+gw+mcb;
         st.integral[i]=integ+(s.pose[i]-s.pose_d[i])/P.loopRate;
     }
-    LANE_FOR(i,12){
+    ASM_FOR(i,12){
         double r=s.swa[i]+P.kdSwingValue*(s.swv[i]-s.footvw[i])+P.kpSwingValue*(s.swp[i]-s.footpw[i]);
         s.rcmd[i]=r*(1.0-s.cmask[i/3]);
     }
     WBC_SYNC();
     // ---- D7: QP vectors and the only dense H block (wbc.cpp:468-515) ----
-    LANE_FOR(e,144){ int i=e/12,j=e%12; double ci=s.cmask[i/3],cj=s.cmask[j/3]; double v=0;
+    ASM_FOR(e,144){ int i=e/12,j=e%12; double ci=s.cmask[i/3],cj=s.cmask[j/3]; double v=0;
         for(int k=0;k<6;k++) v+=(ci*out.Jc[18*i+k])*(cj*out.Jc[18*j+k]);
         out.Hff[e]=v+((i==j)?1.0:0.0); }
-    LANE_FOR(i,12){ double ci=s.cmask[i/3]; double v=0; for(int k=0;k<6;k++) v+=(ci*out.Jc[18*i+k])*s.W[k]; out.gf[i]=-v; }
+    ASM_FOR(i,12){ double ci=s.cmask[i/3]; double v=0; for(int k=0;k<6;k++) v+=(ci*out.Jc[18*i+k])*s.W[k]; out.gf[i]=-v; }
     const double INF=1.0e20;
-    LANE_FOR(i,70){
+    ASM_FOR(i,70){
         double lo,up;
         if(i<6){ const double gw=(i==2)?mc_.total_mass*GRAV:0.0; lo=-gw; up=-gw; }
         else if(i<18){ lo=-s.Jdv_st[i-6]; up=lo; }

@@ -27,34 +27,66 @@ struct BatchIn {      // SoA, instance index fastest
 };
 struct BatchOut { double *tau,*grf,*x,*com; int *rc,*nwsr; signed char* ws; };
 
-#ifndef WBC_UPD_MINBLOCKS
-#define WBC_UPD_MINBLOCKS 8          // resident CTAs per SM the register allocation of kernel 1 is sized for
-#endif
 __constant__ ModelConst c_model;
 
-// ---------------------------------------------------------------- kernel 1: RBD + centroidal transform + QP assembly
-// grid-stride over instances; the RBD stage is ~40 kFLOP per robot, far below the solver's cost
-__global__ void __launch_bounds__(32,WBC_UPD_MINBLOCKS) wbc_update_state_kernel(int N,Params prm,BatchIn in,CtrlState* st,QPData* qpd,unsigned char* first,double* com,double* plantAux){
+// ---------------------------------------------------------------- kernel 1a: rigid-body dynamics of the legs, one THREAD per (robot, leg)
+// The four legs of a robot only couple through the base, so FK, CRBA, RNEA and the foot Jacobian columns of one leg are one independent
+// register-resident job (wbc_rbd.cuh).  Run per warp-of-one-robot that job kept 4 of 32 lanes busy (r01: 10.2 active lanes on average); here
+// a warp carries 8 robots x 4 legs = 32 such jobs.  Lane -> (robot, leg) with the leg fastest: the 3 q / qd loads of a warp touch 4 rows x 8
+// consecutive robots of the SoA inputs (64-byte runs).  Output: one 67-double LegOut record per (robot, leg), read back coalesced by kernel 1b.
+__global__ void __launch_bounds__(128) wbc_rbd_legs_kernel(int N,BatchIn in,LegOut* legs){
     __shared__ ModelConst mc;
-    __shared__ RbdScratch s;
-    __shared__ QPData qp;
-    const int lane=threadIdx.x;
-    { const double* src=(const double*)&c_model; double* dst=(double*)&mc; LANE_FOR(i,MODEL_DOUBLES) dst[i]=src[i]; }
+    { const double* src=(const double*)&c_model; double* dst=(double*)&mc; for(int i=threadIdx.x;i<MODEL_DOUBLES;i+=blockDim.x) dst[i]=src[i]; }
+    __syncthreads();
+    const int t=blockIdx.x*blockDim.x+threadIdx.x, r=t>>2, leg=t&3;
+    if(r>=N) return;
+    LegScratch s;
+    for(int k=0;k<3;k++){ s.q[k]=in.q[(size_t)(3*leg+k)*N+r]; s.qd[k]=in.qd[(size_t)(3*leg+k)*N+r]; }
+    { double qu[4]={in.quat[r],in.quat[(size_t)N+r],in.quat[(size_t)2*N+r],in.quat[(size_t)3*N+r]}, R[9], tw[6];
+      for(int k=0;k<6;k++) tw[k]=in.twist[(size_t)k*N+r];
+      quat_to_R(qu,R); mtv3(R,tw,s.vbody); mtv3(R,tw+3,s.vbody+3); }                    // MIXED -> body-fixed (KDC.cpp:822-825), same operations as kernel 1b
+    rbd_leg(mc,s,leg,0);
+    LegOut& o=legs[(size_t)r*4+leg];
+    for(int i=0;i<13;i++) o.crb[i]=s.crb[0][i];
+    for(int k=0;k<3;k++) for(int i=0;i<6;i++) o.Fraw[k][i]=s.Fraw[k][i];
+    for(int i=0;i<9;i++) o.Hleg[i]=s.Hleg[0][i];
+    for(int i=0;i<3;i++){ o.plin[i]=s.plin[0][i]; o.tauC[i]=s.tauC[i]; o.footp[i]=s.footp[0][i]; o.footv[i]=s.footv[0][i]; }
+    for(int i=0;i<6;i++) o.fb[i]=s.fb[0][i];
+    for(int k=0;k<3;k++) for(int i=0;i<3;i++) o.jcol[k][i]=s.jcol[k][i];
+}
+
+// ---------------------------------------------------------------- kernel 1b: centroidal transform + QP assembly, 32 / WBC_ASM_NL = 2 robots per warp
+// 16 lanes per robot (wbc_assembly.cuh); a warp takes consecutive robots, grid-stride.  Each group reads the four LegOut records of its robot
+// (268 consecutive doubles), runs the dense phase in its own slice of shared memory and writes the compact QP.  A group past the end of the batch
+// re-does the last robot in step with that robot's own group (same warp, same instructions, same values written): no divergent barriers.
+struct UpdSmem { RbdScratch s; QPData qp; };
+constexpr int UPD_GROUPS=32/WBC_ASM_NL;
+__global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,const LegOut* legs,CtrlState* st,QPData* qpd,unsigned char* first,double* com,double* plantAux){
+    extern __shared__ double smem[];
+    ModelConst& mc=*reinterpret_cast<ModelConst*>(smem);
+    const int lane=threadIdx.x&(WBC_ASM_NL-1), grp=threadIdx.x/WBC_ASM_NL;
+    UpdSmem& u=reinterpret_cast<UpdSmem*>(reinterpret_cast<char*>(smem)+sizeof(ModelConst))[grp];
+    RbdScratch& s=u.s; QPData& qp=u.qp;
+    { const double* src=(const double*)&c_model; double* dst=(double*)&mc; for(int i=threadIdx.x;i<MODEL_DOUBLES;i+=32) dst[i]=src[i]; }
     WBC_SYNC();
-    for(int r=blockIdx.x;r<N;r+=gridDim.x){
-        LANE_FOR(k,12){ s.q[k]=in.q[k*N+r]; s.qd[k]=in.qd[k*N+r]; s.swp[k]=in.swp[k*N+r]; s.swv[k]=in.swv[k*N+r]; s.swa[k]=in.swa[k*N+r]; }
-        LANE_FOR(k,6){ s.twist[k]=in.twist[k*N+r]; s.pose_d[k]=in.pose[k*N+r]; s.vel_d[k]=in.vel[k*N+r]; s.acc_d[k]=in.acc[k*N+r]; }
-        LANE_FOR(k,3) s.pb[k]=in.pos[k*N+r];
-        LANE_FOR(k,4) s.cmask[k]=in.contacts[k*N+r]?1.0:0.0;
+    for(int r0=blockIdx.x*UPD_GROUPS;r0<N;r0+=gridDim.x*UPD_GROUPS){
+        const int r=(r0+grp<N)?r0+grp:N-1;
+        ASM_FOR(k,12){ s.q[k]=in.q[k*N+r]; s.qd[k]=in.qd[k*N+r]; s.swp[k]=in.swp[k*N+r]; s.swv[k]=in.swv[k*N+r]; s.swa[k]=in.swa[k*N+r]; }
+        ASM_FOR(k,6){ s.twist[k]=in.twist[k*N+r]; s.pose_d[k]=in.pose[k*N+r]; s.vel_d[k]=in.vel[k*N+r]; s.acc_d[k]=in.acc[k*N+r]; }
+        ASM_FOR(k,3) s.pb[k]=in.pos[k*N+r];
+        ASM_FOR(k,4) s.cmask[k]=in.contacts[k*N+r]?1.0:0.0;
         if(lane==0){ double qu[4]={in.quat[r],in.quat[N+r],in.quat[2*N+r],in.quat[3*N+r]}; quat_to_R(qu,s.Rwb); }
+        { const double* src=(const double*)&legs[(size_t)r*4];                            // leg-phase results of kernel 1a -> the scratch fields the dense phase reads
+          ASM_FOR(i,4*LEGOUT_DOUBLES){ const int l=i/LEGOUT_DOUBLES, o=i-l*LEGOUT_DOUBLES; const double v=src[i];
+              if(o<13) s.crb[l][o]=v; else if(o<31) (&s.Fraw[3*l][0])[o-13]=v; else if(o<40) s.Hleg[l][o-31]=v; else if(o<43) s.plin[l][o-40]=v;
+              else if(o<49) s.fb[l][o-43]=v; else if(o<52) s.tauC[3*l+o-49]=v; else if(o<55) s.footp[l][o-52]=v; else if(o<58) s.footv[l][o-55]=v;
+              else (&s.jcol[3*l][0])[o-58]=v; } }
         WBC_SYNC();
         if(lane==0){ mtv3(s.Rwb,s.twist,s.vbody); mtv3(s.Rwb,s.twist+3,s.vbody+3); }   // MIXED -> body-fixed (KDC.cpp:822-825)
         WBC_SYNC();
-        if(lane<4) rbd_leg(mc,s,lane);
-        WBC_SYNC();
         wbc_assemble(mc,prm,s,st[r],qp,lane,(int)in.switching[r],(int)first[r],plantAux?plantAux+r:nullptr,N);
-        { const double* src=(const double*)&qp; double* dst=(double*)&qpd[r]; LANE_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
-        LANE_FOR(k,3) com[k*N+r]=s.com[k];
+        { const double* src=(const double*)&qp; double* dst=(double*)&qpd[r]; ASM_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
+        ASM_FOR(k,3) com[k*N+r]=s.com[k];
         WBC_SYNC();
     }
 }
@@ -257,14 +289,14 @@ struct wbc_handle {
     double *q=nullptr,*qd=nullptr,*pos=nullptr,*quat=nullptr,*twist=nullptr,*pose=nullptr,*vel=nullptr,*acc=nullptr,*swp=nullptr,*swv=nullptr,*swa=nullptr;
     unsigned char *contacts=nullptr,*prevc=nullptr,*switching=nullptr,*first=nullptr;
     // persistent per-robot state and intermediates
-    CtrlState* ctrl=nullptr; QPData* qpd=nullptr; QPState* qps=nullptr; int* counter=nullptr; long long* prof=nullptr;
+    LegOut* legs=nullptr; CtrlState* ctrl=nullptr; QPData* qpd=nullptr; QPState* qps=nullptr; int* counter=nullptr; long long* prof=nullptr;
     // outputs
     double *tau=nullptr,*grf=nullptr,*x=nullptr,*com=nullptr; int *rc=nullptr,*nwsr=nullptr; signed char* ws=nullptr;
     cudaEvent_t ev[4]={nullptr,nullptr,nullptr,nullptr};
     // planner / plant / rollout
     PlannerState* planner=nullptr; PlannerParams plannerParams; double* plannerCmd=nullptr; unsigned char* published=nullptr;
     double* plantAux=nullptr; int* stats=nullptr; long long tick=0;
-    int smCount=0, qpBlocksPerSM=1, cohortMode=-1; size_t qpSmem=0;
+    int smCount=0, qpBlocksPerSM=1, cohortMode=-1, updBlocksPerSM=1; size_t qpSmem=0, updSmem=0;
     double* duals=nullptr;
     QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false; size_t setupPad=0;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     long long launches=0;
@@ -318,7 +350,7 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     ok=ok&&dalloc(h->q,12*N)==cudaSuccess&&dalloc(h->qd,12*N)==cudaSuccess&&dalloc(h->pos,3*N)==cudaSuccess&&dalloc(h->quat,4*N)==cudaSuccess&&dalloc(h->twist,6*N)==cudaSuccess;
     ok=ok&&dalloc(h->pose,6*N)==cudaSuccess&&dalloc(h->vel,6*N)==cudaSuccess&&dalloc(h->acc,6*N)==cudaSuccess&&dalloc(h->swp,12*N)==cudaSuccess&&dalloc(h->swv,12*N)==cudaSuccess&&dalloc(h->swa,12*N)==cudaSuccess;
     ok=ok&&dalloc(h->contacts,4*N)==cudaSuccess&&dalloc(h->prevc,4*N)==cudaSuccess&&dalloc(h->switching,N)==cudaSuccess&&dalloc(h->first,N)==cudaSuccess;
-    ok=ok&&dalloc(h->ctrl,N)==cudaSuccess&&dalloc(h->qpd,N)==cudaSuccess&&dalloc(h->qps,N)==cudaSuccess&&dalloc(h->counter,1)==cudaSuccess;
+    ok=ok&&dalloc(h->legs,4*N)==cudaSuccess&&dalloc(h->ctrl,N)==cudaSuccess&&dalloc(h->qpd,N)==cudaSuccess&&dalloc(h->qps,N)==cudaSuccess&&dalloc(h->counter,1)==cudaSuccess;
     ok=ok&&dalloc(h->tau,12*N)==cudaSuccess&&dalloc(h->grf,12*N)==cudaSuccess&&dalloc(h->x,42*N)==cudaSuccess&&dalloc(h->com,3*N)==cudaSuccess;
     ok=ok&&dalloc(h->rc,N)==cudaSuccess&&dalloc(h->nwsr,N)==cudaSuccess&&dalloc(h->ws,112*N)==cudaSuccess;
     if(!ok){ h->err=std::string("cudaMalloc: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_NOMEM); }
@@ -336,6 +368,10 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     h->devParams=P;
     if(cudaMemcpyToSymbol(c_model,&mc,sizeof(mc))!=cudaSuccess){
         h->err=std::string("cudaMemcpyToSymbol: ")+cudaGetErrorString(cudaGetLastError())+" (library built for sm_100a only)"; return fail(WBC_ERR_CUDA); }
+    h->updSmem=sizeof(ModelConst)+UPD_GROUPS*sizeof(UpdSmem);
+    if(cudaFuncSetAttribute(wbc_update_state_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->updSmem)!=cudaSuccess
+       ||cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->updBlocksPerSM,wbc_update_state_kernel,32,h->updSmem)!=cudaSuccess||h->updBlocksPerSM<1){
+        h->err=std::string("update-state kernel geometry: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     // solver launch geometry: one warp per CTA, as many CTAs per SM as shared memory allows
     h->qpSmem=sizeof(QPWork)*WBC_GANG;
     if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
@@ -360,7 +396,7 @@ extern "C" int wbc_destroy(wbc_handle* h){
     cudaSetDevice(h->device);
     if(h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
-                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre,h->duals};
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre,h->duals,h->legs};
     for(void* p:ptrs) if(p) cudaFree(p);
     for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
     if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
@@ -405,9 +441,11 @@ extern "C" int wbc_set_reference(wbc_handle* h,const double* pose,const double* 
 extern "C" int wbc_update_state(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
-    int grid=h->smCount*16; if(grid>h->N) grid=h->N;
+    int grid=h->smCount*h->updBlocksPerSM; if(grid>(h->N+UPD_GROUPS-1)/UPD_GROUPS) grid=(h->N+UPD_GROUPS-1)/UPD_GROUPS;
     CK(cudaEventRecord(h->ev[0],h->stream));
-    wbc_update_state_kernel<<<grid,32,0,h->stream>>>(h->N,h->devParams,batch_in(h),h->ctrl,h->qpd,h->first,h->com,h->plantAux);
+    wbc_rbd_legs_kernel<<<(4*h->N+127)/128,128,0,h->stream>>>(h->N,batch_in(h),h->legs);
+    h->launches++; CK(cudaGetLastError());
+    wbc_update_state_kernel<<<grid,32,h->updSmem,h->stream>>>(h->N,h->devParams,batch_in(h),h->legs,h->ctrl,h->qpd,h->first,h->com,h->plantAux);
     h->launches++; CK(cudaGetLastError());
     CK(cudaEventRecord(h->ev[1],h->stream));
     return WBC_OK;

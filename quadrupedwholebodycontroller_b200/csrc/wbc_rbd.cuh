@@ -42,6 +42,15 @@ struct RbdScratch {
     double Jdv_st[12], Jdv_sw[12], rcmd[12], footpw[12], footvw[12], Tdot[108], Y[108];
 };
 
+// what ONE leg hands to the dense phase (67 doubles): the record wbc_rbd_legs_kernel writes per (robot, leg) and wbc_update_state_kernel reads back
+struct LegOut { double crb[13], Fraw[3][6], Hleg[9], plin[3], fb[6], tauC[3], footp[3], footv[3], jcol[3][3]; };
+constexpr int LEGOUT_DOUBLES = sizeof(LegOut)/sizeof(double);
+// per-THREAD scratch of the leg kernel: same member names as RbdScratch, one leg wide (slot 0)
+struct LegScratch {
+    double q[3], qd[3], vbody[6];
+    double crb[1][13], Fraw[3][6], Hleg[1][9], plin[1][3], fb[1][6], tauC[3], footp[1][3], footv[1][3], jcol[3][3];
+};
+
 // S = [0; a] (RevoluteJoint.cpp:189-196).  spatial inertia (m, mc, I about the origin) times motion vector
 WBC_DEV void inertia_mul(double m,const double* mc,const double* I,const double* vl,const double* va,double* hl,double* ha){
     double t[3]; cross3(mc,va,t); hl[0]=m*vl[0]-t[0]; hl[1]=m*vl[1]-t[1]; hl[2]=m*vl[2]-t[2];
@@ -87,7 +96,8 @@ WBC_DEV void rot_axis(const double* u,double th,double* r){
 // One leg: forward pass (ForwardKinematics.cpp:144-226), CRBA (Dynamics.cpp:146-273), RNEA dynamic phase
 // (Dynamics.cpp:65-144) with zero gravity (== generalizedBiasForces - generalizedGravityForces, wbc.cpp:544-551),
 // foot frame position / velocity / Jacobian columns (Jacobians.cpp:16-52).
-WBC_FN void rbd_leg(const ModelConst& mc_,RbdScratch& s,int leg){
+// `slot` = index of the leg inside the scratch `s` (== leg for the per-robot RbdScratch, 0 for the per-thread LegScratch of wbc_rbd_legs_kernel).
+template<class S> WBC_DEV void rbd_leg(const ModelConst& mc_,S& s,int leg,int slot){
     double Rpc[3][9], Rb[3][9], pbk[3][3], vl[3][3], va[3][3], al[3][3], aa[3][3];
     const double* vb=s.vbody;
     double pvl[3]={vb[0],vb[1],vb[2]}, pva[3]={vb[3],vb[4],vb[5]};
@@ -96,12 +106,12 @@ WBC_FN void rbd_leg(const ModelConst& mc_,RbdScratch& s,int leg){
     double pR[9]={1,0,0,0,1,0,0,0,1}, pp[3]={0,0,0};
     for(int k=0;k<3;k++){
         const int b=1+3*leg+k; const double* ax=mc_.axis+3*b; const double* rp=mc_.restP+3*b;
-        double rot[9]; rot_axis(ax,s.q[3*leg+k],rot);
+        double rot[9]; rot_axis(ax,s.q[3*slot+k],rot);
         mm3(mc_.restR+9*b,rot,Rpc[k]);                                  // parent_X_child = rest * Rot(axis,q)
         mm3(pR,Rpc[k],Rb[k]);
         double t[3]; mv3(pR,rp,t); pbk[k][0]=t[0]+pp[0]; pbk[k][1]=t[1]+pp[1]; pbk[k][2]=t[2]+pp[2];
         xf_motion_inv(Rpc[k],rp,pvl,pva,vl[k],va[k]);
-        const double qd=s.qd[3*leg+k];
+        const double qd=s.qd[3*slot+k];
         double vjA[3]={ax[0]*qd,ax[1]*qd,ax[2]*qd};
         va[k][0]+=vjA[0]; va[k][1]+=vjA[1]; va[k][2]+=vjA[2];
         xf_motion_inv(Rpc[k],rp,pal,paa,al[k],aa[k]);
@@ -120,7 +130,7 @@ WBC_FN void rbd_leg(const ModelConst& mc_,RbdScratch& s,int leg){
         double c1[3],c2[3],c3[3]; cross3(va[k],hl,c1); cross3(vl[k],hl,c2); cross3(va[k],ha,c3);
         for(int i=0;i<3;i++){ fl[k][i]+=c1[i]; fa[k][i]+=c2[i]+c3[i]; }
     }
-    for(int i=0;i<3;i++) s.plin[leg][i]=pl[i];
+    for(int i=0;i<3;i++) s.plin[slot][i]=pl[i];
     // backward: RNEA torques + composite inertias + mass-matrix entries
     double cm[3], cmc[3][3], cI[3][9];
     for(int k=2;k>=0;k--){
@@ -133,31 +143,31 @@ WBC_FN void rbd_leg(const ModelConst& mc_,RbdScratch& s,int leg){
             xf_force(Rpc[k+1],mc_.restP+3*bc,fl[k+1],fa[k+1]);
             for(int i=0;i<3;i++){ fl[k][i]+=fl[k+1][i]; fa[k][i]+=fa[k+1][i]; }
         }
-        s.tauC[3*leg+k]=dot3(mc_.axis+3*b,fa[k]);
+        s.tauC[3*slot+k]=dot3(mc_.axis+3*b,fa[k]);
         // CRBA column of DOF (leg,k): F = Ic S
         double Fl[3],Fa[3],zero[3]={0,0,0}; inertia_mul(cm[k],cmc[k],cI[k],zero,mc_.axis+3*b,Fl,Fa);
-        s.Hleg[leg][3*k+k]=dot3(mc_.axis+3*b,Fa);
+        s.Hleg[slot][3*k+k]=dot3(mc_.axis+3*b,Fa);
         for(int a=k;a>=1;a--){
             xf_force(Rpc[a],mc_.restP+3*(1+3*leg+a),Fl,Fa);
             double h=dot3(mc_.axis+3*(3*leg+a),Fa);               // axis of body (leg,a-1)
-            s.Hleg[leg][3*k+(a-1)]=h; s.Hleg[leg][3*(a-1)+k]=h;
+            s.Hleg[slot][3*k+(a-1)]=h; s.Hleg[slot][3*(a-1)+k]=h;
         }
         xf_force(Rpc[0],mc_.restP+3*(1+3*leg),Fl,Fa);
-        for(int i=0;i<3;i++){ s.Fraw[3*leg+k][i]=Fl[i]; s.Fraw[3*leg+k][3+i]=Fa[i]; }
+        for(int i=0;i<3;i++){ s.Fraw[3*slot+k][i]=Fl[i]; s.Fraw[3*slot+k][3+i]=Fa[i]; }
     }
     { const int b=1+3*leg; double mcA[3],IA[9];
       xf_inertia(Rpc[0],mc_.restP+3*b,cm[0],cmc[0],cI[0],mcA,IA);
-      s.crb[leg][0]=cm[0]; for(int i=0;i<3;i++) s.crb[leg][1+i]=mcA[i]; for(int i=0;i<9;i++) s.crb[leg][4+i]=IA[i];
+      s.crb[slot][0]=cm[0]; for(int i=0;i<3;i++) s.crb[slot][1+i]=mcA[i]; for(int i=0;i<9;i++) s.crb[slot][4+i]=IA[i];
       xf_force(Rpc[0],mc_.restP+3*b,fl[0],fa[0]);
-      for(int i=0;i<3;i++){ s.fb[leg][i]=fl[0][i]; s.fb[leg][3+i]=fa[0][i]; } }
+      for(int i=0;i<3;i++){ s.fb[slot][i]=fl[0][i]; s.fb[slot][3+i]=fa[0][i]; } }
     // foot frame (fixed in SHANK): position, velocity of its origin, Jacobian columns, all in base coordinates
     double pf[3]; { double t[3]; mv3(Rb[2],mc_.footP+3*leg,t); pf[0]=t[0]+pbk[2][0]; pf[1]=t[1]+pbk[2][1]; pf[2]=t[2]+pbk[2][2]; }
     { double c[3],t[3]; cross3(va[2],mc_.footP+3*leg,c); t[0]=vl[2][0]+c[0]; t[1]=vl[2][1]+c[1]; t[2]=vl[2][2]+c[2];
-      double w[3]; mv3(Rb[2],t,w); for(int i=0;i<3;i++){ s.footp[leg][i]=pf[i]; s.footv[leg][i]=w[i]; } }
+      double w[3]; mv3(Rb[2],t,w); for(int i=0;i<3;i++){ s.footp[slot][i]=pf[i]; s.footv[slot][i]=w[i]; } }
     for(int k=0;k<3;k++){
         double ab[3],r[3]={pf[0]-pbk[k][0],pf[1]-pbk[k][1],pf[2]-pbk[k][2]},c[3];
         mv3(Rb[k],mc_.axis+3*(1+3*leg+k),ab); cross3(ab,r,c);
-        for(int i=0;i<3;i++) s.jcol[3*leg+k][i]=c[i];
+        for(int i=0;i<3;i++) s.jcol[3*slot+k][i]=c[i];
     }
 }
 

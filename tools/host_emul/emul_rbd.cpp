@@ -24,7 +24,7 @@ extern "C" void emul_tick(const double* params16,const double* q,const double* q
     for(int i=0;i<4;i++) s.cmask[i]=contacts[i]?1.0:0.0;
     quat_to_R(quat,s.Rwb);
     mtv3(s.Rwb,s.twist,s.vbody); mtv3(s.Rwb,s.twist+3,s.vbody+3);
-    for(int leg=0;leg<4;leg++) rbd_leg(mc,s,leg);
+    for(int leg=0;leg<4;leg++) rbd_leg(mc,s,leg,leg);
     wbc_assemble(mc,P,s,*(CtrlState*)state,*(QPData*)qpdata,0,switching,first,nullptr,1);
 }
 extern "C" int emul_sizes(int which){ return which==0?CTRLSTATE_DOUBLES:QPDATA_DOUBLES; }
