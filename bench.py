@@ -333,6 +333,26 @@ def measure(name, steps, warmup, rank, world, local, robots=0, with_parity=True,
     return res
 
 
+def fp32_block(local, n=4096):
+    """cold4096 with the single-precision build of the solver: solver launch time and errors relative to the fp64 product on the same robots"""
+    import quadrupedwholebodycontroller_b200 as wbc
+    from quadrupedwholebodycontroller_b200 import workloads as wl
+    st, ref = wl.randomised(n, seed=1234, contacts="stance")
+    a = wbc.WholeBodyController(n, device=local); b = wbc.WholeBodyController(n, device=local, fp32=True)
+    ms = []
+    for rep in range(3):
+        for c in (a, b):
+            c.setInitialState(); c.setJointAndBaseState(**st); c.setReference(**ref); c.step(); c.synchronize()
+        ms.append((a.lastKernelMs()["solve_qp"], b.lastKernelMs()["solve_qp"]))
+    oa, ob = a.getOutputs(), b.getOutputs(); a.close(); b.close()
+    ok = (oa["rc"] == 0) & (ob["rc"] == 0)
+    rel = lambda x, y: float((np.abs(x - y).max(axis=0) / np.maximum(1.0, np.abs(y).max(axis=0)))[ok].max())
+    t64, t32 = min(m[0] for m in ms), min(m[1] for m in ms)
+    return dict(workload="cold4096", dtype="f32 (QP solver; RBD and assembly stay f64)", solve_qp_ms=t32, solve_qp_ms_f64=t64, solver_solves_per_s=n / t32 * 1e3, speedup_vs_f64=t64 / t32,
+                max_rel_tau_vs_f64=rel(ob["tau"], oa["tau"]), max_rel_grf_vs_f64=rel(ob["grf"], oa["grf"]), rc_equal=float((oa["rc"] == ob["rc"]).mean()),
+                rc0_frac=float((ob["rc"] == 0).mean()), ws_equal=float((oa["ws"] == ob["ws"]).all(axis=0)[ok].mean()), nwsr_mean=float(ob["nwsr"].mean()), tolerance=1e-4)
+
+
 def summarise(name, res, steps, warmup, world, peaks, ncu):
     """the JSON fields of one measured workload"""
     spec, n, ro = res["spec"], res["n"], res["ro"]
@@ -416,6 +436,9 @@ def main():
             also[name] = dict(value=s2["value"], unit=UNIT, steps=k, warmup=3, ms_per_step=s2["ms_per_step"], e2e=s2["e2e"], latency_ms=s2["latency_ms"],
                               tick_latency_ms=s2.get("tick_latency_ms"), fp64_frac=s2["roofline"]["frac"], algorithmic_mflop_per_solve=s2["roofline"]["algorithmic_mflop_per_solve"],
                               kernels_ms=s2["kernels_ms"], solver=s2["solver"], parity=s2.get("parity"), gpu_launches=s2["gpu_launches"], robots_per_gpu=r2["n"], description=WORKLOADS[name]["desc"])
+        # the north star's optional fp32 mode: same batch, solver in single precision (libwbc_b200_f32.so), errors against the fp64 run
+        if rank == 0:
+            also["fp32_mode"] = fp32_block(local)
         line["also"] = also
     if rank == 0 and not args.no_cpu_baseline:
         n_sample = 128 if ro else (2048 if spec["cold"] else 8192)

@@ -9,7 +9,7 @@ import os
 
 import numpy as np
 
-from .build import build_library, LIB_PATH, PROF_LIB_PATH, EXACT_LIB_PATH
+from .build import build_library, LIB_PATH, PROF_LIB_PATH, EXACT_LIB_PATH, F32_LIB_PATH
 
 NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC = 12, 4, 42, 70          # whole_body_controller.hpp:27-32 of the reference
 _libs = {}
@@ -34,10 +34,10 @@ class WbcPlannerParams(C.Structure):
                                           "body_final_velocity", "dt")]
 
 
-def load_library(profiling=False, exact=False):
+def load_library(profiling=False, exact=False, fp32=False):
     """dlopen the CUDA library (profiling=True: the -DWBC_PROFILE build of the same sources; exact=True: the -DWBC_EXACT verification build that
     reproduces qpOASES' arithmetic operation by operation); raises if it has not been built (no fallback of any kind)."""
-    path = EXACT_LIB_PATH if exact else (PROF_LIB_PATH if profiling else LIB_PATH)
+    path = F32_LIB_PATH if fp32 else (EXACT_LIB_PATH if exact else (PROF_LIB_PATH if profiling else LIB_PATH))      # fp32=True: the QP solver in single precision
     if path not in _libs:
         if not os.path.exists(path):
             raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
@@ -115,8 +115,8 @@ class WholeBodyController:
 
     numberOfJoints, numberOfLegs, qpNumberOfVariables, qpNumberOfConstraints = NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC
 
-    def __init__(self, n_robots, device=0, params=None, stream=None, profiling=False, exact=False):
-        lib = self._lib = load_library(profiling, exact)
+    def __init__(self, n_robots, device=0, params=None, stream=None, profiling=False, exact=False, fp32=False):
+        lib = self._lib = load_library(profiling, exact, fp32)
         self.N = int(n_robots)
         self._h = C.c_void_p()
         p = params if params is not None else default_params()

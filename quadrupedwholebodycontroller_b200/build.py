@@ -6,6 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.environ.get("WBC_B200_LIB") or os.path.join(HERE, "libwbc_b200.so")     # override = DEV experiments with another build of the same CUDA library
 EXACT_LIB_PATH = os.path.join(HERE, "libwbc_b200_exact.so")   # same sources with -DWBC_EXACT -fmad=false: qpOASES' arithmetic operation by operation (verification only, slower)
+F32_LIB_PATH = os.path.join(HERE, "libwbc_b200_f32.so")       # same sources with -DWBC_FP32: the QP solver in single precision (qpOASES' __USE_SINGLE_PRECISION__ tolerances); RBD / assembly stay fp64
 PROF_LIB_PATH = os.path.join(HERE, "libwbc_b200_prof.so")     # same sources with -DWBC_PROFILE: clock64 phase timers + algorithmic-flop counter (measurement only)
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -38,6 +39,8 @@ def build_library(force=False, verbose=False):
         jobs.append(subprocess.Popen([nvcc] + NVCC_FLAGS + ["-DWBC_PROFILE", os.path.join(CSRC, "wbc_kernels.cu"), "-o", PROF_LIB_PATH]))
     if force or _stale(EXACT_LIB_PATH):
         jobs.append(subprocess.Popen([nvcc] + NVCC_FLAGS + ["-DWBC_EXACT", "-fmad=false", os.path.join(CSRC, "wbc_kernels.cu"), "-o", EXACT_LIB_PATH]))
+    if force or _stale(F32_LIB_PATH):
+        jobs.append(subprocess.Popen([nvcc] + NVCC_FLAGS + ["-DWBC_FP32", os.path.join(CSRC, "wbc_kernels.cu"), "-o", F32_LIB_PATH]))
     for j in jobs:
         if j.wait() != 0:
             raise RuntimeError("nvcc failed building the CUDA library")

@@ -21,7 +21,13 @@
   // base (S2R SR_CgaCtaId + MOV + LEA) at every predicated access inside the noinline routines.  READ-ONLY data of the calling routine only
   // (the asm is not volatile and has no memory clobber, so the compiler may move or merge these loads).
   WBC_DEV unsigned wbc_saddr(const void* p){ unsigned a=(unsigned)__cvta_generic_to_shared(p); asm volatile("" : "+r"(a)); return a; }   // opaque: stays in a register
+#if defined(WBC_FP32)
+  WBC_DEV float wbc_lds(unsigned a){ float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+  WBC_DEV float wbc_max(float v){ for(int o=16;o>0;o>>=1){ float t=__shfl_xor_sync(0xffffffffu,v,o); v = t>v?t:v; } return v; }
+  WBC_DEV float wbc_bcast(float v,int src){ return __shfl_sync(0xffffffffu,v,src); }
+#else
   WBC_DEV double wbc_lds(unsigned a){ double v; asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
+#endif
   WBC_DEV unsigned wbc_ballot(bool p){ return __ballot_sync(0xffffffffu,p); }
   WBC_DEV double wbc_max(double v){ for(int o=16;o>0;o>>=1){ double t=__shfl_xor_sync(0xffffffffu,v,o); v = t>v?t:v; } return v; }
   WBC_DEV double wbc_bcast(double v,int src){ return __shfl_sync(0xffffffffu,v,src); }
@@ -38,6 +44,8 @@
   WBC_DEV unsigned wbc_ballot(bool p){ return p?1u:0u; }
   WBC_DEV double wbc_max(double v){ return v; }
   WBC_DEV double wbc_bcast(double v,int){ return v; }
+  WBC_DEV float wbc_max(float v){ return v; }
+  WBC_DEV float wbc_bcast(float v,int){ return v; }
   WBC_DEV int    wbc_bcasti(int v,int){ return v; }
   WBC_DEV int    wbc_ffs(unsigned m){ return m?0:-1; }
   WBC_DEV int    wbc_popc(unsigned m){ return m?1:0; }
@@ -57,6 +65,14 @@
 
 namespace wbc {
 
+// arithmetic type of the QP solver: fp64 like qpOASES' default build, or fp32 (-DWBC_FP32 -> libwbc_b200_f32.so, the north star's optional mode:
+// qpOASES' __USE_SINGLE_PRECISION__ constants and tolerances).  RBD, assembly, planner and plant always run in fp64.
+#if defined(WBC_FP32)
+  typedef float real;
+#else
+  typedef double real;
+#endif
+
 constexpr int NJ=12, NLEG=4, NV=42, NC=70;              // whole_body_controller.hpp:27-32
 constexpr double GRAV=9.81;
 
@@ -72,17 +88,20 @@ struct Params {
 //   A rows 0:6   [Mbb 0 -Jst_b^T 0]      rows 6:18  [Jst_b Jst_j 0 0]     rows 18:34 [0 0 Dfr 0]
 //     rows 34:46 [0 Mjj -Jst_j^T 0]      rows 46:58 [Jsw_b Jsw_j 0 -I]    rows 58:70 [Jsw_b Jsw_j 0 +I]
 // with Jst = c (.) Jc and Jsw = (1-c) (.) Jc row masks of ONE centroidal foot Jacobian Jc (12x18).
-struct QPData {
-    double Jc[12*18];      // centroidal foot Jacobian (all four feet, unmasked), row-major
-    double Mbb[36];        // centroidal mass matrix, base block
-    double Mjj[144];       // centroidal mass matrix, joint block
-    double Hff[144];       // H[18:30,18:30]
-    double gf[12];         // g[18:30]
-    double lbA[70], ubA[70];
-    double biasj[12];      // centroidal bias, joint part (for the torque recovery, wbc.cpp:565-568)
-    double mu, rho;
-    double cmask[4];       // 1.0 = stance, 0.0 = swing  (leg order LH, LF, RF, RH)
+template<class T> struct QPDataT {
+    typedef T value_type;
+    T Jc[12*18];      // centroidal foot Jacobian (all four feet, unmasked), row-major
+    T Mbb[36];        // centroidal mass matrix, base block
+    T Mjj[144];       // centroidal mass matrix, joint block
+    T Hff[144];       // H[18:30,18:30]
+    T gf[12];         // g[18:30]
+    T lbA[70], ubA[70];
+    T biasj[12];      // centroidal bias, joint part (for the torque recovery, wbc.cpp:565-568)
+    T mu, rho;
+    T cmask[4];       // 1.0 = stance, 0.0 = swing  (leg order LH, LF, RF, RH)
 };
+typedef QPDataT<double> QPData;      // what the assembly kernel writes to HBM (always fp64)
+typedef QPDataT<real> QPDataR;       // the solver's copy in shared memory, in its arithmetic type
 constexpr int QPDATA_DOUBLES = sizeof(QPData)/sizeof(double);
 
 // ---- per-instance persistent controller state (wbc.hpp:150-161) kept in HBM between ticks ----

@@ -146,11 +146,11 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
 #else
         // all global loads of a robot are issued before the first shared store: the workspace is reached through a generic pointer, so the
         // compiler will not move a load above a store by itself and every 32-element round would cost a full memory round trip
-        { const double* src=(const double*)&qpd[r]; double* dst=(double*)&w.qp; constexpr int K=(QPDATA_DOUBLES+31)/32; double t[K];
+        { const double* src=(const double*)&qpd[r]; real* dst=(real*)&w.qp; constexpr int K=(QPDATA_DOUBLES+31)/32; double t[K];      // fp64 in HBM -> the solver's type
           #pragma unroll
           for(int k=0;k<K;k++){ const int i=lane+32*k; t[k]=(i<QPDATA_DOUBLES)?__ldg(src+i):0.0; }
           #pragma unroll
-          for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPDATA_DOUBLES) dst[i]=t[k]; } }
+          for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPDATA_DOUBLES) dst[i]=(real)t[k]; } }
 #endif
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
 #if defined(WBC_PROFILE)
@@ -160,13 +160,13 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
 #endif
         QPState& S=qs[r];
         if(!isFirst){
-            double tx[2],tl[2],tu[2],ty[4],ta[3],tb[3]; signed char sb[2],sc[3];
+            real tx[2],tl[2],tu[2],ty[4],ta[3],tb[3]; signed char sb[2],sc[3];
             #pragma unroll
-            for(int k=0;k<2;k++){ const int i=lane+32*k; const bool in=i<42; tx[k]=in?S.x[i]:0.0; tl[k]=in?S.lb[i]:0.0; tu[k]=in?S.ub[i]:0.0; sb[k]=in?S.bstat[i]:(signed char)0; }
+            for(int k=0;k<2;k++){ const int i=lane+32*k; const bool in=i<42; tx[k]=in?S.x[i]:real(0); tl[k]=in?S.lb[i]:real(0); tu[k]=in?S.ub[i]:real(0); sb[k]=in?S.bstat[i]:(signed char)0; }
             #pragma unroll
-            for(int k=0;k<4;k++){ const int i=lane+32*k; ty[k]=(i<112)?S.y[i]:0.0; }
+            for(int k=0;k<4;k++){ const int i=lane+32*k; ty[k]=(i<112)?S.y[i]:real(0); }
             #pragma unroll
-            for(int k=0;k<3;k++){ const int i=lane+32*k; const bool in=i<70; ta[k]=in?S.Ax_l[i]:0.0; tb[k]=in?S.Ax_u[i]:0.0; sc[k]=in?S.cstat[i]:(signed char)0; }
+            for(int k=0;k<3;k++){ const int i=lane+32*k; const bool in=i<70; ta[k]=in?S.Ax_l[i]:real(0); tb[k]=in?S.Ax_u[i]:real(0); sc[k]=in?S.cstat[i]:(signed char)0; }
             c.rampOffset=S.rampOffset; c.status=S.status;
             #pragma unroll
             for(int k=0;k<2;k++){ const int i=lane+32*k; if(i<42){ w.x[i]=tx[k]; w.lb[i]=tl[k]; w.ub[i]=tu[k]; w.bstat[i]=sb[k]; } }
@@ -182,16 +182,16 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
         // QProblemB::getPrimalSolution (QProblemB.cpp:774-793) hands x out only in these three states; otherwise the caller's qpSolution_ keeps
         // its previous value (wbc.cpp:536) -- and so does out.x.  The solver's own iterate S.x is stored regardless (it IS the SQProblem member).
         const bool haveSol=(c.status==QPS_AUXILIARYQPSOLVED||c.status==QPS_HOMOTOPYQPSOLVED||c.status==QPS_SOLVED);
-        LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; if(haveSol) out.x[i*N+r]=w.x[i]; else w.x[i]=out.x[i*N+r]; out.ws[i*N+r]=w.bstat[i]; }
+        LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; if(haveSol) out.x[i*N+r]=w.x[i]; else w.x[i]=(real)out.x[i*N+r]; out.ws[i*N+r]=w.bstat[i]; }
         LANE_FOR(i,112) S.y[i]=w.y[i];
         LANE_FOR(i,70){ S.Ax_l[i]=w.Ax_l[i]; S.Ax_u[i]=w.Ax_u[i]; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; }
         WBC_SYNC();
         // computeJointTorques (wbc.cpp:553-577) on the solution still in shared memory: tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*, f* = x[18:30];
         // a robot whose solve did not return 0 publishes zero torques (terminate(), :626-635).  w.x = qpSolution_ here (see above).
-        if(lane<12){ const int i=lane; const QPData& q=WQP;
-            double s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*w.x[6+j];
-            double t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*w.x[18+j];
-            out.tau[i*N+r]= (rcv==0)? (s+q.biasj[i]-t) : 0.0;
+        if(lane<12){ const int i=lane; const QPDataR& q=WQP;
+            real s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*w.x[6+j];
+            real t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*w.x[18+j];
+            out.tau[i*N+r]= (rcv==0)? (double)(s+q.biasj[i]-t) : 0.0;
             out.grf[i*N+r]= w.x[18+i]; }
         if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
                      if(stats){ stats[r]+=1; if(rcv!=0) stats[N+r]+=1; stats[2*N+r]+=nWSR; if(nWSR>stats[3*N+r]) stats[3*N+r]=nWSR; }   // ticks, failed ticks, sum / max of nWSR

@@ -47,14 +47,26 @@ enum : int { QPS_NOTINITIALISED=0, QPS_PREPARINGAUXILIARYQP=1, QPS_AUXILIARYQPSO
 enum : int { ST_LOWER=-1, ST_INACTIVE=0, ST_UPPER=1 };     // Types.hpp:272-280
 
 // Constants.hpp:48-64 and Options::setToReliable (Options.cpp:91-189)
-constexpr double QEPS=2.221e-16, QZERO=1.0e-25, QINFTY=1.0e20;
-constexpr double OPT_terminationTolerance=5.0e6*QEPS, OPT_boundTolerance=1.0e6*QEPS, OPT_boundRelaxation=1.0e4,
-                 OPT_epsNum=-1.0e3*QEPS, OPT_epsDen=1.0e3*QEPS, OPT_maxPrimalJump=1.0e8, OPT_maxDualJump=1.0e8,
-                 OPT_initialFarBounds=1.0e6, OPT_growFarBounds=1.0e3, OPT_epsFlipping=1.0e3*QEPS, OPT_epsIterRef=1.0e2*QEPS,
-                 OPT_epsLITests=1.0e5*QEPS, OPT_ramp0=0.5, OPT_ramp1=1.0;
+#if defined(WBC_FP32)
+// qpOASES built with __USE_SINGLE_PRECISION__: Constants.hpp:46-47, Options.cpp:111-152 (setToDefault) and :203-207 (setToReliable: 3 refinement steps)
+constexpr real QEPS=real(1.193e-07), QZERO=real(1.0e-25), QINFTY=real(1.0e20);
+constexpr real OPT_terminationTolerance=real(1.0e2)*QEPS, OPT_boundTolerance=real(1.0e2)*QEPS, OPT_boundRelaxation=real(1.0e4),
+                 OPT_epsNum=-real(1.0e2)*QEPS, OPT_epsDen=real(1.0e2)*QEPS, OPT_maxPrimalJump=real(1.0e8), OPT_maxDualJump=real(1.0e8),
+                 OPT_initialFarBounds=real(1.0e6), OPT_growFarBounds=real(1.0e3), OPT_epsFlipping=real(5.0e1)*QEPS, OPT_epsIterRef=real(1.0e2)*QEPS,
+                 OPT_epsLITests=real(5.0e1)*QEPS, OPT_ramp0=real(0.5), OPT_ramp1=real(1.0);
+constexpr int OPT_numRefinementSteps=3;
+// the shortcut of the full linear-independence test only trusts clear cases in single precision: everything below 1e-2 |a| runs the reference's test
+constexpr real LI_SURE=real(1.0e-2), LI_NONE=real(-1.0);
+#else
+constexpr real QEPS=real(2.221e-16), QZERO=real(1.0e-25), QINFTY=real(1.0e20);
+constexpr real OPT_terminationTolerance=real(5.0e6)*QEPS, OPT_boundTolerance=real(1.0e6)*QEPS, OPT_boundRelaxation=real(1.0e4),
+                 OPT_epsNum=-real(1.0e3)*QEPS, OPT_epsDen=real(1.0e3)*QEPS, OPT_maxPrimalJump=real(1.0e8), OPT_maxDualJump=real(1.0e8),
+                 OPT_initialFarBounds=real(1.0e6), OPT_growFarBounds=real(1.0e3), OPT_epsFlipping=real(1.0e3)*QEPS, OPT_epsIterRef=real(1.0e2)*QEPS,
+                 OPT_epsLITests=real(1.0e5)*QEPS, OPT_ramp0=real(0.5), OPT_ramp1=real(1.0);
 constexpr int OPT_numRefinementSteps=2;
 // verdict of the full linear-independence test without running it: max|Z'a| > LI_SURE |a| -> independent, <= LI_NONE |a| -> dependent
-constexpr double LI_SURE=1.0e-6, LI_NONE=1.0e-12;
+constexpr real LI_SURE=real(1.0e-6), LI_NONE=real(1.0e-12);
+#endif
 
 constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
 constexpr int SIZET=42;               // sizeT = min(nV,nC)
@@ -121,7 +133,7 @@ WBC_HD int tri(int i){ return (i*(i+1))>>1; }
 
 // persistent solver state of one instance between ticks (HBM) -- what SQProblem keeps across hotstarts
 struct QPState {
-    double x[42], y[112], lb[42], ub[42], Ax_l[70], Ax_u[70];
+    real x[42], y[112], lb[42], ub[42], Ax_l[70], Ax_u[70];
     signed char bstat[42], cstat[70];   // working set; list ORDER is re-derived afresh by setupNewAuxiliaryQP
     int rampOffset, status, pad_;
 };
@@ -129,36 +141,36 @@ struct QPState {
 // per-instance shared-memory workspace (40.9 KB -> 5 instances per SM).  The members up to and including `arow` are all the warm-start
 // TQ rebuild touches (rebuild_TQ): the kernel that runs only that phase allocates just this prefix (QPWORK_TQ_BYTES, 9 instances per SM).
 struct QPWork {
-    double Q[42*LD];
-    double RT[TRI42+1];                         // packed R and T (see RR / TT)
+    real Q[42*LD];
+    real RT[TRI42+1];                         // packed R and T (see RR / TT)
     signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70], pad_[2];
     // phase-local scratch, overlaid: Givens / row vectors + {ratio tests | step-direction temporaries} + LI-exchange vectors,
     // all of it reused as the 12 x nZ block (HZ)_force by the projected Cholesky (which runs when none of them is live)
     union {
         struct {
-            double wv[42], cs_c[42], cs_s[42], tmpv[42], arow[42];
-            union { struct { double num[70], den[70], dAx[70]; }; struct { double tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; };
-            double xFRy[42], xFRz[42], Zdz[42], ym[70];
+            real wv[42], cs_c[42], cs_s[42], tmpv[42], arow[42];
+            union { struct { real num[70], den[70], dAx[70]; }; struct { real tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; };
+            real xFRy[42], xFRz[42], Zdz[42], ym[70];
         };
-        double HZf[12*LD];
+        real HZf[12*LD];
     };
 #if defined(WBC_QPDATA_GLOBAL)
-    const QPData* qpg;                          // compact H, A, new g / lbA / ubA stay in global memory (L1/L2): read-only during the solve
+    const QPDataR* qpg;                         // compact H, A, new g / lbA / ubA stay in global memory (L1/L2): read-only during the solve
 #else
-    QPData qp;                                  // compact H, A, new g / lbA / ubA
+    QPDataR qp;                                 // compact H, A, new g / lbA / ubA
 #endif
-    double x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
-    double dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
-    double dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
-    double rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
+    real x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
+    real dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
+    real dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
+    real rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
 };
-constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(double)+408+5*42*sizeof(double);
-static_assert(offsetof(QPWork,wv)+5*42*sizeof(double)==QPWORK_TQ_BYTES,"layout of the TQ-rebuild prefix");
+constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(real)+408+5*42*sizeof(real);
+static_assert(offsetof(QPWork,wv)+5*42*sizeof(real)==QPWORK_TQ_BYTES,"layout of the TQ-rebuild prefix");
 
 // what the warm-start TQ rebuild hands to the solve kernel (HBM): Q = [Z Y], the nAC rows of T, the index lists
 struct QPPre {
-    double Q[42*LD];
-    double T[TRI42+1];                          // only the first tri(nAC) entries are written / read
+    real Q[42*LD];
+    real T[TRI42+1];                          // only the first tri(nAC) entries are written / read
     signed char AC[70], IAC[70], cstat[70], posAC[70];
     int nAC, nIAC;
     double flops;
@@ -171,8 +183,8 @@ struct QPCtx {
     int status, infeasible, unbounded, rampOffset;
     int frIdentity;      // 1 while the free list is 0,1,..,41 in this order (every warm start until a bound becomes active): products with Q skip the list indirection
     int farRampOffset;   // rampOffset at the last updateFarBounds
-    double farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
-    double tau;
+    real farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
+    real tau;
 #if defined(WBC_PROFILE)
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
     double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
@@ -195,50 +207,53 @@ struct QPCtx {
 #endif
 
 // ---------------------------------------------------------------- structured A and H
-WBC_HD double Ael(const QPData& q,int i,int j){
-    if(i<6){ if(j<6) return q.Mbb[6*i+j]; if(j<18||j>=30) return 0.0; int r=j-18; return -(q.cmask[r/3]*q.Jc[18*r+i]); }
-    if(i<18){ int r=i-6; return (j<18)? q.cmask[r/3]*q.Jc[18*r+j] : 0.0; }
-    if(i<34){ int r=i-18,l=r>>2,k=r&3,c=j-18-3*l; if(c<0||c>2) return 0.0;
-              double d = (c==2)? -q.mu : ((c==(k>>1))? ((k&1)?-1.0:1.0) : 0.0); return d*q.cmask[l]; }
-    if(i<46){ int r=i-34; if(j<6||j>=30) return 0.0; if(j<18) return q.Mjj[12*r+j-6]; int f=j-18; return -(q.cmask[f/3]*q.Jc[18*f+6+r]); }
-    { int r=(i<58)?i-46:i-58; if(j<18) return (1.0-q.cmask[r/3])*q.Jc[18*r+j]; if(j==30+r) return (i<58)?-1.0:1.0; return 0.0; }
+// element decoders in the type of the data they read (fp64 for the host-side dense-QP getter, `real` for the solver's shared-memory copy)
+template<class QD> WBC_HD typename QD::value_type Ael(const QD& q,int i,int j){
+    typedef typename QD::value_type T;
+    if(i<6){ if(j<6) return q.Mbb[6*i+j]; if(j<18||j>=30) return T(0.0); int r=j-18; return -(q.cmask[r/3]*q.Jc[18*r+i]); }
+    if(i<18){ int r=i-6; return (j<18)? q.cmask[r/3]*q.Jc[18*r+j] : T(0.0); }
+    if(i<34){ int r=i-18,l=r>>2,k=r&3,c=j-18-3*l; if(c<0||c>2) return T(0.0);
+              T d = (c==2)? -q.mu : ((c==(k>>1))? ((k&1)?T(-1.0):T(1.0)) : T(0.0)); return d*q.cmask[l]; }
+    if(i<46){ int r=i-34; if(j<6||j>=30) return T(0.0); if(j<18) return q.Mjj[12*r+j-6]; int f=j-18; return -(q.cmask[f/3]*q.Jc[18*f+6+r]); }
+    { int r=(i<58)?i-46:i-58; if(j<18) return (T(1.0)-q.cmask[r/3])*q.Jc[18*r+j]; if(j==30+r) return (i<58)?T(-1.0):T(1.0); return T(0.0); }
 }
-WBC_HD double Hel(const QPData& q,int i,int j){
+template<class QD> WBC_HD typename QD::value_type Hel(const QD& q,int i,int j){
+    typedef typename QD::value_type T;
     if(i>=18&&i<30&&j>=18&&j<30) return q.Hff[12*(i-18)+(j-18)];
-    if(i!=j) return 0.0; return (i>=30)?q.rho:1.0;
+    if(i!=j) return T(0.0); return (i>=30)?q.rho:T(1.0);
 }
-WBC_FN double Ael_dev(const QPData& q,int i,int j){ return Ael(q,i,j); }       // ONE device copy of the element decoder
+template<class QD> WBC_FN real Ael_dev(const QD& q,int i,int j){ return (real)Ael(q,i,j); }       // ONE device copy of the element decoder
 // Structured products with A (whole_body_controller.cpp:492-497): no per-element decoding, only the non-zero blocks.
 // All of them ACCUMULATE ONTO THE GIVEN VALUE term by term, y <- y + sgn*a_ij*v_j in ascending j, which is what the reference's dense
 // loops do (DenseMatrix::times / transTimes with index lists, Matrices.cpp:332-590, and the DGEMM replacement, BLASReplacement.cpp:36-92:
 // `y[.] += val*x` / `y[.] -= val*x` onto the existing y; zero entries of the dense row add exactly 0).  sgn is +1.0 or -1.0 exactly,
 // so (sgn*a)*v == +-(a*v) bit for bit.
 // Arow_acc: y + sgn*(A v)_i for a 42-vector v (callers mask v to the free / fixed columns beforehand: the reference visits the selected columns only).
-WBC_FN double Arow_acc(const QPData& q,int i,const double* v,double y,double sgn){
+WBC_FN real Arow_acc(const QPDataR& q,int i,const real* v,real y,real sgn){
     if(i<6){ for(int j=0;j<6;j++) y+=(sgn*q.Mbb[6*i+j])*v[j]; for(int f=0;f<12;f++) y-=(sgn*(q.cmask[f/3]*q.Jc[18*f+i]))*v[18+f]; return y; }
-    if(i<18){ const int r=i-6; const double c=q.cmask[r/3]; if(c==0.0) return y; for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return y; }
-    if(i<34){ const int r=i-18,l=r>>2,k=r&3; const double c=q.cmask[l]; if(c==0.0) return y; const double* f=v+18+3*l;
-              const double d=(k&1)?-sgn:sgn;
+    if(i<18){ const int r=i-6; const real c=q.cmask[r/3]; if(c==real(0.0)) return y; for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return y; }
+    if(i<34){ const int r=i-18,l=r>>2,k=r&3; const real c=q.cmask[l]; if(c==real(0.0)) return y; const real* f=v+18+3*l;
+              const real d=(k&1)?-sgn:sgn;
               if(k<2){ y+=d*f[0]; } else { y+=d*f[1]; }
               return y-(sgn*q.mu)*f[2]; }
     if(i<46){ const int r=i-34; for(int j=0;j<12;j++) y+=(sgn*q.Mjj[12*r+j])*v[6+j]; for(int f=0;f<12;f++) y-=(sgn*(q.cmask[f/3]*q.Jc[18*f+6+r]))*v[18+f]; return y; }
-    { const int r=(i<58)?i-46:i-58; const double c=1.0-q.cmask[r/3]; if(c!=0.0) for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return (i<58)? y-sgn*v[30+r] : y+sgn*v[30+r]; }
+    { const int r=(i<58)?i-46:i-58; const real c=real(1.0)-q.cmask[r/3]; if(c!=real(0.0)) for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return (i<58)? y-sgn*v[30+r] : y+sgn*v[30+r]; }
 }
 // Acol_acc: y + sgn*(A' yv)_j for a 70-vector yv by constraint number (0 for inactive constraints), rows visited in ascending order
-WBC_FN double Acol_acc(const QPData& q,int j,const double* yv,double y,double sgn){
+WBC_FN real Acol_acc(const QPDataR& q,int j,const real* yv,real y,real sgn){
     if(j<18){
         if(j<6) for(int i=0;i<6;i++) y+=(sgn*q.Mbb[6*i+j])*yv[i];
         for(int r=0;r<12;r++) y+=(sgn*(q.cmask[r/3]*q.Jc[18*r+j]))*yv[6+r];
         if(j>=6) for(int r=0;r<12;r++) y+=(sgn*q.Mjj[12*r+(j-6)])*yv[34+r];
-        for(int r=0;r<12;r++) y+=(sgn*((1.0-q.cmask[r/3])*q.Jc[18*r+j]))*yv[46+r];
-        for(int r=0;r<12;r++) y+=(sgn*((1.0-q.cmask[r/3])*q.Jc[18*r+j]))*yv[58+r];
+        for(int r=0;r<12;r++) y+=(sgn*((real(1.0)-q.cmask[r/3])*q.Jc[18*r+j]))*yv[46+r];
+        for(int r=0;r<12;r++) y+=(sgn*((real(1.0)-q.cmask[r/3])*q.Jc[18*r+j]))*yv[58+r];
         return y;
     }
-    if(j<30){ const int f=j-18,l=f/3,c=f-3*l; const double cf=q.cmask[l];
+    if(j<30){ const int f=j-18,l=f/3,c=f-3*l; const real cf=q.cmask[l];
         for(int i=0;i<6;i++) y-=(sgn*(cf*q.Jc[18*f+i]))*yv[i];
-        const double* yf=yv+18+4*l;
-        if(c==2){ const double m=sgn*(cf*q.mu); y-=m*yf[0]; y-=m*yf[1]; y-=m*yf[2]; y-=m*yf[3]; }
-        else { const double d=sgn*cf; y+=d*yf[2*c]; y-=d*yf[2*c+1]; }
+        const real* yf=yv+18+4*l;
+        if(c==2){ const real m=sgn*(cf*q.mu); y-=m*yf[0]; y-=m*yf[1]; y-=m*yf[2]; y-=m*yf[3]; }
+        else { const real d=sgn*cf; y+=d*yf[2*c]; y-=d*yf[2*c+1]; }
         for(int r=0;r<12;r++) y-=(sgn*(cf*q.Jc[18*f+6+r]))*yv[34+r];
         return y; }
     y-=sgn*yv[46+(j-30)];
@@ -254,41 +269,41 @@ WBC_DEV unsigned force_mask(const QPWork& w,const QPCtx& c,int sel){
     return wbc_ballot(c.lane<12&&(sel==2||((w.bstat[18+(c.lane<12?c.lane:0)]!=0)==(sel==1))));
 #endif
 }
-WBC_FN double Hrow_acc(const QPWork& w,int i,const double* v,int sel,unsigned fm,double y,double sgn){
-    if(i>=18&&i<30){ const double* h=&WQP.Hff[i-18];
+WBC_FN real Hrow_acc(const QPWork& w,int i,const real* v,int sel,unsigned fm,real y,real sgn){
+    if(i>=18&&i<30){ const real* h=&WQP.Hff[i-18];
         #pragma unroll
         for(int u=0;u<12;u++) if((fm>>u)&1u) y+=(sgn*h[12*u])*v[18+u];
         return y; }
     if(sel!=2 && ((w.bstat[i]!=0)!=(sel==1))) return y;
-    return y+(sgn*((i>=30)?WQP.rho:1.0))*v[i];
+    return y+(sgn*((i>=30)?WQP.rho:real(1.0)))*v[i];
 }
 // masked copies: vm = v restricted to free (sel 0) / fixed (sel 1) variables; ym = yAC scattered to constraint numbers
-WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const double* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:0.0; WBC_SYNC(); }
-WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const double* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:0.0; WBC_SYNC(); }
+WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const real* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:real(0.0); WBC_SYNC(); }
+WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const real* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:real(0.0); WBC_SYNC(); }
 
 // ---------------------------------------------------------------- products with Q = [Z Y] (one copy each: instruction cache)
 // out[i] = sgn * sum_j Q(FR[j], col0+i) t[FR[j]],  i < ncols   (t by variable number; lane per column; FR-list order like the reference).
 // A lane owns columns i and i+32 and walks both in the same loop (two independent chains, t loaded once).  While the free list is
 // the identity (c.frIdentity) the list indirection is skipped -- same terms, same order.
-WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const double* t,double sgn,double* out){
+WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const real* t,real sgn,real* out){
     const int lane=c.lane, nFR=c.nFR;
 #if WBC_NL==1
-    for(int i=0;i<ncols;i++){ const double* q=&w.Q[LD*(col0+i)]; double s=0.0; for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s+=q[jj]*t[jj]; } out[i]=sgn*s; }
+    for(int i=0;i<ncols;i++){ const real* q=&w.Q[LD*(col0+i)]; real s=real(0.0); for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s+=q[jj]*t[jj]; } out[i]=sgn*s; }
 #else
     const bool in0=lane<ncols, in1=lane+32<ncols;
-    const double* q0=&w.Q[LD*(col0+(in0?lane:0))]; const double* q1=&w.Q[LD*(col0+(in1?lane+32:0))];
-    double s0=0.0,s1=0.0;
+    const real* q0=&w.Q[LD*(col0+(in0?lane:0))]; const real* q1=&w.Q[LD*(col0+(in1?lane+32:0))];
+    real s0=real(0.0),s1=real(0.0);
     if(c.frIdentity){
         if(ncols>32){
             #pragma unroll 6
-            for(int j=0;j<42;j++){ const double tj=t[j]; s0+=q0[j]*tj; s1+=q1[j]*tj; }
+            for(int j=0;j<42;j++){ const real tj=t[j]; s0+=q0[j]*tj; s1+=q1[j]*tj; }
         } else {
             #pragma unroll 6
             for(int j=0;j<42;j++) s0+=q0[j]*t[j];
         }
     } else if(ncols>32){
         #pragma unroll 4
-        for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; const double tj=t[jj]; s0+=q0[jj]*tj; s1+=q1[jj]*tj; }
+        for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; const real tj=t[jj]; s0+=q0[jj]*tj; s1+=q1[jj]*tj; }
     } else {
         #pragma unroll 4
         for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s0+=q0[jj]*t[jj]; }
@@ -300,18 +315,18 @@ WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const dou
 }
 // v = sum_j Q(FR[i], col0+j) x[j] for every free variable FR[i]:  acc[FR[i]] += v,  and keep[FR[i]] = v if keep != null   (lane per row,
 // rows i and i+32 of the list in one loop)
-WBC_FN void Q_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const double* x,double* acc,double* keep){
+WBC_FN void Q_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const real* x,real* acc,real* keep){
     const int lane=c.lane, nFR=c.nFR;
 #if WBC_NL==1
-    for(int i=0;i<nFR;i++){ const int ii=(int)w.FR[i]; const double* q=&w.Q[ii+LD*col0]; double s=0.0; for(int j=0;j<ncols;j++) s+=q[LD*j]*x[j]; if(keep) keep[ii]=s; acc[ii]+=s; }
+    for(int i=0;i<nFR;i++){ const int ii=(int)w.FR[i]; const real* q=&w.Q[ii+LD*col0]; real s=real(0.0); for(int j=0;j<ncols;j++) s+=q[LD*j]*x[j]; if(keep) keep[ii]=s; acc[ii]+=s; }
 #else
     const bool in0=lane<nFR, in1=lane+32<nFR;
     const int i0=in0?(int)w.FR[lane]:0, i1=in1?(int)w.FR[lane+32]:0;
-    const double* q0=&w.Q[i0+LD*col0]; const double* q1=&w.Q[i1+LD*col0];
-    double s0=0.0,s1=0.0;
+    const real* q0=&w.Q[i0+LD*col0]; const real* q1=&w.Q[i1+LD*col0];
+    real s0=real(0.0),s1=real(0.0);
     if(nFR>32){
         #pragma unroll 4
-        for(int j=0;j<ncols;j++){ const double xj=x[j]; s0+=q0[LD*j]*xj; s1+=q1[LD*j]*xj; }
+        for(int j=0;j<ncols;j++){ const real xj=x[j]; s0+=q0[LD*j]*xj; s1+=q1[LD*j]*xj; }
     } else {
         #pragma unroll 4
         for(int j=0;j<ncols;j++) s0+=q0[LD*j]*x[j];
@@ -363,11 +378,11 @@ WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ c.frIdentity=0; WBC_SYN
 WBC_DEV int trisolve_row0(int kind,int n,int i){      // packed index of L(i,0)
     return kind==0? tri(i) : kind==1? tri(n-1)+n-1-i : kind==2? TRI42-1-tri(i) : TRI42-1-(tri(n-1)+n-1-i);
 }
-WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,int bs,double* a,int as,const double* rd,int rs){
+WBC_FN void trisolve(int lane,int kind,int n,const real* RT,const real* b,int bs,real* a,int as,const real* rd,int rs){
     const int d0= kind==0? 1 : kind==1? -(n-1) : kind==2? -1 : n-1, dd= kind==1? 1 : kind==3? -1 : 0;
 #if WBC_NL==1
-    (void)lane; double u[42];
-    for(int k=0;k<n;k++){ double sum=b[k*bs]; int off=trisolve_row0(kind,n,k), d=d0;
+    (void)lane; real u[42];
+    for(int k=0;k<n;k++){ real sum=b[k*bs]; int off=trisolve_row0(kind,n,k), d=d0;
         for(int j=0;j<k;j++){ sum-=RT[off]*u[j]; off+=d; d+=dd; }
         u[k]=WBC_BYDIAG(sum,rd[k*rs]); }
     for(int k=0;k<n;k++) a[k*as]=u[k];
@@ -375,29 +390,29 @@ WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,in
     const bool in0=lane<n, in1=lane+32<n;
     const unsigned L=wbc_saddr(RT);                           // 32-bit shared address of the packed R/T buffer (read-only here)
     int o0=in0?trisolve_row0(kind,n,lane):0, d=d0;
-    double s0=in0?b[lane*bs]:0.0, r0=in0?rd[lane*rs]:1.0, l0=(in0&&lane>0)?wbc_lds(L+8u*o0):0.0;
+    real s0=in0?b[lane*bs]:real(0.0), r0=in0?rd[lane*rs]:real(1.0), l0=(in0&&lane>0)?wbc_lds(L+(unsigned)sizeof(real)*o0):real(0.0);
     WBC_SYNC();                                              // a may alias b
     // l0 is loaded as 0 for lanes <= k, so the update needs no predicate and a finished lane keeps its final sum: u_k = s0*r0 is
     // formed for the broadcast at step k and once more, from the same operands, for the store after the loop.
     if(n<=32){
         #pragma unroll 2
         for(int k=0;k<n;k++){
-            const double ak=__shfl_sync(0xffffffffu,WBC_BYDIAG(s0,r0),k);
+            const real ak=__shfl_sync(0xffffffffu,WBC_BYDIAG(s0,r0),k);
             o0+=d; d+=dd;
-            const double nl=(lane>k+1&&in0)?wbc_lds(L+8u*o0):0.0;   // next column's entry, independent of the chain
+            const real nl=(lane>k+1&&in0)?wbc_lds(L+(unsigned)sizeof(real)*o0):real(0.0);   // next column's entry, independent of the chain
             s0=WBC_FNMA(l0,ak,s0);
             l0=nl;
         }
         if(in0) a[lane*as]=WBC_BYDIAG(s0,r0);
     } else {
         int o1=in1?trisolve_row0(kind,n,lane+32):0;
-        double s1=in1?b[(lane+32)*bs]:0.0, r1=in1?rd[(lane+32)*rs]:1.0, l1=in1?wbc_lds(L+8u*o1):0.0;
+        real s1=in1?b[(lane+32)*bs]:real(0.0), r1=in1?rd[(lane+32)*rs]:real(1.0), l1=in1?wbc_lds(L+(unsigned)sizeof(real)*o1):real(0.0);
         #pragma unroll 2
         for(int k=0;k<n;k++){
-            const double mine=(k<32)?WBC_BYDIAG(s0,r0):WBC_BYDIAG(s1,r1);
-            const double ak=__shfl_sync(0xffffffffu,mine,k&31);
+            const real mine=(k<32)?WBC_BYDIAG(s0,r0):WBC_BYDIAG(s1,r1);
+            const real ak=__shfl_sync(0xffffffffu,mine,k&31);
             o0+=d; o1+=d; d+=dd;
-            const double nl0=(lane>k+1&&in0)?wbc_lds(L+8u*o0):0.0, nl1=(lane+32>k+1&&in1)?wbc_lds(L+8u*o1):0.0;
+            const real nl0=(lane>k+1&&in0)?wbc_lds(L+(unsigned)sizeof(real)*o0):real(0.0), nl1=(lane+32>k+1&&in1)?wbc_lds(L+(unsigned)sizeof(real)*o1):real(0.0);
             s0=WBC_FNMA(l0,ak,s0); s1=WBC_FNMA(l1,ak,s1);
             l0=nl0; l1=nl1;
         }
@@ -410,20 +425,20 @@ WBC_FN void trisolve(int lane,int kind,int n,const double* RT,const double* b,in
 // reciprocals of T's diagonal TT(k, sizeT-1-k); false if a pivot fails the |.| > EPS test of QProblem::backsolveT
 WBC_FN bool prepare_T(QPWork& w,const QPCtx& c){
     const int lane=c.lane; bool bad=false; WBC_SYNC();
-    LANE_FOR(k,c.nAC){ const double d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=WBC_RDIAG(d); }
+    LANE_FOR(k,c.nAC){ const real d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=WBC_RDIAG(d); }
     WBC_SYNC();
     return wbc_ballot(bad)==0u;
 }
 // QProblem::backsolveT (QProblem.cpp:4518-4565).  b, a indexed by AC position.  prepare_T must have run since T last changed.
 // unknown u_k = a[nT-1-k]; row i, column j<i:  TT(i,sizeT-1-j)  resp.  TT(nT-1-j,tcol+i) for the transposed system
-WBC_DEV void backsolveT(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a){
+WBC_DEV void backsolveT(QPWork& w,const QPCtx& c,const real* b,bool transposed,real* a){
     const int nT=c.nAC;
     if(nT<=0) return;
     if(!transposed) trisolve(c.lane,0,nT,w.RT,b,1,a+nT-1,-1,w.rdT,1);
     else            trisolve(c.lane,1,nT,w.RT,b,1,a+nT-1,-1,w.rdT+nT-1,-1);
 }
 // QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b.  w.rdR = 1/diag(R).
-WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed,double* a,int nR){
+WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const real* b,bool transposed,real* a,int nR){
     if(nR<=0) return;
     if(transposed){ trisolve(c.lane,2,nR,w.RT,b,1,a,1,w.rdR,1); return; }
 #if defined(WBC_EXACT_BACKSUB)
@@ -431,7 +446,7 @@ WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed
     // it has only just computed: a serial chain of nR^2/2 operations that the streaming form below (terms in the order the unknowns become
     // available: j = nR-1 down to i+1) re-orders.  Exact build: the serial form, every lane redundantly, lane 0 stores.
     { const int lane=c.lane; WBC_SYNC();
-      for(int i=nR-1;i>=0;--i){ double sum=b[i]; for(int j=i+1;j<nR;++j) sum-=RR(i,j)*a[j]; const double v=WBC_BYDIAG(sum,w.rdR[i]); WBC_SYNC(); if(lane==0) a[i]=v; WBC_SYNC(); } }
+      for(int i=nR-1;i>=0;--i){ real sum=b[i]; for(int j=i+1;j<nR;++j) sum-=RR(i,j)*a[j]; const real v=WBC_BYDIAG(sum,w.rdR[i]); WBC_SYNC(); if(lane==0) a[i]=v; WBC_SYNC(); } }
 #else
     trisolve(c.lane,3,nR,w.RT,b+nR-1,-1,a+nR-1,-1,w.rdR+nR-1,-1);
 #endif
@@ -441,9 +456,9 @@ WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const double* b,bool transposed
 // QProblem::setupTQfactorisation (QProblem.cpp:2169-2193)
 WBC_DEV void setupTQfactorisation(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(e,42*LD) w.Q[e]=0.0;                     // packed T needs no clearing: every entry of a row is written when the row is created
+    LANE_FOR(e,42*LD) w.Q[e]=real(0.0);                     // packed T needs no clearing: every entry of a row is written when the row is created
     WBC_SYNC();
-    LANE_FOR(i,c.nFR) QQ((int)w.FR[i],i)=1.0;
+    LANE_FOR(i,c.nFR) QQ((int)w.FR[i],i)=real(1.0);
     WBC_SYNC();
 }
 // DPOTRF "U" of LAPACKReplacement.cpp:39-77 on the leading n x n block of R.  Row i: the lane that owns column j forms R(i,j); its
@@ -454,31 +469,31 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
     WBC_SYNC();
 #if WBC_NL==1
     for(int i=0;i<n;i++){
-        double sum=RR(i,i); for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);
-        if(!(sum>0.0)) return false;
-        const double d=sqrt(sum), rd=WBC_RDIAG(d); RR(i,i)=d; w.rdR[i]=rd;
-        for(int j=i+1;j<n;j++){ double s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=WBC_BYDIAG(s2,rd); }
+        real sum=RR(i,i); for(int k=i-1;k>=0;k--) sum-=RR(k,i)*RR(k,i);
+        if(!(sum>real(0.0))) return false;
+        const real d=sqrt(sum), rd=WBC_RDIAG(d); RR(i,i)=d; w.rdR[i]=rd;
+        for(int j=i+1;j<n;j++){ real s2=RR(i,j); for(int k=i-1;k>=0;k--) s2-=RR(k,i)*RR(k,j); RR(i,j)=WBC_BYDIAG(s2,rd); }
     }
 #else
     // lane t owns columns t and t+32 for the whole factorisation (fixed pointers, no per-row index arithmetic); packed column j lives
     // at RT[TRI42-1-tri(j) - row].  At row i the lanes left of the diagonal run the same loop on in-bounds data and discard the result.
     const bool own0=lane<n, own1=lane+32<n;
-    double* c0=&w.RT[TRI42-1-tri(own0?lane:0)];                // &RR(0,lane)
-    double* c1=&w.RT[TRI42-1-tri(own1?lane+32:0)];
-    const double* ci=&w.RT[TRI42-1];                           // &RR(0,i)
+    real* c0=&w.RT[TRI42-1-tri(own0?lane:0)];                // &RR(0,lane)
+    real* c1=&w.RT[TRI42-1-tri(own1?lane+32:0)];
+    const real* ci=&w.RT[TRI42-1];                           // &RR(0,i)
     for(int i=0;i<n;i++){
-        double s0=c0[-i], s1=0.0;
+        real s0=c0[-i], s1=real(0.0);
         if(n>32){
             s1=c1[-i];
             #pragma unroll 2
-            for(int r=i-1;r>=0;r--){ const double rki=ci[-r]; s0-=rki*c0[-r]; s1-=rki*c1[-r]; }
+            for(int r=i-1;r>=0;r--){ const real rki=ci[-r]; s0-=rki*c0[-r]; s1-=rki*c1[-r]; }
         } else {
             #pragma unroll 2
             for(int r=i-1;r>=0;r--) s0-=ci[-r]*c0[-r];
         }
-        const double sum=wbc_bcast((i<32)?s0:s1,i&31);
-        if(!(sum>0.0)) return false;
-        const double d=sqrt(sum), rd=WBC_RDIAG(d);
+        const real sum=wbc_bcast((i<32)?s0:s1,i&31);
+        if(!(sum>real(0.0))) return false;
+        const real d=sqrt(sum), rd=WBC_RDIAG(d);
         if(lane==(i&31)){ if(i<32) c0[-i]=d; else c1[-i]=d; w.rdR[i]=rd; }
         if(own0&&lane>i) c0[-i]=WBC_BYDIAG(s0,rd);
         if(own1&&lane+32>i) c1[-i]=WBC_BYDIAG(s1,rd);
@@ -496,20 +511,20 @@ WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
     const int lane=c.lane, nt=(nZ+TS-1)/TS, ntiles=nt*(nt+1)/2;
     LANE_FOR(t,ntiles){
         int ti=0, rem=t; while(rem>=nt-ti){ rem-=nt-ti; ti++; } const int tj=ti+rem;
-        double acc[TS][TS];
+        real acc[TS][TS];
         #pragma unroll
         for(int a=0;a<TS;a++){
             #pragma unroll
-            for(int b=0;b<TS;b++) acc[a][b]=0.0; }
+            for(int b=0;b<TS;b++) acc[a][b]=real(0.0); }
         #pragma unroll 1
         for(int ii=0;ii<nFR;ii++){
-            const int v=(int)w.FR[ii]; double zj[TS],wk[TS];
+            const int v=(int)w.FR[ii]; real zj[TS],wk[TS];
             #pragma unroll
             for(int b=0;b<TS;b++) zj[b]=QQ(v,TS*tj+b);
             if(v>=18&&v<30){
                 #pragma unroll
                 for(int a=0;a<TS;a++) wk[a]=w.HZf[(v-18)*LD+TS*ti+a];
-            } else { const double dv=(v>=30)?WQP.rho:1.0;
+            } else { const real dv=(v>=30)?WQP.rho:real(1.0);
                 #pragma unroll
                 for(int a=0;a<TS;a++) wk[a]=dv*QQ(v,TS*ti+a); }
             #pragma unroll
@@ -536,9 +551,9 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
     if(nZ==0&&c.nFX+c.nAC!=0) return QP_OK;
     if(c.nAC==0){
         if(c.nFX!=0){ // make Z trivial
-            LANE_FOR(i,42) for(int j=0;j<nZ;j++) QQ(i,j)=0.0;
+            LANE_FOR(i,42) for(int j=0;j<nZ;j++) QQ(i,j)=real(0.0);
             WBC_SYNC();
-            LANE_FOR(j,nZ) QQ((int)w.FR[j],j)=1.0;
+            LANE_FOR(j,nZ) QQ((int)w.FR[j],j)=real(1.0);
         }
         fill_R_with_H(w,c);
     } else {
@@ -549,7 +564,7 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
         for(int base=0;base<nFR;base+=WBC_NL){ const int i=base+lane; const int v=(i<nFR)?(int)w.FR[i]:0; const bool isf=(i<nFR)&&v>=18&&v<30;
             const unsigned m=wbc_ballot(isf); if(isf) ffl[nff+wbc_rank(m,lane)]=v-18; nff+=wbc_popc(m); }
         WBC_SYNC();
-        LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; double s=0;
+        LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; real s=0;
             for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
             w.HZf[a*LD+k]=s; }
         WBC_SYNC();
@@ -575,27 +590,27 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
     for(int base=0;base<nFR;base+=WBC_NL){ const int i=base+lane; const int v=(i<nFR)?(int)w.FR[i]:0; const bool isf=(i<nFR)&&v>=18&&v<30;
         const unsigned m=wbc_ballot(isf); if(isf) ffl[nff+wbc_rank(m,lane)]=v-18; nff+=wbc_popc(m); }
     WBC_SYNC();
-    LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; double s=0;
+    LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; real s=0;
         for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
         w.HZf[a*LD+k]=s; }
     WBC_SYNC();
-    double* col=w.ym;                                           // behind the 12 x LD block of (HZ)_force inside the scratch union
-    LANE_FOR(i,nZ){ double s=0.0;
-        for(int ii=0;ii<nFR;ii++){ const int v=(int)w.FR[ii]; const double z=QQ(v,n);
-            const double hk=(v>=18&&v<30)? w.HZf[(v-18)*LD+i] : ((v>=30)?WQP.rho:1.0)*QQ(v,i);
+    real* col=w.ym;                                           // behind the 12 x LD block of (HZ)_force inside the scratch union
+    LANE_FOR(i,nZ){ real s=real(0.0);
+        for(int ii=0;ii<nFR;ii++){ const int v=(int)w.FR[ii]; const real z=QQ(v,n);
+            const real hk=(v>=18&&v<30)? w.HZf[(v-18)*LD+i] : ((v>=30)?WQP.rho:real(1.0))*QQ(v,i);
             s+=z*hk; }
         col[i]=s; }
     WBC_SYNC();
-    const double* rn=&RR(0,n);                                  // packed column n: RR(k,n) = rn[-k]
+    const real* rn=&RR(0,n);                                  // packed column n: RR(k,n) = rn[-k]
     for(int i=0;i<n;i++){
-        double s=col[i]; const double* ri=&RR(0,i);
+        real s=col[i]; const real* ri=&RR(0,i);
         for(int k=i-1;k>=0;k--) s-=ri[-k]*rn[-k];
         RR(i,n)=WBC_BYDIAG(s,w.rdR[i]);
     }
-    double sum=col[n];
+    real sum=col[n];
     for(int k=n-1;k>=0;k--) sum-=rn[-k]*rn[-k];
-    if(!(sum>0.0)) return QP_RET_HESSIAN_NOT_SPD;
-    const double d=sqrt(sum);
+    if(!(sum>real(0.0))) return QP_RET_HESSIAN_NOT_SPD;
+    const real d=sqrt(sum);
     RR(n,n)=d; w.rdR[n]=WBC_RDIAG(d);
     WBC_SYNC();
     return QP_OK;
@@ -605,36 +620,36 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
 // QProblem::determineStepDirection (QProblem.cpp:4637-4975), HST_POSDEF branch.
 // delta_* point to 42- / 70-long vectors by variable / constraint number.  Results: w.dx (free and fixed parts, by
 // variable number), w.dyAC (by AC position), w.dyFX (by variable number).
-WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const double* dlbA,const double* dubA,const double* dlb,const double* dub,
+WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,const real* dlbA,const real* dubA,const real* dlb,const real* dub,
                                   bool bCzero,bool bBzero){
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
     if(!prepare_T(w,c)) return QP_RET_STEPDIRECTION_FAILED_TQ;
     const unsigned ffm=force_mask(w,c,0), fxm=force_mask(w,c,1);
     // I) delta_xFX
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= (bBzero||!dlb)?0.0:((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=0.0; }
-    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=0.0; w.tB[i]= (bCzero||!dlbA)?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= (bBzero||!dlb)?real(0.0):((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=real(0.0); }
+    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=real(0.0); w.tB[i]= (bCzero||!dlbA)?real(0.0):((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
     WBC_SYNC();
     int nref=0;
     for(int r=0;r<=OPT_numRefinementSteps;r++){
         if(nFR>0){
-            LANE_FOR(i,nFR) w.xTMP[(int)w.FR[i]]=0.0;
+            LANE_FOR(i,nFR) w.xTMP[(int)w.FR[i]]=real(0.0);
             WBC_SYNC();
             if(nAC>0){
-                if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=0.0; WBC_SYNC(); }
+                if(bCzero&&bBzero){ LANE_FOR(i,nAC) w.xFRy[i]=real(0.0); WBC_SYNC(); }
                 else {
-                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-1.0); WBC_SYNC(); }
+                    if(!bBzero&&r==0){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-real(1.0)); WBC_SYNC(); }
                     backsolveT(w,c,w.tB,false,w.xFRy);
                     Q_times(w,c,nZ,nAC,w.xFRy,w.xTMP,nullptr);
                 }
             }
-            LANE_FOR(i,nZ) w.xFRz[i]=0.0;
+            LANE_FOR(i,nZ) w.xFRz[i]=real(0.0);
             // HMX*delta_xFX and HFR*delta_xFRy into tempA
-            if(!bBzero&&r==0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.dx,1,fxm,w.tA[ii],1.0); } WBC_SYNC(); }
-            if(nAC>0&&(!bCzero||!bBzero)){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.xTMP,0,ffm,w.tA[ii],1.0); } }
+            if(!bBzero&&r==0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.dx,1,fxm,w.tA[ii],real(1.0)); } WBC_SYNC(); }
+            if(nAC>0&&(!bCzero||!bBzero)){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.xTMP,0,ffm,w.tA[ii],real(1.0)); } }
             WBC_SYNC();
             if(nZ>0){
-                Qt_times(w,c,0,nZ,w.tA,-1.0,w.xFRz);
+                Qt_times(w,c,0,nZ,w.tA,-real(1.0),w.xFRz);
                 backsolveR(w,c,w.xFRz,true,w.xFRz,nZ);
                 backsolveR(w,c,w.xFRz,false,w.xFRz,nZ);
                 Q_times(w,c,0,nZ,w.xFRz,w.xTMP,w.Zdz);
@@ -642,8 +657,8 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         }
         // III) delta_yAC
         if(nAC>0){
-            if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.Zdz,0,ffm,w.tA[ii],1.0); } WBC_SYNC(); }
-            Qt_times(w,c,nZ,nAC,w.tA,1.0,w.tB);
+            if(nZ>0){ LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=Hrow_acc(w,ii,w.Zdz,0,ffm,w.tA[ii],real(1.0)); } WBC_SYNC(); }
+            Qt_times(w,c,nZ,nAC,w.tA,real(1.0),w.tB);
             backsolveT(w,c,w.tB,true,w.yTMP);
         }
         WBC_SYNC();
@@ -653,14 +668,14 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
         nref=r;
         if(r==OPT_numRefinementSteps) break;                 // the reference computes one more residual here and never reads it
         // residuals for the next refinement pass
-        double rnrm=0.0;
+        real rnrm=real(0.0);
         scatter_yAC(w,c,w.dyAC);
-        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double t=dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,1.0); t=Hrow_acc(w,ii,w.dx,1,fxm,t,1.0); t=Acol_acc(WQP,ii,w.ym,t,-1.0); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; real t=dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
         // bA - A_FR dx_FR - A_FX dx_FX: the free columns first, then the fixed ones, each accumulated onto tempB (QProblem.cpp:4934-4935)
         mask_vars(w,c,w.dx,0);
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double t= (bCzero||!dlbA)?0.0:((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
-            w.tB[i]=Arow_acc(WQP,ii,w.vm,t,-1.0); }
-        if(!bBzero&&dlb){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-1.0); }
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real t= (bCzero||!dlbA)?real(0.0):((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
+            w.tB[i]=Arow_acc(WQP,ii,w.vm,t,-real(1.0)); }
+        if(!bBzero&&dlb){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-real(1.0)); }
         LANE_FOR(i,nAC) rnrm=fmax(rnrm,fabs(w.tB[i]));
         rnrm=wbc_max(rnrm);
 #if !defined(__CUDACC__) && defined(WBC_QP_DBG)
@@ -674,7 +689,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
     WBC_FLOPS((1.0+nref)*(2.0*nAC*nAC+4.0*nFR*nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+nref*(2.0*nFR*nFR+4.0*nAC*42.0)); (void)nref;
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; double t=dg[ii]; t=Acol_acc(WQP,ii,w.ym,t,-1.0); t=Hrow_acc(w,ii,w.dx,0,ffm,t,1.0); t=Hrow_acc(w,ii,w.dx,1,fxm,t,1.0); w.dyFX[ii]=t; }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; real t=dg[ii]; t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); w.dyFX[ii]=t; }
     WBC_SYNC();
     WBC_DBG_VEC("dxFR",w.dx[(int)w.FR[i]],nFR); WBC_DBG_VEC("dyAC",w.dyAC[i],nAC); WBC_DBG_VEC("dyFX",w.dyFX[(int)w.FX[i]],nFX); WBC_DBG_VEC("dxFX",w.dx[(int)w.FX[i]],nFX);
     return QP_OK;
@@ -685,8 +700,8 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const double* dg,const doub
 // list sequentially, replacing the candidate whenever num_i < t*den_i with the CURRENT t.  Exactly the same chain of
 // winners is produced here: a ballot finds the first later entry that beats the current t, t is updated, repeat.
 // stat == 0: plain test (performPlainRatioTest, QProblem.cpp:4256-4275: num > epsNum, den > epsDen, t*den > num).
-WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const double* num,const double* den,
-                              double& t,int& BC_idx){
+WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const real* num,const real* den,
+                              real& t,int& BC_idx){
     const int lane=c.lane; BC_idx=-1; int pos=0;
     WBC_SYNC();
     for(;;){
@@ -694,7 +709,7 @@ WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const s
         for(int base=(pos/WBC_NL)*WBC_NL; base<n; base+=WBC_NL){
             int i=base+lane; bool f=false;
             if(i>=pos&&i<n){
-                double nu=num[i], de=den[i];
+                real nu=num[i], de=den[i];
                 if(stat){ if(stat[(int)idx[i]]==ST_UPPER){ nu=-nu; de=-de; }
                           f=(de>=OPT_epsDen)&&(nu>=OPT_epsNum)&&(nu<t*de); }
                 else f=(nu>OPT_epsNum)&&(de>OPT_epsDen)&&(t*de>nu);
@@ -711,17 +726,17 @@ WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const s
 // Targets of the current homotopy = the user's data with every infinite side replaced by a far bound (QProblem::updateFarBounds,
 // QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246: +-farbound*(1+ramp(i)), ramp offset as of the call).  There are no user bounds on
 // x; the targets are functions of (index, farbound, offset) and are evaluated where needed instead of being stored.
-WBC_DEV double far_rv(const QPCtx& c,int idx){ const int nRamp=42+70; const double t=(double)((idx+c.farRampOffset)%nRamp)/(double)(nRamp-1);
-    return c.farbound*(1.0+(1.0-t)*OPT_ramp0+t*OPT_ramp1); }
-WBC_DEV double tgt_lb(const QPCtx& c,int i){ return -far_rv(c,i); }
-WBC_DEV double tgt_ub(const QPCtx& c,int i){ return far_rv(c,i); }
-WBC_DEV double tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),WQP.lbA[i]); }
-WBC_DEV double tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),WQP.ubA[i]); }
+WBC_DEV real far_rv(const QPCtx& c,int idx){ const int nRamp=42+70; const real t=(real)((idx+c.farRampOffset)%nRamp)/(real)(nRamp-1);
+    return c.farbound*(real(1.0)+(real(1.0)-t)*OPT_ramp0+t*OPT_ramp1); }
+WBC_DEV real tgt_lb(const QPCtx& c,int i){ return -far_rv(c,i); }
+WBC_DEV real tgt_ub(const QPCtx& c,int i){ return far_rv(c,i); }
+WBC_DEV real tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),WQP.lbA[i]); }
+WBC_DEV real tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),WQP.ubA[i]); }
 // QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are WQP.gf (g_new) and the far-bounded data
 WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ double gn=(i>=18&&i<30)?WQP.gf[i-18]:0.0; w.dg[i]=gn-w.g[i]; const double rv=far_rv(c,i); w.dlb[i]=-rv-w.lb[i]; w.dub[i]=rv-w.ub[i]; }
-    LANE_FOR(i,70){ const double rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,WQP.lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,WQP.ubA[i])-w.ubA[i]; }
+    LANE_FOR(i,42){ real gn=(i>=18&&i<30)?WQP.gf[i-18]:real(0.0); w.dg[i]=gn-w.g[i]; const real rv=far_rv(c,i); w.dlb[i]=-rv-w.lb[i]; w.dub[i]=rv-w.ub[i]; }
+    LANE_FOR(i,70){ const real rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,WQP.lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,WQP.ubA[i])-w.ubA[i]; }
     WBC_SYNC();
     bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(w.dlb[ii])>QEPS||fabs(w.dub[ii])>QEPS) nz=true; }
     bBzero=(wbc_ballot(nz)==0u);
@@ -731,23 +746,23 @@ WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzer
 // QProblem::getRelativeHomotopyLength (QProblem.cpp:5372-5410, QProblemB.cpp:2113-2157) is only ever compared with the termination
 // tolerance: max_i |d_i|/s_i <= tol  <=>  no |d_i| > tol*s_i -- evaluated in that form (no fp64 divisions), s_i = max(|target_i|,1).
 WBC_FN bool homotopyFinished(const QPWork& w,const QPCtx& c){
-    const int lane=c.lane; const double tol=OPT_terminationTolerance; bool over=false;
-    LANE_FOR(i,42){ const double gn=(i>=18&&i<30)?WQP.gf[i-18]:0.0; if(fabs(gn-w.g[i])>tol*fmax(fabs(gn),1.0)) over=true;
-                    const double rv=far_rv(c,i), s=tol*fmax(rv,1.0); if(fabs(-rv-w.lb[i])>s||fabs(rv-w.ub[i])>s) over=true; }
-    LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(fabs(l-w.lbA[i])>tol*fmax(fabs(l),1.0)||fabs(u-w.ubA[i])>tol*fmax(fabs(u),1.0)) over=true; }
+    const int lane=c.lane; const real tol=OPT_terminationTolerance; bool over=false;
+    LANE_FOR(i,42){ const real gn=(i>=18&&i<30)?WQP.gf[i-18]:real(0.0); if(fabs(gn-w.g[i])>tol*fmax(fabs(gn),real(1.0))) over=true;
+                    const real rv=far_rv(c,i), s=tol*fmax(rv,real(1.0)); if(fabs(-rv-w.lb[i])>s||fabs(rv-w.ub[i])>s) over=true; }
+    LANE_FOR(i,70){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(fabs(l-w.lbA[i])>tol*fmax(fabs(l),real(1.0))||fabs(u-w.ubA[i])>tol*fmax(fabs(u),real(1.0))) over=true; }
     return wbc_ballot(over)==0u;
 }
 // QProblem::setupAuxiliaryQPgradient (QProblem.cpp:2602-2641): g = y_B - H x + A' y_C
 WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ double t=w.y[i]; t=Hrow_acc(w,i,w.x,2,0xfffu,t,-1.0);
-        w.g[i]=Acol_acc(WQP,i,w.y+42,t,1.0); }
+    LANE_FOR(i,42){ real t=w.y[i]; t=Hrow_acc(w,i,w.x,2,0xfffu,t,-real(1.0));
+        w.g[i]=Acol_acc(WQP,i,w.y+42,t,real(1.0)); }
     WBC_SYNC();
 }
 // QProblem::performStep (QProblem.cpp:4981-5278)
 WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_isBound){
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nIAC=c.nIAC;
-    c.tau=1.0; BC_idx=-1; BC_status=2 /*ST_UNDEFINED*/; BC_isBound=false; int tmp;
+    c.tau=real(1.0); BC_idx=-1; BC_status=2 /*ST_UNDEFINED*/; BC_isBound=false; int tmp;
     WBC_FLOPS(2.0*nIAC*42.0+10.0*(42+70));
     WBC_SYNC();
     // I.1 active constraints' duals
@@ -761,36 +776,36 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
     WBC_SYNC();
     // II.1 inactive constraints
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_acc(WQP,ii,w.dx,0.0,1.0); }
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_acc(WQP,ii,w.dx,real(0.0),real(1.0)); }
     WBC_SYNC();
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],0.0); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],real(0.0)); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=false; }
     WBC_SYNC();
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_u[ii],0.0); w.den[i]=w.dAx[ii]-w.dubA[ii]; }
+    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_u[ii],real(0.0)); w.den[i]=w.dAx[ii]-w.dubA[ii]; }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=false; }
     WBC_SYNC();
     // II.2 free variables
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.x[ii]-w.lb[ii],0.0); w.den[i]=w.dlb[ii]-w.dx[ii]; }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.x[ii]-w.lb[ii],real(0.0)); w.den[i]=w.dlb[ii]-w.dx[ii]; }
     performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=true; }
     WBC_SYNC();
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.ub[ii]-w.x[ii],0.0); w.den[i]=w.dx[ii]-w.dub[ii]; }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.ub[ii]-w.x[ii],real(0.0)); w.den[i]=w.dx[ii]-w.dub[ii]; }
     performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=true; }
     WBC_SYNC();
     // III) step
     if(c.tau>QZERO){
-        const double tau=c.tau;
+        const real tau=c.tau;
         LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.x[ii]+=tau*w.dx[ii]; }
         LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.x[ii]+=tau*w.dx[ii]; w.y[ii]+=tau*w.dyFX[ii]; }
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]+=tau*w.dyAC[i]; }
         LANE_FOR(i,42){ w.g[i]+=tau*w.dg[i]; w.lb[i]+=tau*w.dlb[i]; w.ub[i]+=tau*w.dub[i]; }
         LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
         WBC_SYNC();
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; double ax=Arow_acc(WQP,ii,w.x,0.0,1.0); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
-        LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; double da=w.dAx[ii];
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real ax=Arow_acc(WQP,ii,w.x,real(0.0),real(1.0)); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
+        LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; real da=w.dAx[ii];
             w.Ax[ii]+=tau*da; w.Ax_l[ii]+=tau*(da-w.dlbA[ii]); w.Ax_u[ii]+=tau*(w.dubA[ii]-da); }
         WBC_SYNC();
     }
@@ -799,24 +814,24 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
 WBC_FN void performRamping(QPWork& w,QPCtx& c){
     const int lane=c.lane, nRamp=42+70+70+42; WBC_SYNC();
     LANE_FOR(i,42){
-        double tP=(double)((i+c.rampOffset)%nRamp)/(double)(nRamp-1), rP=(1.0-tP)*OPT_ramp0+tP*OPT_ramp1;
-        double tD=(double)((42+70+70+i+c.rampOffset)%nRamp)/(double)(nRamp-1), rD=(1.0-tD)*OPT_ramp0+tD*OPT_ramp1;
-        int bs=w.bstat[i]; double xi=w.x[i], sca=fmax(fabs(xi),1.0);
+        real tP=(real)((i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
+        real tD=(real)((42+70+70+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rD=(real(1.0)-tD)*OPT_ramp0+tD*OPT_ramp1;
+        int bs=w.bstat[i]; real xi=w.x[i], sca=fmax(fabs(xi),real(1.0));
         if(bs!=ST_LOWER) w.lb[i]=xi-sca*rP;
         if(bs!=ST_UPPER) w.ub[i]=xi+sca*rP;
         if(bs==ST_LOWER){ w.lb[i]=xi; w.y[i]=+rD; }
         if(bs==ST_UPPER){ w.ub[i]=xi; w.y[i]=-rD; }
-        if(bs==ST_INACTIVE) w.y[i]=0.0;
+        if(bs==ST_INACTIVE) w.y[i]=real(0.0);
     }
     LANE_FOR(i,70){
-        double tP=(double)((42+i+c.rampOffset)%nRamp)/(double)(nRamp-1), rP=(1.0-tP)*OPT_ramp0+tP*OPT_ramp1;
-        double tD=(double)((42+70+i+c.rampOffset)%nRamp)/(double)(nRamp-1), rD=(1.0-tD)*OPT_ramp0+tD*OPT_ramp1;
-        int cs=w.cstat[i]; double ax=w.Ax[i], sca=fmax(fabs(ax),1.0);
+        real tP=(real)((42+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
+        real tD=(real)((42+70+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rD=(real(1.0)-tD)*OPT_ramp0+tD*OPT_ramp1;
+        int cs=w.cstat[i]; real ax=w.Ax[i], sca=fmax(fabs(ax),real(1.0));
         if(cs!=ST_LOWER) w.lbA[i]=ax-sca*rP;
         if(cs!=ST_UPPER) w.ubA[i]=ax+sca*rP;
         if(cs==ST_LOWER){ w.lbA[i]=ax; w.y[42+i]=+rD; }
         if(cs==ST_UPPER){ w.ubA[i]=ax; w.y[42+i]=-rD; }
-        if(cs==ST_INACTIVE) w.y[42+i]=0.0;
+        if(cs==ST_INACTIVE) w.y[42+i]=real(0.0);
         w.Ax_l[i]=ax-w.lbA[i]; w.Ax_u[i]=w.ubA[i]-ax;
     }
     setupAuxiliaryQPgradient(w,c);
@@ -825,23 +840,23 @@ WBC_FN void performRamping(QPWork& w,QPCtx& c){
 // QProblem::performDriftCorrection (QProblem.cpp:5559-5652)
 WBC_FN void performDriftCorrection(QPWork& w,QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ int bs=w.bstat[i]; double xi=w.x[i];
-        if(bs==ST_LOWER){ w.lb[i]=xi; w.ub[i]=fmax(w.ub[i],xi); w.y[i]=fmax(w.y[i],0.0); }
-        else if(bs==ST_UPPER){ w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=xi; w.y[i]=fmin(w.y[i],0.0); }
-        else { w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=fmax(w.ub[i],xi); w.y[i]=0.0; } }
-    LANE_FOR(i,70){ int cs=w.cstat[i]; double ax=w.Ax[i];
-        if(cs==ST_LOWER){ w.lbA[i]=ax; w.Ax_l[i]=0.0; w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=fmax(w.y[42+i],0.0); }
-        else if(cs==ST_UPPER){ w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=ax; w.Ax_u[i]=0.0; w.y[42+i]=fmin(w.y[42+i],0.0); }
-        else { w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=0.0; } }
+    LANE_FOR(i,42){ int bs=w.bstat[i]; real xi=w.x[i];
+        if(bs==ST_LOWER){ w.lb[i]=xi; w.ub[i]=fmax(w.ub[i],xi); w.y[i]=fmax(w.y[i],real(0.0)); }
+        else if(bs==ST_UPPER){ w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=xi; w.y[i]=fmin(w.y[i],real(0.0)); }
+        else { w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=fmax(w.ub[i],xi); w.y[i]=real(0.0); } }
+    LANE_FOR(i,70){ int cs=w.cstat[i]; real ax=w.Ax[i];
+        if(cs==ST_LOWER){ w.lbA[i]=ax; w.Ax_l[i]=real(0.0); w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=fmax(w.y[42+i],real(0.0)); }
+        else if(cs==ST_UPPER){ w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=ax; w.Ax_u[i]=real(0.0); w.y[42+i]=fmin(w.y[42+i],real(0.0)); }
+        else { w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=real(0.0); } }
     setupAuxiliaryQPgradient(w,c);
 }
 
 // ---------------------------------------------------------------- Givens (QProblemB.ipp:409-470, four-multiplication form)
-WBC_DEV void computeGivens(double xold,double yold,double& xnew,double& ynew,double& cc,double& ss){
-    if(fabs(yold)<QZERO){ cc=1.0; ss=0.0; xnew=xold; ynew=yold; }
-    else { double mu=fabs(xold); if(fabs(yold)>mu) mu=fabs(yold);
-           double t=mu*sqrt((xold/mu)*(xold/mu)+(yold/mu)*(yold/mu)); if(xold<0.0) t=-t;
-           cc=xold/t; ss=yold/t; xnew=t; ynew=0.0; }
+WBC_DEV void computeGivens(real xold,real yold,real& xnew,real& ynew,real& cc,real& ss){
+    if(fabs(yold)<QZERO){ cc=real(1.0); ss=real(0.0); xnew=xold; ynew=yold; }
+    else { real mu=fabs(xold); if(fabs(yold)>mu) mu=fabs(yold);
+           real t=mu*sqrt((xold/mu)*(xold/mu)+(yold/mu)*(yold/mu)); if(xold<real(0.0)) t=-t;
+           cc=xold/t; ss=yold/t; xnew=t; ynew=real(0.0); }
 }
 // The column-wise Givens chains of addConstraint / addBound: rotation j is defined by (wv[j+1], wv[j]) where wv[j] is the
 // result of rotation j-1 -- a scalar recurrence every lane evaluates redundantly -- and then applied to the column
@@ -853,22 +868,22 @@ WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
 #if defined(WBC_EXACT_GIVENS)
     { // the reference's serial recurrence (QProblem.cpp:2909-2925, 3401-3450): rotation j is computed from (wv[j+1], result of rotation j-1); every lane
       // evaluates it redundantly, lane 0 stores
-        double prev=(nrot>0)?w.wv[0]:0.0;
-        for(int j=0;j<nrot;j++){ double xn,yn,cc,ss; computeGivens(w.wv[j+1],prev,xn,yn,cc,ss); if(lane==0){ w.cs_c[j]=cc; w.cs_s[j]=ss; } prev=xn; }
+        real prev=(nrot>0)?w.wv[0]:real(0.0);
+        for(int j=0;j<nrot;j++){ real xn,yn,cc,ss; computeGivens(w.wv[j+1],prev,xn,yn,cc,ss); if(lane==0){ w.cs_c[j]=cc; w.cs_s[j]=ss; } prev=xn; }
         WBC_SYNC();
         if(nrot>0&&lane==0) w.wv[nrot]=prev;
         WBC_SYNC();
         return;
     }
 #endif
-    double tlast=w.wv[0];
+    real tlast=w.wv[0];
     LANE_FOR(j,nrot){
-        double P=0.0; for(int k=0;k<=j;k++) P+=w.wv[k]*w.wv[k];      // sequential on purpose: a warp scan re-associates the sum and moved one degenerate working set
-        const double xold=w.wv[j+1];
-        const double yold=(j==0)?w.wv[0]:((w.wv[j]<0.0)?-sqrt(P):sqrt(P));
-        double cc,ss,t;
-        if(fabs(yold)<QZERO){ cc=1.0; ss=0.0; t=xold; }
-        else { t=sqrt(P+xold*xold); if(xold<0.0) t=-t; const double rt=1.0/t; cc=xold*rt; ss=yold*rt; }
+        real P=real(0.0); for(int k=0;k<=j;k++) P+=w.wv[k]*w.wv[k];      // sequential on purpose: a warp scan re-associates the sum and moved one degenerate working set
+        const real xold=w.wv[j+1];
+        const real yold=(j==0)?w.wv[0]:((w.wv[j]<real(0.0))?-sqrt(P):sqrt(P));
+        real cc,ss,t;
+        if(fabs(yold)<QZERO){ cc=real(1.0); ss=real(0.0); t=xold; }
+        else { t=sqrt(P+xold*xold); if(xold<real(0.0)) t=-t; const real rt=real(1.0)/t; cc=xold*rt; ss=yold*rt; }
         w.cs_c[j]=cc; w.cs_s[j]=ss; if(j==nrot-1) tlast=t;
     }
     WBC_SYNC();
@@ -878,8 +893,8 @@ WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
 WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
     const int lane=c.lane;
 #if WBC_NL==1
-    for(int i=0;i<nrows;i++){ int ii=(int)w.FR[i]; double qa=QQ(ii,0);
-        for(int j=0;j<nrot;j++){ double qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
+    for(int i=0;i<nrows;i++){ int ii=(int)w.FR[i]; real qa=QQ(ii,0);
+        for(int j=0;j<nrot;j++){ real qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
         QQ(ii,nrot)=qa; }
 #else
     if(nrows>32){
@@ -888,24 +903,24 @@ WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
         const int half=(nrows+1)>>1;
         if(lane<half){
             const bool two=lane+half<nrows;
-            double* r0=&w.Q[(int)w.FR[lane]]; double* r1=&w.Q[(int)w.FR[two?lane+half:lane]];
+            real* r0=&w.Q[(int)w.FR[lane]]; real* r1=&w.Q[(int)w.FR[two?lane+half:lane]];
             if(two){
-                double a0=r0[0], a1=r1[0];
+                real a0=r0[0], a1=r1[0];
                 #pragma unroll 2
-                for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=r1[LD*(j+1)];
+                for(int j=0;j<nrot;j++){ const real cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)], b1=r1[LD*(j+1)];
                     r0[LD*j]=-ss*b0+cc*a0; r1[LD*j]=-ss*b1+cc*a1; a0=cc*b0+ss*a0; a1=cc*b1+ss*a1; }
                 r0[LD*nrot]=a0; r1[LD*nrot]=a1;
             } else {                                             // odd row count: the last lane of the first half has one row
-                double a0=r0[0];
-                for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
+                real a0=r0[0];
+                for(int j=0;j<nrot;j++){ const real cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
                 r0[LD*nrot]=a0;
             }
         }
     } else if(lane<nrows){
-        double* r0=&w.Q[(int)w.FR[lane]];
-        double a0=r0[0];
+        real* r0=&w.Q[(int)w.FR[lane]];
+        real a0=r0[0];
         #pragma unroll 2
-        for(int j=0;j<nrot;j++){ const double cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
+        for(int j=0;j<nrot;j++){ const real cc=w.cs_c[j], ss=w.cs_s[j], b0=r0[LD*(j+1)]; r0[LD*j]=-ss*b0+cc*a0; a0=cc*b0+ss*a0; }
         r0[LD*nrot]=a0;
     }
 #endif
@@ -927,10 +942,10 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
           // borderline cases: the full test's "zero" is |Z (Z'HZ)^-1 Z'a|, which vanishes with Z'a (measured on 6655 tests of
           // this QP family: independent rows have max|Z'a| >= 1e-2 |a|, dependent ones exactly 0).  Only the band in between
           // runs the reference's test.
-            double l2=0.0; for(int i=0;i<nFR;i++){ const double a=w.tmpv[(int)w.FR[i]]; l2+=a*a; }
-            Qt_times(w,c,0,nZ,w.tmpv,1.0,w.xFRz); double mx=0.0; LANE_FOR(j,nZ) mx=fmax(mx,fabs(w.xFRz[j]));
+            real l2=real(0.0); for(int i=0;i<nFR;i++){ const real a=w.tmpv[(int)w.FR[i]]; l2+=a*a; }
+            Qt_times(w,c,0,nZ,w.tmpv,real(1.0),w.xFRz); real mx=real(0.0); LANE_FOR(j,nZ) mx=fmax(mx,fabs(w.xFRz[j]));
             mx=wbc_max(mx);
-            const double nrm=sqrt(l2);
+            const real nrm=sqrt(l2);
             const bool sureLI=mx>LI_SURE*nrm, sureLD=mx<=LI_NONE*nrm;
 #if defined(WBC_EXACT)
             shortcut= sureLI?1:(sureLD?0:-1);
@@ -940,14 +955,14 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         }
         int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
         if(rv!=QP_OK) return false;
-        double weight=0.0, zero=0.0;
+        real weight=real(0.0), zero=real(0.0);
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
         LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; weight=fmax(weight,fabs(w.dyFX[ii])); zero=fmax(zero,fabs(w.dx[ii])); }
         LANE_FOR(i,nFR) zero=fmax(zero,fabs(w.dx[(int)w.FR[i]]));
         weight=wbc_max(weight); zero=wbc_max(zero);
 #if !defined(__CUDACC__) && defined(WBC_LI_STATS)
-        { double l2=0.0,mx=0.0,amax=0.0; for(int i=0;i<nFR;i++){ double a=w.tmpv[(int)w.FR[i]]; l2+=a*a; amax=fmax(amax,fabs(a)); }
-          for(int j=0;j<nZ;j++){ double sum=0.0; for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=w.tmpv[ii]*QQ(ii,j); } mx=fmax(mx,fabs(sum)); }
+        { real l2=real(0.0),mx=real(0.0),amax=real(0.0); for(int i=0;i<nFR;i++){ real a=w.tmpv[(int)w.FR[i]]; l2+=a*a; amax=fmax(amax,fabs(a)); }
+          for(int j=0;j<nZ;j++){ real sum=real(0.0); for(int i=0;i<nFR;i++){ int ii=(int)w.FR[i]; sum+=w.tmpv[ii]*QQ(ii,j); } mx=fmax(mx,fabs(sum)); }
           printf("LISTAT C %d %.3e %.3e %.3e %.3e %.3e\n",(int)(zero>OPT_epsLITests*weight),mx,l2,amax,zero,weight); }
 #endif
 #if defined(WBC_EXACT)
@@ -957,9 +972,9 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     }
     LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
     WBC_SYNC();
-    double l2=0.0; for(int i=0;i<nFR;i++){ double a=w.arow[(int)w.FR[i]]; l2+=a*a; }
+    real l2=real(0.0); for(int i=0;i<nFR;i++){ real a=w.arow[(int)w.FR[i]]; l2+=a*a; }
     bool li=false;
-    Qt_times(w,c,0,nZ,w.arow,1.0,w.xFRz); LANE_FOR(j,nZ) if(fabs(w.xFRz[j])>OPT_epsLITests*l2) li=true;
+    Qt_times(w,c,0,nZ,w.arow,real(1.0),w.xFRz); LANE_FOR(j,nZ) if(fabs(w.xFRz[j])>OPT_epsLITests*l2) li=true;
     return wbc_ballot(li)!=0u;
 }
 // QProblem::addBound_checkLI (QProblem.cpp:3487-3590)
@@ -969,7 +984,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
     if(fullTest){
         int shortcut=-1; (void)shortcut;
         { // same shortcut as addConstraint_checkLI with a = e_number
-            double mx=0.0; LANE_FOR(i,nZ) mx=fmax(mx,fabs(QQ(number,i)));
+            real mx=real(0.0); LANE_FOR(i,nZ) mx=fmax(mx,fabs(QQ(number,i)));
             mx=wbc_max(mx);
             const bool sureLI=mx>LI_SURE, sureLD=mx<=LI_NONE;
 #if defined(WBC_EXACT)
@@ -978,11 +993,11 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
             if(sureLI||sureLD){ WBC_FLOPS(3.0*(2.0*c.nAC*c.nAC+4.0*c.nFR*c.nAC+4.0*c.nFR*nZ+4.0*c.nFR*c.nFR+4.0*nZ*nZ)+2.0*(2.0*c.nFR*c.nFR+4.0*c.nAC*42.0)); return sureLI; }
 #endif
         }
-        LANE_FOR(j,42) w.tmpv[j]=(j==number)?1.0:0.0;
+        LANE_FOR(j,42) w.tmpv[j]=(j==number)?real(1.0):real(0.0);
         WBC_SYNC();
         int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
         if(rv!=QP_OK) return false;
-        double weight=0.0, zero=0.0;
+        real weight=real(0.0), zero=real(0.0);
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
         LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; weight=fmax(weight,fabs(w.dyFX[ii])); zero=fmax(zero,fabs(w.dx[ii])); }
         LANE_FOR(i,c.nFR) zero=fmax(zero,fabs(w.dx[(int)w.FR[i]]));
@@ -1003,7 +1018,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
 // xiB in w.Zdz (variable number).  returns QP_OK, or QP_RET_HOTSTART_STOPPED_INFEASIBILITY if no index can leave.
 WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBound){
     const int lane=c.lane, nAC=c.nAC, nFX=c.nFX;
-    double y_min=OPT_maxDualJump; int ymn=-1, ymnb=-1;
+    real y_min=OPT_maxDualJump; int ymn=-1, ymnb=-1;
     WBC_SYNC();
     LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=w.xFRy[i]; }
     performRatioTest(c,nAC,w.AC,w.cstat,w.num,w.den,y_min,ymn);
@@ -1016,11 +1031,11 @@ WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBou
     LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]-=y_min*w.xFRy[i]; }
     LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.y[ii]-=y_min*w.Zdz[ii]; }
     WBC_SYNC();
-    if(lane==0){ double v=(status==ST_LOWER)?y_min:-y_min; if(isBound) w.y[number]=v; else w.y[42+number]=v; }
+    if(lane==0){ real v=(status==ST_LOWER)?y_min:-y_min; if(isBound) w.y[number]=v; else w.y[42+number]=v; }
     WBC_SYNC();
     int rv;
-    if(ymIsBound){ rv=removeBound(w,c,ymn); if(rv!=QP_OK) return rv; if(lane==0) w.y[ymn]=0.0; }
-    else { rv=removeConstraint(w,c,ymn); if(rv!=QP_OK) return rv; if(lane==0) w.y[42+ymn]=0.0; }
+    if(ymIsBound){ rv=removeBound(w,c,ymn); if(rv!=QP_OK) return rv; if(lane==0) w.y[ymn]=real(0.0); }
+    else { rv=removeConstraint(w,c,ymn); if(rv!=QP_OK) return rv; if(lane==0) w.y[42+ymn]=real(0.0); }
     WBC_SYNC();
     return QP_OK;
 }
@@ -1028,25 +1043,25 @@ WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBou
 WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
     const int lane=c.lane;
     if(addConstraint_checkLI(w,c,number,true)) return QP_OK;
-    const int nFR=c.nFR, nAC=c.nAC, nFX=c.nFX, nZ=nFR-nAC; const double sg=(C_status==ST_LOWER)?1.0:-1.0;
+    const int nFR=c.nFR, nAC=c.nAC, nFX=c.nFX, nZ=nFR-nAC; const real sg=(C_status==ST_LOWER)?real(1.0):-real(1.0);
     WBC_SYNC();
     if(nAC>0){
         LANE_FOR(j,42) w.arow[j]=sg*Ael_dev(WQP,number,j);
         WBC_SYNC();
-        Qt_times(w,c,nZ,nAC,w.arow,1.0,w.tB);
+        Qt_times(w,c,nZ,nAC,w.arow,real(1.0),w.tB);
         if(!prepare_T(w,c)) return QP_RET_UNSUPPORTED_PATH;
         backsolveT(w,c,w.tB,true,w.xFRy);
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=Acol_acc(WQP,ii,w.ym,sg*Ael_dev(WQP,number,ii),-1.0); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=Acol_acc(WQP,ii,w.ym,sg*Ael_dev(WQP,number,ii),-real(1.0)); }
     return ensureLI_exchange(w,c,number,C_status,false);
 }
 // QProblem::addBound_ensureLI (QProblem.cpp:3596-3780)
 WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
     const int lane=c.lane;
     if(addBound_checkLI(w,c,number,true)) return QP_OK;
-    const int nAC=c.nAC, nFX=c.nFX, nZ=c.nFR-nAC; const double sg=(B_status==ST_LOWER)?1.0:-1.0;
+    const int nAC=c.nAC, nFX=c.nFX, nZ=c.nFR-nAC; const real sg=(B_status==ST_LOWER)?real(1.0):-real(1.0);
     WBC_SYNC();
     if(nAC>0){
         LANE_FOR(i,nAC) w.tB[i]=sg*QQ(number,nZ+i);
@@ -1055,7 +1070,7 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
     }
     WBC_SYNC();
     scatter_yAC(w,c,w.xFRy);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=Acol_acc(WQP,ii,w.ym,0.0,-1.0); }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.Zdz[ii]=Acol_acc(WQP,ii,w.ym,real(0.0),-real(1.0)); }
     return ensureLI_exchange(w,c,number,B_status,true);
 }
 
@@ -1079,24 +1094,24 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
     // row [wZ wY] = aFR' [Z Y]
     LANE_FOR(j,42) w.arow[j]=Ael_dev(WQP,number,j);
     WBC_SYNC();
-    Qt_times(w,c,0,c.nFR,w.arow,1.0,w.wv);
+    Qt_times(w,c,0,c.nFR,w.arow,real(1.0),w.wv);
     addConstraint_tail(w,c,number,C_status);
     return QP_OK;
 }
 // setupAuxiliaryWorkingSet step of the warm start (SQProblem.cpp:340-515 -> QProblem.cpp:2212-2378): cheap LI test
 // (addConstraint_checkLI, QProblem.cpp:3081-3105) and addConstraint without LI exchange.  Both need aFR'Z; it is computed once
 // (the first nZ entries of aFR'[Z Y] are the very same sums).
-WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,const QPData& qd,int number,int C_status){
+template<class QD> WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,const QD& qd,int number,int C_status){
     const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_SYNC();
     LANE_FOR(j,42) w.arow[j]=Ael_dev(qd,number,j);
     WBC_SYNC();
-    double l2=0.0;
+    real l2=real(0.0);
     if(c.frIdentity){
         #pragma unroll 6
-        for(int i=0;i<42;i++){ const double a=w.arow[i]; l2+=a*a; }
-    } else for(int i=0;i<nFR;i++){ const double a=w.arow[(int)w.FR[i]]; l2+=a*a; }
-    Qt_times(w,c,0,nFR,w.arow,1.0,w.wv);
+        for(int i=0;i<42;i++){ const real a=w.arow[i]; l2+=a*a; }
+    } else for(int i=0;i<nFR;i++){ const real a=w.arow[(int)w.FR[i]]; l2+=a*a; }
+    Qt_times(w,c,0,nFR,w.arow,real(1.0),w.wv);
     bool li=false; LANE_FOR(j,nZ) if(fabs(w.wv[j])>OPT_epsLITests*l2) li=true;
     if(wbc_ballot(li)==0u) return;
     addConstraint_tail(w,c,number,C_status);
@@ -1119,9 +1134,9 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
     apply_chain_Q(w,c,(nAC>0)?nrot:(nZ-1),nFR);
     if(nAC>0){
         // T rows: rotation j >= nZ-1 touches rows i >= nFR-2-j at column 1+tcol-nZ+j, paired with the temporary column tmp
-        LANE_FOR(i,nAC){ double tmp=0.0; int j0=nFR-2-i; if(j0<nZ-1) j0=nZ-1;
-            for(int j=j0;j<=nFR-2;j++){ int col=1+tcol-nZ+j; double xo=TT(i,col), cc=w.cs_c[j], ss=w.cs_s[j];
-                double xn=cc*xo+ss*tmp, yn=-ss*xo+cc*tmp; tmp=xn; TT(i,col)=yn; } }
+        LANE_FOR(i,nAC){ real tmp=real(0.0); int j0=nFR-2-i; if(j0<nZ-1) j0=nZ-1;
+            for(int j=j0;j<=nFR-2;j++){ int col=1+tcol-nZ+j; real xo=TT(i,col), cc=w.cs_c[j], ss=w.cs_s[j];
+                real xn=cc*xo+ss*tmp, yn=-ss*xo+cc*tmp; tmp=xn; TT(i,col)=yn; } }
     }
     moveFreeToFixed(w,c,number,B_status);
     return QP_OK;
@@ -1139,11 +1154,11 @@ WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
         LANE_FOR(m,nAC){ for(int i=number_idx+1;i<nAC;i++){ if(m<i) TT(i-1,SIZET-1-m)=TT(i,SIZET-1-m); else if(m==i) w.wv[i-1]=TT(i,SIZET-1-m); } }
         for(int j=nAC-2-number_idx;j>=0;j--){
             WBC_SYNC();
-            const int pr=nAC-2-j; double xn,yn,cc,ss; computeGivens(TT(pr,tcol+1+j),w.wv[pr],xn,yn,cc,ss);
+            const int pr=nAC-2-j; real xn,yn,cc,ss; computeGivens(TT(pr,tcol+1+j),w.wv[pr],xn,yn,cc,ss);
             WBC_SYNC();
             if(lane==0){ TT(pr,tcol+1+j)=xn; w.wv[pr]=yn; }
-            for(int i=nAC-j-1+lane;i<nAC-1;i+=WBC_NL){ double xo=TT(i,tcol+1+j), yo=TT(i,tcol+j); TT(i,tcol+1+j)=cc*xo+ss*yo; TT(i,tcol+j)=-ss*xo+cc*yo; }
-            LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; double xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
+            for(int i=nAC-j-1+lane;i<nAC-1;i+=WBC_NL){ real xo=TT(i,tcol+1+j), yo=TT(i,tcol+j); TT(i,tcol+1+j)=cc*xo+ss*yo; TT(i,tcol+j)=-ss*xo+cc*yo; }
+            LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; real xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
         }
     }
     moveActiveToInactive(w,c,number);
@@ -1154,18 +1169,18 @@ WBC_FN int removeBound(QPWork& w,QPCtx& c,int number){
     const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     moveFixedToFree(w,c,number);
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; QQ(ii,nFR)=0.0; QQ(number,i)=0.0; }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; QQ(ii,nFR)=real(0.0); QQ(number,i)=real(0.0); }
     WBC_SYNC();
-    if(lane==0) QQ(number,nFR)=1.0;
+    if(lane==0) QQ(number,nFR)=real(1.0);
     if(nAC>0){
         LANE_FOR(i,nAC) w.tmpv[i]=Ael_dev(WQP,(int)w.AC[i],number);
         for(int j=nAC-1;j>=0;j--){
             WBC_SYNC();
-            const int pr=nAC-1-j; double xn,yn,cc,ss; computeGivens(w.tmpv[pr],TT(pr,tcol+j),xn,yn,cc,ss);
+            const int pr=nAC-1-j; real xn,yn,cc,ss; computeGivens(w.tmpv[pr],TT(pr,tcol+j),xn,yn,cc,ss);
             WBC_SYNC();
             if(lane==0){ TT(pr,tcol+j)=xn; w.tmpv[pr]=yn; }
-            for(int i=nAC-j+lane;i<nAC;i+=WBC_NL){ double xo=w.tmpv[i], yo=TT(i,tcol+j); TT(i,tcol+j)=cc*xo+ss*yo; w.tmpv[i]=-ss*xo+cc*yo; }
-            LANE_FOR(i,nFR+1){ int ii=(int)w.FR[i]; double xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
+            for(int i=nAC-j+lane;i<nAC;i+=WBC_NL){ real xo=w.tmpv[i], yo=TT(i,tcol+j); TT(i,tcol+j)=cc*xo+ss*yo; w.tmpv[i]=-ss*xo+cc*yo; }
+            LANE_FOR(i,nFR+1){ int ii=(int)w.FR[i]; real xo=QQ(ii,nZ+1+j), yo=QQ(ii,nZ+j); QQ(ii,nZ+1+j)=cc*xo+ss*yo; QQ(ii,nZ+j)=-ss*xo+cc*yo; }
         }
     }
     WBC_SYNC();
@@ -1178,8 +1193,8 @@ WBC_FN int changeActiveSet(QPWork& w,QPCtx& c,int BC_idx,int BC_status,bool BC_i
     int rv=QP_OK;
     if(BC_status==2) return QP_OK;
     if(BC_status==ST_INACTIVE){
-        if(BC_isBound){ rv=removeBound(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[BC_idx]=0.0; }
-        else { rv=removeConstraint(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[42+BC_idx]=0.0; }
+        if(BC_isBound){ rv=removeBound(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[BC_idx]=real(0.0); }
+        else { rv=removeConstraint(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[42+BC_idx]=real(0.0); }
         WBC_SYNC();
     } else {
         if(BC_isBound) rv=addBound(w,c,BC_idx,BC_status,true,true);
@@ -1188,7 +1203,7 @@ WBC_FN int changeActiveSet(QPWork& w,QPCtx& c,int BC_idx,int BC_status,bool BC_i
     return rv;
 }
 // QProblem::updateFarBounds (QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246): see far_rv
-WBC_DEV void updateFarBounds(QPWork&,QPCtx& c,double curFarBound){ c.farbound=curFarBound; c.farRampOffset=c.rampOffset; }
+WBC_DEV void updateFarBounds(QPWork&,QPCtx& c,real curFarBound){ c.farbound=curFarBound; c.farRampOffset=c.rampOffset; }
 // QProblem::solveQP (QProblem.cpp:1477-1747); nWSR in/out like the reference
 WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
@@ -1229,8 +1244,8 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
 // QProblem::hotstart (QProblem.cpp:446-640): far-bound outer loop
 WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane; const int nWSR_max=nWSR; int nWSR_performed=0;
-    double farbound=OPT_initialFarBounds;
-    { double m=0.0; LANE_FOR(i,70){ double u=WQP.ubA[i], l=WQP.lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
+    real farbound=OPT_initialFarBounds;
+    { real m=real(0.0); LANE_FOR(i,70){ real u=WQP.ubA[i], l=WQP.lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
     updateFarBounds(w,c,farbound);
     int rv;
     for(;;){
@@ -1242,9 +1257,9 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
             if(farbound>=QINFTY){ rv=QP_RET_HOTSTART_STOPPED_INFEASIBILITY; break; }
             updateFarBounds(w,c,farbound);
         } else if(c.status==QPS_SOLVED){
-            const double tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
+            const real tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
             LANE_FOR(i,42){ if(fabs(tgt_lb(c,i)-w.x[i])<tol) na++; if(fabs(tgt_ub(c,i)-w.x[i])<tol) na++; }
-            LANE_FOR(i,70){ const double l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>WQP.lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<WQP.ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
+            LANE_FOR(i,70){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>WQP.lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<WQP.ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
             if(wbc_ballot(na>0)==0u) break;
             c.status=QPS_HOMOTOPYQPSOLVED;
             if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
@@ -1258,10 +1273,10 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
 // fixed at its (far) lower bound (initialStatusBounds = ST_LOWER) and no active constraint.
 WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ w.x[i]=0.0; w.y[i]=0.0; w.g[i]=0.0; w.lb[i]=0.0; w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
-    LANE_FOR(i,70){ w.y[42+i]=0.0; w.Ax[i]=0.0; w.lbA[i]=-OPT_boundRelaxation; w.ubA[i]=OPT_boundRelaxation; w.Ax_l[i]=OPT_boundRelaxation; w.Ax_u[i]=OPT_boundRelaxation;
+    LANE_FOR(i,42){ w.x[i]=real(0.0); w.y[i]=real(0.0); w.g[i]=real(0.0); w.lb[i]=real(0.0); w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
+    LANE_FOR(i,70){ w.y[42+i]=real(0.0); w.Ax[i]=real(0.0); w.lbA[i]=-OPT_boundRelaxation; w.ubA[i]=OPT_boundRelaxation; w.Ax_l[i]=OPT_boundRelaxation; w.Ax_u[i]=OPT_boundRelaxation;
                     w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
-    c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.frIdentity=0; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=0.0;
+    c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.frIdentity=0; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=real(0.0);
     setupTQfactorisation(w,c);
     c.status=QPS_AUXILIARYQPSOLVED;
     performRamping(w,c);
@@ -1277,7 +1292,7 @@ WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
 // free / inactive again, Q = I, T empty, then the old active constraints (`old` = their statuses) re-added in ascending order with the
 // cheap LI test and no LI exchange.  Touches only the prefix of the workspace (Q, T, lists, Givens vectors, arow) and reads the QP
 // data through `qd`, so it also runs as a kernel of its own with 9 robots per SM (wbc_warm_setup_kernel).
-WBC_FN void rebuild_TQ(QPWork& w,QPCtx& c,const QPData& qd,const signed char* old){
+template<class QD> WBC_FN void rebuild_TQ(QPWork& w,QPCtx& c,const QD& qd,const signed char* old){
     const int lane=c.lane;
     LANE_FOR(i,42){ w.FR[i]=(signed char)i; }
     LANE_FOR(i,70){ w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; }
@@ -1317,17 +1332,17 @@ WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
     constexpr int KB=19;                                                        // 3 batches of 19 x 32 doubles cover Q (1806)
     #pragma unroll 1
     for(int base=0;base<42*LD;base+=KB*WBC_NL){
-        double t[KB];
+        real t[KB];
         #pragma unroll
-        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<42*LD)?p.Q[i]:0.0; }
+        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<42*LD)?p.Q[i]:real(0.0); }
         #pragma unroll
         for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; if(i<42*LD) w.Q[i]=t[k]; }
     }
     #pragma unroll 1
     for(int base=0;base<nT;base+=KB*WBC_NL){
-        double t[KB];
+        real t[KB];
         #pragma unroll
-        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<nT)?p.T[i]:0.0; }
+        for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<nT)?p.T[i]:real(0.0); }
         #pragma unroll
         for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; if(i<nT) w.RT[i]=t[k]; }
     }
@@ -1345,7 +1360,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
     WBC_FLOPS(4.0*42*42+4.0*70*42);
-    LANE_FOR(i,70){ double ax=Arow_acc(WQP,i,w.x,0.0,1.0); w.Ax[i]=ax; double l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    LANE_FOR(i,70){ real ax=Arow_acc(WQP,i,w.x,real(0.0),real(1.0)); w.Ax[i]=ax; real l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;

@@ -10,7 +10,7 @@ extern "C" void* emulqp_create(){ EmulQP* e=new EmulQP; memset(e,0,sizeof(*e)); 
 extern "C" void emulqp_destroy(void* h){ delete (EmulQP*)h; }
 // first != 0: init (cold), else hotstart.  outputs: x[42], y[112], ws[112], returns rc; *nwsr in/out
 extern "C" int emulqp_solve(void* h,const double* qpdata,int first,int* nwsr,double* x,double* y,signed char* ws){
-    EmulQP* e=(EmulQP*)h; memcpy(&e->w.qp,qpdata,sizeof(QPData));
+    EmulQP* e=(EmulQP*)h; { real* dst=(real*)&e->w.qp; for(int i=0;i<QPDATA_DOUBLES;i++) dst[i]=(real)qpdata[i]; }
     int n=*nwsr; int rc;
     if(first) rc=qp_init(e->w,e->c,n);
     else if(getenv("EMUL_SPLIT")){          // the two-kernel warm start: rebuild in a second workspace, hand over through QPPre
@@ -20,7 +20,7 @@ extern "C" int emulqp_solve(void* h,const double* qpdata,int first,int* nwsr,dou
         rc=qp_hotstart(e->w,e->c,n,&pre);
     } else rc=qp_hotstart(e->w,e->c,n,nullptr);
     *nwsr=n;
-    memcpy(x,e->w.x,42*8); memcpy(y,e->w.y,112*8);
+    for(int i=0;i<42;i++) x[i]=e->w.x[i]; for(int i=0;i<112;i++) y[i]=e->w.y[i];
     for(int i=0;i<42;i++) ws[i]=e->w.bstat[i]; for(int i=0;i<70;i++) ws[42+i]=e->w.cstat[i];
     return rc;
 }
