@@ -101,7 +101,17 @@ template<class T> struct QPDataT {
     T cmask[4];       // 1.0 = stance, 0.0 = swing  (leg order LH, LF, RF, RH)
 };
 typedef QPDataT<double> QPData;      // what the assembly kernel writes to HBM (always fp64)
-typedef QPDataT<real> QPDataR;       // the solver's copy in shared memory, in its arithmetic type
+// The part of it the solver keeps in shared memory, in its arithmetic type: the matrix blocks every product with A and H reads.  The constraint
+// bounds lbA / ubA (read twice per working-set change, element-wise) and bias_j (read once, by the torque epilogue) stay in HBM / L1: 1.2 KB of
+// shared memory per robot that decide whether an SM holds 5 or 6 robots.
+template<class T> struct QPHotT {
+    typedef T value_type;
+    T Jc[12*18], Mbb[36], Mjj[144], Hff[144], gf[12];    // same order as the head of QPDataT
+    T mu, rho, cmask[4];
+};
+typedef QPHotT<real> QPHotR;
+constexpr int QPHOT_HEAD = 12*18+36+144+144+12;            // leading elements shared with QPDataT
+static_assert(sizeof(QPHotT<double>)/sizeof(double)==QPHOT_HEAD+6,"QPHot layout");
 constexpr int QPDATA_DOUBLES = sizeof(QPData)/sizeof(double);
 
 // ---- per-instance persistent controller state (wbc.hpp:150-161) kept in HBM between ticks ----

@@ -10,8 +10,12 @@
 #include <string>
 #include <vector>
 #include "../../include/wbc_b200.h"
-#ifndef WBC_GANG
-#define WBC_GANG 5              /* solver warps (= robots in flight) per CTA, one CTA per SM: 5 x 41.5 KB of shared memory */
+#ifndef WBC_GANG                /* solver warps (= robots in flight) per CTA, one CTA per SM: as many as the 227 KB of shared memory hold */
+  #if defined(WBC_FP32)
+    #define WBC_GANG 11         /* 11 x 19.0 KB */
+  #else
+    #define WBC_GANG 6          /* 6 x 37.6 KB */
+  #endif
 #endif
 #include "wbc_assembly.cuh"
 #include "wbc_qp.cuh"
@@ -107,7 +111,7 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
     unsigned long long* guard=reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(smem)+QPWORK_TQ_BYTES);
     constexpr int NGUARD=(int)((sizeof(QPWork)-QPWORK_TQ_BYTES)/8);
     if(canary){ LANE_FOR(i,NGUARD) guard[i]=0xFFFFFFFFFFFFFFFFull; WBC_SYNC(); }
-    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
 #if defined(WBC_PROFILE)
     c.flops=0.0;
 #endif
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
 }
 
 // ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart) + torque recovery
-// One robot per warp; WBC_GANG warps per CTA (one CTA per SM: WBC_GANG x 41.5 KB of shared memory) walk the iterations of their robots in
+// One robot per warp; WBC_GANG warps per CTA (one CTA per SM: 6 x 37.6 KB of shared memory in fp64, 11 x 19.0 KB in fp32) walk the iterations of their robots in
 // step (wbc_qp.cuh "gang mode").  Robots are pulled from an atomic work counter.  cohort = 0: a warp fetches its next robot as soon as
 // it is done (hot-started ticks: iteration counts 0..100); cohort = 1: the gang fetches together and waits for its slowest member (cold
 // batches: all members then sit at the same iteration index with matrices of the same size, which keeps the barrier waits short).
@@ -141,18 +145,15 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
         if(cohort){ if(gang_bar(r>=N)) break; }                      // the whole gang is out of work
         if(r>=N){ while(!gang_bar(1)){} if(cohort) continue; break; }     // keep the others' barriers complete until every warp is done
         const bool isFirst=first[r]!=0;
-#if defined(WBC_QPDATA_GLOBAL)
-        if(lane==0) w.qpg=&qpd[r];
-#else
         // all global loads of a robot are issued before the first shared store: the workspace is reached through a generic pointer, so the
-        // compiler will not move a load above a store by itself and every 32-element round would cost a full memory round trip
-        { const double* src=(const double*)&qpd[r]; real* dst=(real*)&w.qp; constexpr int K=(QPDATA_DOUBLES+31)/32; double t[K];      // fp64 in HBM -> the solver's type
+        // compiler will not move a load above a store by itself and every 32-element round would cost a full memory round trip.
+        // Only the matrix blocks (head of QPData) and mu, rho, cmask (its last 6 elements) go to shared memory, converted to the solver's type.
+        { const double* src=(const double*)&qpd[r]; real* dst=(real*)&w.qp; constexpr int K=(QPHOT_HEAD+6+31)/32; double t[K];
           #pragma unroll
-          for(int k=0;k<K;k++){ const int i=lane+32*k; t[k]=(i<QPDATA_DOUBLES)?__ldg(src+i):0.0; }
+          for(int k=0;k<K;k++){ const int i=lane+32*k; t[k]=(i<QPHOT_HEAD)?__ldg(src+i):((i<QPHOT_HEAD+6)?__ldg(src+(QPDATA_DOUBLES-6)+(i-QPHOT_HEAD)):0.0); }
           #pragma unroll
-          for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPDATA_DOUBLES) dst[i]=(real)t[k]; } }
-#endif
-        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED;
+          for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPHOT_HEAD+6) dst[i]=(real)t[k]; } }
+        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
 #if defined(WBC_PROFILE)
         for(int k=0;k<8;k++) c.prof[k]=0;
         c.flops=0.0;
@@ -188,10 +189,10 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
         WBC_SYNC();
         // computeJointTorques (wbc.cpp:553-577) on the solution still in shared memory: tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*, f* = x[18:30];
         // a robot whose solve did not return 0 publishes zero torques (terminate(), :626-635).  w.x = qpSolution_ here (see above).
-        if(lane<12){ const int i=lane; const QPDataR& q=WQP;
+        if(lane<12){ const int i=lane; const QPHotR& q=WQP;
             real s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*w.x[6+j];
             real t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*w.x[18+j];
-            out.tau[i*N+r]= (rcv==0)? (double)(s+q.biasj[i]-t) : 0.0;
+            out.tau[i*N+r]= (rcv==0)? (double)(s+(real)c.qg->biasj[i]-t) : 0.0;
             out.grf[i*N+r]= w.x[18+i]; }
         if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
                      if(stats){ stats[r]+=1; if(rcv!=0) stats[N+r]+=1; stats[2*N+r]+=nWSR; if(nWSR>stats[3*N+r]) stats[3*N+r]=nWSR; }   // ticks, failed ticks, sum / max of nWSR

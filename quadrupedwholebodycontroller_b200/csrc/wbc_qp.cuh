@@ -70,11 +70,7 @@ constexpr real LI_SURE=real(1.0e-6), LI_NONE=real(1.0e-12);
 
 constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
 constexpr int SIZET=42;               // sizeT = min(nV,nC)
-#if defined(WBC_QPDATA_GLOBAL)
-  #define WQP (*w.qpg)
-#else
-  #define WQP (w.qp)
-#endif
+#define WQP (w.qp)
 #define QQ(i,j) w.Q[(i)+LD*(j)]       // Types.hpp:141-147: Q column-major
 // R (nZ x nZ upper triangular) and T (nAC x nAC reverse triangular) are the only parts of the reference's 42x42 R and T
 // arrays that are ever read, and nZ + nAC = nFR <= 42, so both live PACKED in one 903-entry buffer: T's row i (its i+1
@@ -138,7 +134,7 @@ struct QPState {
     int rampOffset, status, pad_;
 };
 
-// per-instance shared-memory workspace (40.9 KB -> 5 instances per SM).  The members up to and including `arow` are all the warm-start
+// per-instance shared-memory workspace (37.6 KB in fp64 -> 6 instances per SM; 19.0 KB in fp32 -> 11).  The members up to and including `arow` are all the warm-start
 // TQ rebuild touches (rebuild_TQ): the kernel that runs only that phase allocates just this prefix (QPWORK_TQ_BYTES, 9 instances per SM).
 struct QPWork {
     real Q[42*LD];
@@ -148,24 +144,22 @@ struct QPWork {
     // all of it reused as the 12 x nZ block (HZ)_force by the projected Cholesky (which runs when none of them is live)
     union {
         struct {
-            real wv[42], cs_c[42], cs_s[42], tmpv[42], arow[42];
-            union { struct { real num[70], den[70], dAx[70]; }; struct { real tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; };
+            real tmpv[42], arow[42];
+            // three groups that are never live together: ratio tests (performStep, LI exchange) | step-direction temporaries | Givens vectors of an add
+            // (computed only after the LI test / exchange of the same add has finished with the other two)
+            union { struct { real num[70], den[70], dAx[70]; }; struct { real tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; struct { real wv[42], cs_c[42], cs_s[42]; }; };
             real xFRy[42], xFRz[42], Zdz[42], ym[70];
         };
         real HZf[12*LD];
     };
-#if defined(WBC_QPDATA_GLOBAL)
-    const QPDataR* qpg;                         // compact H, A, new g / lbA / ubA stay in global memory (L1/L2): read-only during the solve
-#else
-    QPDataR qp;                                 // compact H, A, new g / lbA / ubA
-#endif
+    QPHotR qp;                                  // the matrix blocks of the compact QP (H, A); lbA / ubA / bias_j are read from HBM through QPCtx::qg
     real x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
-    real dg[42], dlb[42], dub[42], dlbA[70], dubA[70];         // data shift
+    real dlbA[70], dubA[70];                                     // data shift of the constraint bounds (the shifts of g, lb, ub are re-evaluated where used: shift_dg / shift_dlb / shift_dub)
     real dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
     real rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
 };
 constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(real)+408+5*42*sizeof(real);
-static_assert(offsetof(QPWork,wv)+5*42*sizeof(real)==QPWORK_TQ_BYTES,"layout of the TQ-rebuild prefix");
+static_assert(offsetof(QPWork,tmpv)+5*42*sizeof(real)==QPWORK_TQ_BYTES,"layout of the TQ-rebuild prefix");
 
 // what the warm-start TQ rebuild hands to the solve kernel (HBM): Q = [Z Y], the nAC rows of T, the index lists
 struct QPPre {
@@ -185,6 +179,7 @@ struct QPCtx {
     int farRampOffset;   // rampOffset at the last updateFarBounds
     real farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
     real tau;
+    const QPData* qg;    // this robot's compact QP in HBM (fp64): new lbA / ubA targets, bias_j
 #if defined(WBC_PROFILE)
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
     double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
@@ -229,7 +224,7 @@ template<class QD> WBC_FN real Ael_dev(const QD& q,int i,int j){ return (real)Ae
 // `y[.] += val*x` / `y[.] -= val*x` onto the existing y; zero entries of the dense row add exactly 0).  sgn is +1.0 or -1.0 exactly,
 // so (sgn*a)*v == +-(a*v) bit for bit.
 // Arow_acc: y + sgn*(A v)_i for a 42-vector v (callers mask v to the free / fixed columns beforehand: the reference visits the selected columns only).
-WBC_FN real Arow_acc(const QPDataR& q,int i,const real* v,real y,real sgn){
+WBC_FN real Arow_acc(const QPHotR& q,int i,const real* v,real y,real sgn){
     if(i<6){ for(int j=0;j<6;j++) y+=(sgn*q.Mbb[6*i+j])*v[j]; for(int f=0;f<12;f++) y-=(sgn*(q.cmask[f/3]*q.Jc[18*f+i]))*v[18+f]; return y; }
     if(i<18){ const int r=i-6; const real c=q.cmask[r/3]; if(c==real(0.0)) return y; for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return y; }
     if(i<34){ const int r=i-18,l=r>>2,k=r&3; const real c=q.cmask[l]; if(c==real(0.0)) return y; const real* f=v+18+3*l;
@@ -240,7 +235,7 @@ WBC_FN real Arow_acc(const QPDataR& q,int i,const real* v,real y,real sgn){
     { const int r=(i<58)?i-46:i-58; const real c=real(1.0)-q.cmask[r/3]; if(c!=real(0.0)) for(int j=0;j<18;j++) y+=(sgn*q.Jc[18*r+j])*v[j]; return (i<58)? y-sgn*v[30+r] : y+sgn*v[30+r]; }
 }
 // Acol_acc: y + sgn*(A' yv)_j for a 70-vector yv by constraint number (0 for inactive constraints), rows visited in ascending order
-WBC_FN real Acol_acc(const QPDataR& q,int j,const real* yv,real y,real sgn){
+WBC_FN real Acol_acc(const QPHotR& q,int j,const real* yv,real y,real sgn){
     if(j<18){
         if(j<6) for(int i=0;i<6;i++) y+=(sgn*q.Mbb[6*i+j])*yv[i];
         for(int r=0;r<12;r++) y+=(sgn*(q.cmask[r/3]*q.Jc[18*r+j]))*yv[6+r];
@@ -594,7 +589,7 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
         for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
         w.HZf[a*LD+k]=s; }
     WBC_SYNC();
-    real* col=w.ym;                                           // behind the 12 x LD block of (HZ)_force inside the scratch union
+    real* col=w.dx;                                           // the step direction is dead between performStep and the next determineStepDirection
     LANE_FOR(i,nZ){ real s=real(0.0);
         for(int ii=0;ii<nFR;ii++){ const int v=(int)w.FR[ii]; const real z=QQ(v,n);
             const real hk=(v>=18&&v<30)? w.HZf[(v-18)*LD+i] : ((v>=30)?WQP.rho:real(1.0))*QQ(v,i);
@@ -616,18 +611,28 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
     return QP_OK;
 }
 
+// Data shift of the gradient and of the (far) bounds on x, QProblemB::determineDataShift (QProblemB.cpp:1694-1750): delta = target - current.  They are
+// functions of the current g / lb / ub, the new gradient and the far bound, so they are re-evaluated where they are used instead of being kept in
+// 1 KB of shared memory (what decides whether an SM holds 5 or 6 robots); g, lb and ub only change in the update of performStep, which reads them last.
+WBC_DEV real far_rv(const QPCtx& c,int idx);
+WBC_DEV real shift_dg(const QPWork& w,int i){ const real gn=(i>=18&&i<30)?WQP.gf[i-18]:real(0.0); return gn-w.g[i]; }
+WBC_DEV real shift_dlb(const QPWork& w,const QPCtx& c,int i){ return -far_rv(c,i)-w.lb[i]; }
+WBC_DEV real shift_dub(const QPWork& w,const QPCtx& c,int i){ return far_rv(c,i)-w.ub[i]; }
+
 // ---------------------------------------------------------------- step direction
 // QProblem::determineStepDirection (QProblem.cpp:4637-4975), HST_POSDEF branch.
 // delta_* point to 42- / 70-long vectors by variable / constraint number.  Results: w.dx (free and fixed parts, by
 // variable number), w.dyAC (by AC position), w.dyFX (by variable number).
-WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,const real* dlbA,const real* dubA,const real* dlb,const real* dub,
+// `dg` != null: the given gradient shift and no shift of bounds / constraint bounds (linear-independence tests); `dg` == null: the homotopy's own data shift
+WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
                                   bool bCzero,bool bBzero){
     const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
     if(!prepare_T(w,c)) return QP_RET_STEPDIRECTION_FAILED_TQ;
     const unsigned ffm=force_mask(w,c,0), fxm=force_mask(w,c,1);
     // I) delta_xFX
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= (bBzero||!dlb)?real(0.0):((w.bstat[ii]==ST_LOWER)?dlb[ii]:dub[ii]); }
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=real(0.0); }
+    const bool shift=(dg==nullptr); const real* dlbA=shift?w.dlbA:nullptr; const real* dubA=shift?w.dubA:nullptr;
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= (bBzero||!shift)?real(0.0):((w.bstat[ii]==ST_LOWER)?shift_dlb(w,c,ii):shift_dub(w,c,ii)); }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=shift?shift_dg(w,ii):dg[ii]; w.dx[ii]=real(0.0); }
     LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=real(0.0); w.tB[i]= (bCzero||!dlbA)?real(0.0):((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
     WBC_SYNC();
     int nref=0;
@@ -670,12 +675,12 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,const real* 
         // residuals for the next refinement pass
         real rnrm=real(0.0);
         scatter_yAC(w,c,w.dyAC);
-        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; real t=dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; real t=shift?shift_dg(w,ii):dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
         // bA - A_FR dx_FR - A_FX dx_FX: the free columns first, then the fixed ones, each accumulated onto tempB (QProblem.cpp:4934-4935)
         mask_vars(w,c,w.dx,0);
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real t= (bCzero||!dlbA)?real(0.0):((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
             w.tB[i]=Arow_acc(WQP,ii,w.vm,t,-real(1.0)); }
-        if(!bBzero&&dlb){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-real(1.0)); }
+        if(!bBzero&&shift){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-real(1.0)); }
         LANE_FOR(i,nAC) rnrm=fmax(rnrm,fabs(w.tB[i]));
         rnrm=wbc_max(rnrm);
 #if !defined(__CUDACC__) && defined(WBC_QP_DBG)
@@ -689,7 +694,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,const real* 
     WBC_FLOPS((1.0+nref)*(2.0*nAC*nAC+4.0*nFR*nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+nref*(2.0*nFR*nFR+4.0*nAC*42.0)); (void)nref;
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; real t=dg[ii]; t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); w.dyFX[ii]=t; }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; real t=shift?shift_dg(w,ii):dg[ii]; t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); w.dyFX[ii]=t; }
     WBC_SYNC();
     WBC_DBG_VEC("dxFR",w.dx[(int)w.FR[i]],nFR); WBC_DBG_VEC("dyAC",w.dyAC[i],nAC); WBC_DBG_VEC("dyFX",w.dyFX[(int)w.FX[i]],nFX); WBC_DBG_VEC("dxFX",w.dx[(int)w.FX[i]],nFX);
     return QP_OK;
@@ -730,15 +735,14 @@ WBC_DEV real far_rv(const QPCtx& c,int idx){ const int nRamp=42+70; const real t
     return c.farbound*(real(1.0)+(real(1.0)-t)*OPT_ramp0+t*OPT_ramp1); }
 WBC_DEV real tgt_lb(const QPCtx& c,int i){ return -far_rv(c,i); }
 WBC_DEV real tgt_ub(const QPCtx& c,int i){ return far_rv(c,i); }
-WBC_DEV real tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),WQP.lbA[i]); }
-WBC_DEV real tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),WQP.ubA[i]); }
+WBC_DEV real tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),(real)c.qg->lbA[i]); }
+WBC_DEV real tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),(real)c.qg->ubA[i]); }
 // QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are WQP.gf (g_new) and the far-bounded data
 WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ real gn=(i>=18&&i<30)?WQP.gf[i-18]:real(0.0); w.dg[i]=gn-w.g[i]; const real rv=far_rv(c,i); w.dlb[i]=-rv-w.lb[i]; w.dub[i]=rv-w.ub[i]; }
-    LANE_FOR(i,70){ const real rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,WQP.lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,WQP.ubA[i])-w.ubA[i]; }
+    LANE_FOR(i,70){ const real rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,(real)c.qg->lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,(real)c.qg->ubA[i])-w.ubA[i]; }
     WBC_SYNC();
-    bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(w.dlb[ii])>QEPS||fabs(w.dub[ii])>QEPS) nz=true; }
+    bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(shift_dlb(w,c,ii))>QEPS||fabs(shift_dub(w,c,ii))>QEPS) nz=true; }
     bBzero=(wbc_ballot(nz)==0u);
     nz=false; LANE_FOR(i,c.nAC){ int ii=(int)w.AC[i]; if(fabs(w.dlbA[ii])>QEPS||fabs(w.dubA[ii])>QEPS) nz=true; }
     bCzero=(wbc_ballot(nz)==0u);
@@ -787,11 +791,11 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=false; }
     WBC_SYNC();
     // II.2 free variables
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.x[ii]-w.lb[ii],real(0.0)); w.den[i]=w.dlb[ii]-w.dx[ii]; }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.x[ii]-w.lb[ii],real(0.0)); w.den[i]=shift_dlb(w,c,ii)-w.dx[ii]; }
     performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=true; }
     WBC_SYNC();
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.ub[ii]-w.x[ii],real(0.0)); w.den[i]=w.dx[ii]-w.dub[ii]; }
+    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.ub[ii]-w.x[ii],real(0.0)); w.den[i]=w.dx[ii]-shift_dub(w,c,ii); }
     performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=true; }
     WBC_SYNC();
@@ -801,7 +805,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
         LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.x[ii]+=tau*w.dx[ii]; }
         LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.x[ii]+=tau*w.dx[ii]; w.y[ii]+=tau*w.dyFX[ii]; }
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]+=tau*w.dyAC[i]; }
-        LANE_FOR(i,42){ w.g[i]+=tau*w.dg[i]; w.lb[i]+=tau*w.dlb[i]; w.ub[i]+=tau*w.dub[i]; }
+        LANE_FOR(i,42){ const real rv=far_rv(c,i); w.g[i]+=tau*shift_dg(w,i); w.lb[i]+=tau*(-rv-w.lb[i]); w.ub[i]+=tau*(rv-w.ub[i]); }
         LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
         WBC_SYNC();
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real ax=Arow_acc(WQP,ii,w.x,real(0.0),real(1.0)); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
@@ -953,7 +957,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
             if(sureLI||sureLD){ WBC_FLOPS(3.0*(2.0*c.nAC*c.nAC+4.0*nFR*c.nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+2.0*(2.0*nFR*nFR+4.0*c.nAC*42.0)); return sureLI; }
 #endif
         }
-        int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
+        int rv=determineStepDirection(w,c,w.tmpv,false,false);
         if(rv!=QP_OK) return false;
         real weight=real(0.0), zero=real(0.0);
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
@@ -995,7 +999,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         }
         LANE_FOR(j,42) w.tmpv[j]=(j==number)?real(1.0):real(0.0);
         WBC_SYNC();
-        int rv=determineStepDirection(w,c,w.tmpv,nullptr,nullptr,nullptr,nullptr,false,false);
+        int rv=determineStepDirection(w,c,w.tmpv,false,false);
         if(rv!=QP_OK) return false;
         real weight=real(0.0), zero=real(0.0);
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
@@ -1218,7 +1222,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
         WBC_TIC(t0);
         bool bCzero,bBzero; determineDataShift(w,c,bCzero,bBzero);
         WBC_TOC(t0,0);
-        int rv=determineStepDirection(w,c,w.dg,w.dlbA,w.dubA,w.dlb,w.dub,bCzero,bBzero);
+        int rv=determineStepDirection(w,c,nullptr,bCzero,bBzero);
         WBC_TOC(t0,1);
         if(rv!=QP_OK){ nWSR=iter; return rv; }
         int BC_idx,BC_status; bool BC_isBound;
@@ -1245,7 +1249,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
 WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane; const int nWSR_max=nWSR; int nWSR_performed=0;
     real farbound=OPT_initialFarBounds;
-    { real m=real(0.0); LANE_FOR(i,70){ real u=WQP.ubA[i], l=WQP.lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
+    { real m=real(0.0); LANE_FOR(i,70){ real u=(real)c.qg->ubA[i], l=(real)c.qg->lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
     updateFarBounds(w,c,farbound);
     int rv;
     for(;;){
@@ -1259,7 +1263,7 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
         } else if(c.status==QPS_SOLVED){
             const real tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
             LANE_FOR(i,42){ if(fabs(tgt_lb(c,i)-w.x[i])<tol) na++; if(fabs(tgt_ub(c,i)-w.x[i])<tol) na++; }
-            LANE_FOR(i,70){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>WQP.lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<WQP.ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
+            LANE_FOR(i,70){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>(real)c.qg->lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<(real)c.qg->ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
             if(wbc_ballot(na>0)==0u) break;
             c.status=QPS_HOMOTOPYQPSOLVED;
             if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
