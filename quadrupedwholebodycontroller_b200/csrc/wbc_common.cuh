@@ -28,6 +28,17 @@
 #else
   WBC_DEV double wbc_lds(unsigned a){ double v; asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
 #endif
+  // Bulk asynchronous copies HBM -> shared memory (cp.async.bulk, SASS UBLKCP) completing on an mbarrier: one instruction moves a robot's
+  // rebuilt factorisation (Q and T, up to 21.7 KB) or its QP blocks (4.4 KB) while the warp goes on with other work, instead of staging
+  // 32-element rounds through registers with a memory round trip each.  Addresses and sizes are multiples of 16 bytes.
+  WBC_DEV void wbc_mbar_init(unsigned bar,unsigned count){ asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar),"r"(count) : "memory"); }
+  WBC_DEV void wbc_mbar_init_fence(){ asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  WBC_DEV void wbc_fence_proxy_async(){ asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }      // generic-proxy accesses of this thread before async-proxy writes
+  WBC_DEV void wbc_mbar_expect_tx(unsigned bar,unsigned bytes){ asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar),"r"(bytes) : "memory"); }
+  WBC_DEV void wbc_bulk_g2s(unsigned dst,const void* src,unsigned bytes,unsigned bar){
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" :: "r"(dst),"l"(__cvta_generic_to_global(src)),"r"(bytes),"r"(bar) : "memory"); }
+  WBC_DEV void wbc_mbar_wait(unsigned bar,unsigned parity){
+      unsigned ok; do{ asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar),"r"(parity) : "memory"); }while(!ok); }
   WBC_DEV unsigned wbc_ballot(bool p){ return __ballot_sync(0xffffffffu,p); }
   WBC_DEV double wbc_max(double v){ for(int o=16;o>0;o>>=1){ double t=__shfl_xor_sync(0xffffffffu,v,o); v = t>v?t:v; } return v; }
   WBC_DEV double wbc_bcast(double v,int src){ return __shfl_sync(0xffffffffu,v,src); }

@@ -140,20 +140,45 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
     extern __shared__ double smem[];
     QPWork& w=*reinterpret_cast<QPWork*>(reinterpret_cast<char*>(smem)+(size_t)(threadIdx.x>>5)*sizeof(QPWork));
     const int lane=threadIdx.x&31;
+    // two mbarriers per warp behind the workspaces: [0] the QP blocks (fp64 build), [1] the rebuilt Q / T of a hot-started robot
+    const unsigned barH=wbc_saddr(reinterpret_cast<char*>(smem)+(size_t)WBC_GANG*sizeof(QPWork)+16*(threadIdx.x>>5)), barQ=barH+8u;
+    unsigned parH=0u, parQ=0u;
+    if(lane==0){ wbc_mbar_init(barH,1u); wbc_mbar_init(barQ,1u); wbc_mbar_init_fence(); wbc_fence_proxy_async(); }
+    WBC_SYNC();
     for(;;){
         int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
         if(cohort){ if(gang_bar(r>=N)) break; }                      // the whole gang is out of work
         if(r>=N){ while(!gang_bar(1)){} if(cohort) continue; break; }     // keep the others' barriers complete until every warp is done
         const bool isFirst=first[r]!=0;
+        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
+        c.tqBar=0u; c.tqParity=0u;
+        // Bulk asynchronous copies first (cp.async.bulk -> mbarrier): the robot's QP blocks and, for a hot-started robot whose factorisation kernel 2a
+        // rebuilt, Q and T (21.7 KB in fp64) -- the latter is not needed before qp_hotstart has formed A x and the auxiliary gradient, so its
+        // flight time is hidden.  WBC_SYNC + proxy fence: every lane has finished with the previous robot's workspace before the async proxy writes it.
+        WBC_SYNC();
+        const bool bulkQT=(pre!=nullptr)&&!isFirst;
+        if(lane==0){
+            wbc_fence_proxy_async();
+#if !defined(WBC_FP32)
+            wbc_mbar_expect_tx(barH,(unsigned)(QPHOT_HEAD*sizeof(double)));
+            wbc_bulk_g2s(wbc_saddr(&w.qp),&qpd[r],(unsigned)(QPHOT_HEAD*sizeof(double)),barH);
+#endif
+            if(bulkQT){ constexpr unsigned QTB=(unsigned)(((42*LD+TRI42+1)*sizeof(real))/16*16);
+                wbc_mbar_expect_tx(barQ,QTB); wbc_bulk_g2s(wbc_saddr(w.Q),pre[r].Q,QTB,barQ); }
+        }
+        if(bulkQT){ c.tqBar=barQ; c.tqParity=parQ; parQ^=1u; }
         // all global loads of a robot are issued before the first shared store: the workspace is reached through a generic pointer, so the
         // compiler will not move a load above a store by itself and every 32-element round would cost a full memory round trip.
-        // Only the matrix blocks (head of QPData) and mu, rho, cmask (its last 6 elements) go to shared memory, converted to the solver's type.
+        // Only the matrix blocks (head of QPData) and mu, rho, cmask (its last 6 elements) go to shared memory, in the solver's type.
+#if defined(WBC_FP32)
         { const double* src=(const double*)&qpd[r]; real* dst=(real*)&w.qp; constexpr int K=(QPHOT_HEAD+6+31)/32; double t[K];
           #pragma unroll
           for(int k=0;k<K;k++){ const int i=lane+32*k; t[k]=(i<QPHOT_HEAD)?__ldg(src+i):((i<QPHOT_HEAD+6)?__ldg(src+(QPDATA_DOUBLES-6)+(i-QPHOT_HEAD)):0.0); }
           #pragma unroll
           for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPHOT_HEAD+6) dst[i]=(real)t[k]; } }
-        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
+#else
+        const double tailv=(lane<6)?__ldg((const double*)&qpd[r]+(QPDATA_DOUBLES-6)+lane):0.0;
+#endif
 #if defined(WBC_PROFILE)
         for(int k=0;k<8;k++) c.prof[k]=0;
         c.flops=0.0;
@@ -176,9 +201,14 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
             #pragma unroll
             for(int k=0;k<3;k++){ const int i=lane+32*k; if(i<70){ w.Ax_l[i]=ta[k]; w.Ax_u[i]=tb[k]; w.cstat[i]=sc[k]; } }
         }
+#if !defined(WBC_FP32)
+        if(lane<6) ((real*)&w.qp)[QPHOT_HEAD+lane]=tailv;
+        wbc_mbar_wait(barH,parH); parH^=1u;
+#endif
         WBC_SYNC();
         int nWSR=nWSRmax;
         const int rcv= isFirst? qp_init(w,c,nWSR) : qp_hotstart(w,c,nWSR,pre?&pre[r]:nullptr);
+        if(c.tqBar){ wbc_mbar_wait(c.tqBar,c.tqParity); c.tqBar=0u; }            // qp_hotstart returned before it needed Q / T: the copy must still land before the workspace is reused
         WBC_SYNC();
         // QProblemB::getPrimalSolution (QProblemB.cpp:774-793) hands x out only in these three states; otherwise the caller's qpSolution_ keeps
         // its previous value (wbc.cpp:536) -- and so does out.x.  The solver's own iterate S.x is stored regardless (it IS the SQProblem member).
@@ -374,7 +404,7 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
        ||cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->updBlocksPerSM,wbc_update_state_kernel,32,h->updSmem)!=cudaSuccess||h->updBlocksPerSM<1){
         h->err=std::string("update-state kernel geometry: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     // solver launch geometry: one warp per CTA, as many CTAs per SM as shared memory allows
-    h->qpSmem=sizeof(QPWork)*WBC_GANG;
+    h->qpSmem=sizeof(QPWork)*WBC_GANG+16*WBC_GANG;                                  // + two mbarriers per warp
     if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,WBC_QP_THREADS,h->qpSmem)!=cudaSuccess||nb<1){

@@ -139,7 +139,7 @@ struct QPState {
 struct QPWork {
     real Q[42*LD];
     real RT[TRI42+1];                         // packed R and T (see RR / TT)
-    signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70], pad_[2];
+    signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70], pad_[10];     // 416 B: Q, RT, the scratch block and qp all start on 16-byte boundaries (bulk copies)
     // phase-local scratch, overlaid: Givens / row vectors + {ratio tests | step-direction temporaries} + LI-exchange vectors,
     // all of it reused as the 12 x nZ block (HZ)_force by the projected Cholesky (which runs when none of them is live)
     union {
@@ -158,17 +158,19 @@ struct QPWork {
     real dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
     real rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
 };
-constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(real)+408+5*42*sizeof(real);
+constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(real)+416+5*42*sizeof(real);
 static_assert(offsetof(QPWork,tmpv)+5*42*sizeof(real)==QPWORK_TQ_BYTES,"layout of the TQ-rebuild prefix");
+static_assert(sizeof(QPWork)%16==0&&(sizeof(real)==4||offsetof(QPWork,qp)%16==0)&&offsetof(QPWork,RT)==42*LD*sizeof(real),"16-byte layout the bulk copies of the solve kernel rely on");
 
 // what the warm-start TQ rebuild hands to the solve kernel (HBM): Q = [Z Y], the nAC rows of T, the index lists
-struct QPPre {
+struct alignas(16) QPPre {
     real Q[42*LD];
-    real T[TRI42+1];                          // only the first tri(nAC) entries are written / read
+    real T[TRI42+1];                          // only the first tri(nAC) entries are written; Q and T have the layout of QPWork's Q and RT (one bulk copy brings both)
     signed char AC[70], IAC[70], cstat[70], posAC[70];
     int nAC, nIAC;
     double flops;
 };
+static_assert(sizeof(QPPre)%16==0&&offsetof(QPPre,T)==42*LD*sizeof(real),"QPPre: Q and T contiguous like QPWork's Q and RT, records 16-byte aligned");
 
 // scalar solver state, replicated in every lane
 struct QPCtx {
@@ -180,6 +182,7 @@ struct QPCtx {
     real farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
     real tau;
     const QPData* qg;    // this robot's compact QP in HBM (fp64): new lbA / ubA targets, bias_j
+    unsigned tqBar, tqParity;   // != 0: a bulk copy of the rebuilt Q / T into w.Q, w.RT is in flight on this mbarrier (shared-space address) with this phase parity
 #if defined(WBC_PROFILE)
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
     double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
@@ -1333,6 +1336,14 @@ WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
     #pragma unroll
     for(int k=0;k<3;k++){ const int i=lane+WBC_NL*k; const bool in=i<70; l0[k]=in?p.AC[i]:(signed char)0; l1[k]=in?p.IAC[i]:(signed char)0; l2[k]=in?p.cstat[i]:(signed char)0; l3[k]=in?p.posAC[i]:(signed char)0; }
 #endif
+#if WBC_NL>1
+    if(c.tqBar){                                                               // Q and T were requested by a bulk copy when the robot was fetched (wbc_solve_qp_kernel): wait for it
+        wbc_mbar_wait(c.tqBar,c.tqParity); c.tqBar=0u;
+        constexpr int QT=42*LD+TRI42+1, QT16=(int)((QT*sizeof(real))/16*16/sizeof(real));     // fp32: the last two elements do not fill a 16-byte unit
+        if(QT16<QT&&lane<QT-QT16&&QT16+lane-42*LD<nT) w.RT[QT16+lane-42*LD]=p.T[QT16+lane-42*LD];
+    } else
+#endif
+    {
     constexpr int KB=19;                                                        // 3 batches of 19 x 32 doubles cover Q (1806)
     #pragma unroll 1
     for(int base=0;base<42*LD;base+=KB*WBC_NL){
@@ -1349,6 +1360,7 @@ WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
         for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; t[k]=(i<nT)?p.T[i]:real(0.0); }
         #pragma unroll
         for(int k=0;k<KB;k++){ const int i=base+lane+WBC_NL*k; if(i<nT) w.RT[i]=t[k]; }
+    }
     }
 #if WBC_NL>1
     #pragma unroll
