@@ -99,7 +99,7 @@ int wbc_get_duals(wbc_handle* h, double* y);
 int wbc_warm_start_split(const wbc_handle* h);
 /* Explicit switches for tests and measurements; every setting gives bit-identical results.  Keys: "warm_start_split" (0 = rebuild the
  * TQ factorisation inside the solve kernel), "cohort" (-1 auto, 0 never, 1 always: gang scheduling of the solve kernel),
- * "setup_canary" (1 = guard the workspace prefix of the warm-start kernel). */
+ * "setup_canary" (1 = guard the workspace prefix of the warm-start kernel), "rollout_graph" (0 = wbc_rollout never replays a CUDA graph). */
 int wbc_set_option(wbc_handle* h, const char* key, int value);
 
 /* Test / inspection hook: the dense QP of robot i as the reference would hand it to qpOASES (row-major H[42*42], g[42],
@@ -145,7 +145,9 @@ int wbc_plant_enable(wbc_handle* h);
 int wbc_plant_step(wbc_handle* h);
 /* `ticks` control ticks of the closed loop (src/whole_body_controller.cpp:639-673 with the planner node beside it):
  * every `planner_every`-th tick (4 = 400 Hz / 100 Hz) one planner period, then updateState, solveQP, computeJointTorques, plant step.
- * Asynchronous on the stream.  Needs wbc_planner_create and wbc_plant_enable. */
+ * Asynchronous on the stream.  Needs wbc_planner_create and wbc_plant_enable.  In the steady state (every robot hot-started) a whole planner
+ * period is replayed as ONE CUDA graph launch (captured on first use; wbc_set_option "rollout_graph" 0 switches it off): same kernels in
+ * the same order, same results; the per-kernel timers of wbc_last_kernel_ms are only updated by ticks issued as plain launches. */
 int wbc_rollout(wbc_handle* h, int ticks, int planner_every);
 /* per-robot rollout statistics since the last reset: control ticks, ticks whose solve did not return 0, sum and max of nWSR */
 int wbc_rollout_stats(wbc_handle* h, int* ticks, int* failed_ticks, int* nwsr_sum, int* nwsr_max, int reset);

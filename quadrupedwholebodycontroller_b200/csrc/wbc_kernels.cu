@@ -330,6 +330,8 @@ struct wbc_handle {
     int smCount=0, qpBlocksPerSM=1, cohortMode=-1, updBlocksPerSM=1; size_t qpSmem=0, updSmem=0;
     double* duals=nullptr;
     QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false; size_t setupPad=0;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
+    // closed-loop rollout as a CUDA graph: one planner period (planner tick + graphPeriod control ticks incl. the plant) captured once, replayed per period
+    cudaGraph_t graph=nullptr; cudaGraphExec_t graphExec=nullptr; int graphPeriod=0; long long graphLaunches=0; bool capturing=false, useGraph=true;
     long long launches=0;
     std::string err;
 };
@@ -422,10 +424,12 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     return WBC_OK;
 }
 
+static void drop_graph(wbc_handle* h);
 extern "C" int wbc_destroy(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     cudaSetDevice(h->device);
     if(h->stream) cudaStreamSynchronize(h->stream);
+    drop_graph(h);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
                   h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre,h->duals,h->legs};
     for(void* p:ptrs) if(p) cudaFree(p);
@@ -473,12 +477,12 @@ extern "C" int wbc_update_state(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
     int grid=h->smCount*h->updBlocksPerSM; if(grid>(h->N+UPD_GROUPS-1)/UPD_GROUPS) grid=(h->N+UPD_GROUPS-1)/UPD_GROUPS;
-    CK(cudaEventRecord(h->ev[0],h->stream));
+    if(!h->capturing) CK(cudaEventRecord(h->ev[0],h->stream));
     wbc_rbd_legs_kernel<<<(4*h->N+127)/128,128,0,h->stream>>>(h->N,batch_in(h),h->legs);
     h->launches++; CK(cudaGetLastError());
     wbc_update_state_kernel<<<grid,32,h->updSmem,h->stream>>>(h->N,h->devParams,batch_in(h),h->legs,h->ctrl,h->qpd,h->first,h->com,h->plantAux);
     h->launches++; CK(cudaGetLastError());
-    CK(cudaEventRecord(h->ev[1],h->stream));
+    if(!h->capturing) CK(cudaEventRecord(h->ev[1],h->stream));
     return WBC_OK;
 }
 extern "C" int wbc_solve_qp(wbc_handle* h){
@@ -489,7 +493,7 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     // cohort scheduling only when every robot of the batch cold-starts (nothing solved since the last full reset)
     const int cohort= h->cohortMode<0 ? (h->maybeWarm?0:1) : h->cohortMode;
     CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
-    CK(cudaEventRecord(h->ev[1],h->stream));
+    if(!h->capturing) CK(cudaEventRecord(h->ev[1],h->stream));
     bool two=h->split&&h->maybeWarm;
     if(two&&!h->pre&&cudaMalloc(&h->pre,sizeof(QPPre)*(size_t)h->N)!=cudaSuccess){      // 22 KB per robot; without it the solve kernel rebuilds the factorisation itself
         cudaGetLastError(); h->pre=nullptr; h->split=false; two=false;
@@ -501,14 +505,14 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
     wbc_solve_qp_kernel<<<grid,WBC_QP_THREADS,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,cohort,two?h->pre:nullptr,h->stats);
     h->launches++; CK(cudaGetLastError());
     h->maybeWarm=true;
-    CK(cudaEventRecord(h->ev[2],h->stream));
+    if(!h->capturing) CK(cudaEventRecord(h->ev[2],h->stream));
     return WBC_OK;
 }
 extern "C" int wbc_compute_joint_torques(wbc_handle* h){
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
     // tau and f* were written by the epilogue of wbc_solve_qp_kernel from the solution in shared memory; nothing is left to launch
-    CK(cudaEventRecord(h->ev[3],h->stream));
+    if(!h->capturing) CK(cudaEventRecord(h->ev[3],h->stream));
     return WBC_OK;
 }
 extern "C" int wbc_step(wbc_handle* h){ int r; if((r=wbc_update_state(h))||(r=wbc_solve_qp(h))||(r=wbc_compute_joint_torques(h))) return r; return WBC_OK; }
@@ -566,6 +570,7 @@ extern "C" int wbc_planner_reset(wbc_handle* h,int first,int count){
     return WBC_OK;
 }
 extern "C" int wbc_planner_create(wbc_handle* h,const wbc_planner_params* p){
+    if(h) drop_graph(h);
     if(!h) return WBC_ERR_ARG;
     CK(cudaSetDevice(h->device));
     wbc_planner_params d; if(p) d=*p; else wbc_planner_default_params(&d);
@@ -633,14 +638,50 @@ extern "C" int wbc_plant_step(wbc_handle* h){
     h->launches++; CK(cudaGetLastError());
     return WBC_OK;
 }
+static void drop_graph(wbc_handle* h){
+    if(h->graphExec){ cudaGraphExecDestroy(h->graphExec); h->graphExec=nullptr; }
+    if(h->graph){ cudaGraphDestroy(h->graph); h->graph=nullptr; }
+    h->graphPeriod=0;
+}
+static int rollout_tick(wbc_handle* h,int planner_every){
+    int r;
+    if(h->tick%planner_every==0) if((r=wbc_planner_tick(h))) return r;
+    if((r=wbc_step(h))||(r=wbc_plant_step(h))) return r;
+    h->tick++;
+    return WBC_OK;
+}
+// One planner period of the steady-state closed loop (every robot hot-started, kernel 2a's workspace allocated) is the same 1 + 6 x planner_every
+// stream operations every time: it is captured into a CUDA graph once and replayed, so a small batch (<= 888 robots: 0.2 ms ticks) pays one graph
+// launch per period instead of 25 kernel launches.  Results are those of the plain loop (same kernels, same order); the per-kernel event timers
+// (wbc_last_kernel_ms) are not updated by replayed periods.
+static int build_rollout_graph(wbc_handle* h,int planner_every){
+    drop_graph(h);
+    const long long tick0=h->tick, l0=h->launches;
+    if(cudaStreamBeginCapture(h->stream,cudaStreamCaptureModeThreadLocal)!=cudaSuccess){ cudaGetLastError(); return WBC_ERR_CUDA; }
+    h->capturing=true; int r=WBC_OK;
+    for(int t=0;t<planner_every&&r==WBC_OK;t++) r=rollout_tick(h,planner_every);
+    h->capturing=false;
+    cudaGraph_t g=nullptr; const cudaError_t e=cudaStreamEndCapture(h->stream,&g);
+    h->tick=tick0; h->graphLaunches=h->launches-l0; h->launches=l0;                  // nothing ran yet
+    if(r!=WBC_OK||e!=cudaSuccess||!g){ if(g) cudaGraphDestroy(g); cudaGetLastError(); return r!=WBC_OK?r:WBC_ERR_CUDA; }
+    h->graph=g;
+    if(cudaGraphInstantiate(&h->graphExec,h->graph,0)!=cudaSuccess){ cudaGetLastError(); drop_graph(h); return WBC_ERR_CUDA; }
+    h->graphPeriod=planner_every;
+    return WBC_OK;
+}
 extern "C" int wbc_rollout(wbc_handle* h,int ticks,int planner_every){
     if(!h) return WBC_ERR_ARG;
     if(ticks<0||planner_every<1||!h->plantAux||!h->planner){ h->err="wbc_rollout: needs wbc_planner_create, wbc_plant_enable, ticks >= 0 and planner_every >= 1"; return WBC_ERR_ARG; }
-    int r;
-    for(int t=0;t<ticks;t++){
-        if(h->tick%planner_every==0) if((r=wbc_planner_tick(h))) return r;
-        if((r=wbc_step(h))||(r=wbc_plant_step(h))) return r;
-        h->tick++;
+    CK(cudaSetDevice(h->device));
+    int r, t=0;
+    while(t<ticks){
+        const bool steady=h->useGraph&&h->maybeWarm&&h->split&&h->pre&&h->cohortMode<=0&&!h->prof&&h->tick%planner_every==0&&ticks-t>=planner_every;
+        if(steady&&(h->graphExec==nullptr||h->graphPeriod!=planner_every)){
+            if(build_rollout_graph(h,planner_every)!=WBC_OK){ h->useGraph=false; h->err="wbc_rollout: CUDA graph capture failed, continuing with plain launches"; continue; } }
+        if(steady){
+            CK(cudaGraphLaunch(h->graphExec,h->stream));
+            h->tick+=planner_every; t+=planner_every; h->launches+=h->graphLaunches;
+        } else { if((r=rollout_tick(h,planner_every))) return r; t++; }
     }
     return WBC_OK;
 }
@@ -675,6 +716,8 @@ extern "C" int wbc_warm_start_split(const wbc_handle* h){ return (h&&h->split)?1
 extern "C" int wbc_set_option(wbc_handle* h,const char* key,int value){
     if(!h||!key) return WBC_ERR_ARG;
     const std::string k(key);
+    drop_graph(h);                                                            // every switch below changes what a captured period would launch
+    if(k=="rollout_graph"){ h->useGraph=value!=0; return WBC_OK; }            // 0: wbc_rollout issues plain launches every tick
     if(k=="warm_start_split"){ h->split=value!=0; return WBC_OK; }            // 0: rebuild the TQ factorisation inside the solve kernel
     if(k=="cohort"){ h->cohortMode=value; return WBC_OK; }                    // -1 auto, 0 never, 1 always (gang scheduling of kernel 2)
     if(k=="setup_canary"){                                                    // guard the prefix allocation of kernel 2a (tests)

@@ -226,3 +226,24 @@ def test_plant_invariants_stance_feet_and_power_balance(wbc, orc, wl):
           f"power-balance error {p400:.3e} W (scale {s400:.3e}) at 400 Hz, {p1600:.3e} W (scale {s1600:.3e}) at 1600 Hz")
     assert d400 < 1e-3 and abs(d1600 - d400) < 0.1 * d400, (d400, d1600)
     assert p400 < 0.25 * s400 and p1600 < 0.6 * p400, (p400, s400, p1600, s1600)             # the energy rate matches tau . qdot to first order in dt
+
+
+def test_rollout_graph_replay_equals_plain_launches(wbc, wl):
+    """wbc_rollout replays a captured planner period (CUDA graph) once every robot is hot-started: outputs, states, per-robot statistics and
+    the launch count must be those of the plain per-tick launches -- incl. a tick count that is not a multiple of the period and a call that
+    starts in the middle of a period."""
+    n = 600
+    st, ref, cmd = wl.rollout_start(n)
+
+    def run(graph):
+        ctl = wbc.WholeBodyController(n); ctl.plannerCreate(); ctl.plantEnable(); ctl.setOption("rollout_graph", graph)
+        ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.plannerSetCmdVel(cmd[0].copy(), cmd[1].copy(), cmd[2].copy())
+        ctl.rollout(3); ctl.rollout(58); ctl.rollout(40)          # 101 ticks: cold tick, part periods, 24 whole periods
+        out = ctl.getOutputs(), ctl.getState(), ctl.rolloutStats(), ctl.launchCount()
+        ctl.close()
+        return out
+    o0, s0, t0, l0 = run(0)
+    o1, s1, t1, l1 = run(1)
+    assert all(np.array_equal(o0[k], o1[k]) for k in o0) and all(np.array_equal(s0[k], s1[k]) for k in s0)
+    assert all(np.array_equal(t0[k], t1[k]) for k in t0) and (t1["ticks"] == 101).all()
+    assert l0 == l1
