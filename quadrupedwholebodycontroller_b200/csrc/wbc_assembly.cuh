@@ -38,6 +38,14 @@ WBC_DEV void eul_rpy(const double* R,double* rpy){
 // ones, nu_dot = T^-1 (a - Tdot nu):  d = p_com - p_base (3), B = Mbb^-1 Mbj (72), Tdot_top nu (6).
 WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,CtrlState& st,QPData& out,int lane,int switching,int first,double* plant,int N){
     const double* R=s.Rwb;
+    // the previous tick's T (finite difference of D5) is requested now and used ~100 lines further down: inside the loop that consumes it every load
+    // would sit behind the shared-memory store of the trip before (the compiler cannot prove the two do not alias) and cost a memory round trip per trip
+    constexpr int KT=(108+WBC_ASM_NL-1)/WBC_ASM_NL; double told_[KT];
+    #pragma unroll
+    for(int k=0;k<KT;k++){ const int e=lane+WBC_ASM_NL*k; told_[k]=(e<108&&!first)?st.Told[e]:0.0; }
+    constexpr int KI=(6+WBC_ASM_NL-1)/WBC_ASM_NL; double integ_[KI];
+    #pragma unroll
+    for(int k=0;k<KI;k++){ const int i=lane+WBC_ASM_NL*k; integ_[k]=(i<6&&!first)?st.integral[i]:0.0; }
     // ---- D1: base totals (locked inertia, CoM, momentum, gravity-free base wrench) ----
     if(lane==0){
         double m=mc_.mass[0], mcb[3]={mc_.mcom[0],mc_.mcom[1],mc_.mcom[2]}, I[9]; for(int i=0;i<9;i++) I[i]=mc_.inertia[i];
@@ -143,9 +151,10 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     }
     WBC_SYNC();
     // Tdot^-1 (top rows) for the NEXT tick = -X [Tdot_b X, Tdot_j - Tdot_b B]   (wbc.cpp:293)
-    ASM_FOR(e,108){ int i=e/18,j=e%18; double v=0;
-        if(!switching){ double told=first?((i==j)?1.0:0.0):st.Told[e]; v=(s.Ttop[e]-told)/timeStep; }
-        s.Tdot[e]=v; }
+    #pragma unroll
+    for(int k=0;k<KT;k++){ const int e=lane+WBC_ASM_NL*k; if(e<108){ int i=e/18,j=e%18; double v=0;
+        if(!switching){ double told=first?((i==j)?1.0:0.0):told_[k]; v=(s.Ttop[e]-told)/timeStep; }
+        s.Tdot[e]=v; } }
     WBC_SYNC();
     if(plant){
         ASM_FOR(i,3) plant[(size_t)i*N]=s.d[i];
@@ -160,14 +169,15 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     ASM_FOR(e,108){ int i=e/18,j=e%18; double v=0; for(int k=0;k<6;k++) v+=s.X[6*i+k]*s.Y[18*k+j]; st.TdotInv[e]=-v; st.Told[e]=s.Ttop[e]; }
     ASM_FOR(e,216){ const double c=s.cmask[e/54]; double jc=out.Jc[e]; st.Jstold[e]=c*jc; st.Jswold[e]=(1.0-c)*jc; }
     // ---- D6: desired wrench (wbc.cpp:426-445), swing command (wbc.cpp:447-464) ----
-    ASM_FOR(i,6){
+    #pragma unroll
+    for(int kk=0;kk<KI;kk++){ const int i=lane+WBC_ASM_NL*kk; if(i<6){
         const double kp=(i==2)?P.kpValueZ:P.kpValue;
         double mcb=0; for(int k=0;k<6;k++) mcb+=out.Mbb[6*i+k]*s.acc_d[k];     // needs out.Mbb: written before the D3 barrier
         const double gw=(i==2)?mc_.total_mass*GRAV:0.0;
-        const double integ=first?0.0:st.integral[i];
+        const double integ=integ_[kk];                                       // first tick: 0
         s.W[i]=-kp*(s.pose[i]-s.pose_d[i])-P.kdValue*(s.vcom[i]-s.vel_d[i])-P.kiValue*integ+gw+mcb;
         st.integral[i]=integ+(s.pose[i]-s.pose_d[i])/P.loopRate;
-    }
+    } }
     ASM_FOR(i,12){
         double r=s.swa[i]+P.kdSwingValue*(s.swv[i]-s.footvw[i])+P.kpSwingValue*(s.swp[i]-s.footpw[i]);
         s.rcmd[i]=r*(1.0-s.cmask[i/3]);

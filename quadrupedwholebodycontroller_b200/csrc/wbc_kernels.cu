@@ -75,13 +75,33 @@ __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,B
     WBC_SYNC();
     for(int r0=blockIdx.x*UPD_GROUPS;r0<N;r0+=gridDim.x*UPD_GROUPS){
         const int r=(r0+grp<N)?r0+grp:N-1;
-        ASM_FOR(k,12){ s.q[k]=in.q[k*N+r]; s.qd[k]=in.qd[k*N+r]; s.swp[k]=in.swp[k*N+r]; s.swv[k]=in.swv[k*N+r]; s.swa[k]=in.swa[k*N+r]; }
-        ASM_FOR(k,6){ s.twist[k]=in.twist[k*N+r]; s.pose_d[k]=in.pose[k*N+r]; s.vel_d[k]=in.vel[k*N+r]; s.acc_d[k]=in.acc[k*N+r]; }
-        ASM_FOR(k,3) s.pb[k]=in.pos[k*N+r];
-        ASM_FOR(k,4) s.cmask[k]=in.contacts[k*N+r]?1.0:0.0;
-        if(lane==0){ double qu[4]={in.quat[r],in.quat[N+r],in.quat[2*N+r],in.quat[3*N+r]}; quat_to_R(qu,s.Rwb); }
-        { const double* src=(const double*)&legs[(size_t)r*4];                            // leg-phase results of kernel 1a -> the scratch fields the dense phase reads
-          ASM_FOR(i,4*LEGOUT_DOUBLES){ const int l=i/LEGOUT_DOUBLES, o=i-l*LEGOUT_DOUBLES; const double v=src[i];
+        // the controller state of this robot is read half-way through the assembly: ask L2 for it now
+        if(lane==0) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(__cvta_generic_to_global(&st[r])),"r"((unsigned)sizeof(CtrlState)) : "memory");
+        // every global load of the robot is issued before the first shared store (the scratch is reached through a generic pointer: a load behind a
+        // store stays behind it, and each 16-element round would cost its own memory round trip)
+        constexpr int K12=(12+WBC_ASM_NL-1)/WBC_ASM_NL, K6=(6+WBC_ASM_NL-1)/WBC_ASM_NL, KL=(4*LEGOUT_DOUBLES+WBC_ASM_NL-1)/WBC_ASM_NL;
+        double v12[5][K12], v6[4][K6], vpb=0.0, q0=1.0, q1=0.0, q2=0.0, q3=0.0, tl[KL]; unsigned char vc=0;
+        #pragma unroll
+        for(int j=0;j<K12;j++){ const int k=lane+WBC_ASM_NL*j; const bool in_=k<12; const size_t o=(size_t)(in_?k:0)*N+r;
+            v12[0][j]=in_?in.q[o]:0.0; v12[1][j]=in_?in.qd[o]:0.0; v12[2][j]=in_?in.swp[o]:0.0; v12[3][j]=in_?in.swv[o]:0.0; v12[4][j]=in_?in.swa[o]:0.0; }
+        #pragma unroll
+        for(int j=0;j<K6;j++){ const int k=lane+WBC_ASM_NL*j; const bool in_=k<6; const size_t o=(size_t)(in_?k:0)*N+r;
+            v6[0][j]=in_?in.twist[o]:0.0; v6[1][j]=in_?in.pose[o]:0.0; v6[2][j]=in_?in.vel[o]:0.0; v6[3][j]=in_?in.acc[o]:0.0; }
+        if(lane<3) vpb=in.pos[(size_t)lane*N+r];
+        if(lane<4) vc=in.contacts[(size_t)lane*N+r];
+        if(lane==0){ q0=in.quat[r]; q1=in.quat[N+r]; q2=in.quat[2*N+r]; q3=in.quat[3*N+r]; }
+        { const double* src=(const double*)&legs[(size_t)r*4];                            // leg-phase results of kernel 1a
+          #pragma unroll
+          for(int j=0;j<KL;j++){ const int i=lane+WBC_ASM_NL*j; tl[j]=(i<4*LEGOUT_DOUBLES)?src[i]:0.0; } }
+        #pragma unroll
+        for(int j=0;j<K12;j++){ const int k=lane+WBC_ASM_NL*j; if(k<12){ s.q[k]=v12[0][j]; s.qd[k]=v12[1][j]; s.swp[k]=v12[2][j]; s.swv[k]=v12[3][j]; s.swa[k]=v12[4][j]; } }
+        #pragma unroll
+        for(int j=0;j<K6;j++){ const int k=lane+WBC_ASM_NL*j; if(k<6){ s.twist[k]=v6[0][j]; s.pose_d[k]=v6[1][j]; s.vel_d[k]=v6[2][j]; s.acc_d[k]=v6[3][j]; } }
+        if(lane<3) s.pb[lane]=vpb;
+        if(lane<4) s.cmask[lane]=vc?1.0:0.0;
+        if(lane==0){ double qu[4]={q0,q1,q2,q3}; quat_to_R(qu,s.Rwb); }
+        #pragma unroll
+        for(int j=0;j<KL;j++){ const int i=lane+WBC_ASM_NL*j; if(i<4*LEGOUT_DOUBLES){ const int l=i/LEGOUT_DOUBLES, o=i-l*LEGOUT_DOUBLES; const double v=tl[j];       // -> the scratch fields the dense phase reads
               if(o<13) s.crb[l][o]=v; else if(o<31) (&s.Fraw[3*l][0])[o-13]=v; else if(o<40) s.Hleg[l][o-31]=v; else if(o<43) s.plin[l][o-40]=v;
               else if(o<49) s.fb[l][o-43]=v; else if(o<52) s.tauC[3*l+o-49]=v; else if(o<55) s.footp[l][o-52]=v; else if(o<58) s.footv[l][o-55]=v;
               else (&s.jcol[3*l][0])[o-58]=v; } }
