@@ -2,6 +2,7 @@
 library (symbol offsets from `cuobjdump -elf`): instructions executed, stall samples and the top stall reasons per function."""
 import csv, collections, subprocess, sys, re, os
 rep_csv, so, kernel = sys.argv[1], sys.argv[2], sys.argv[3]
+which = int(sys.argv[4]) if len(sys.argv) > 4 else 1      # 1-based index of the kernel inside the report
 elf = subprocess.run(["cuobjdump", "-elf", so], capture_output=True, text=True).stdout
 syms = []
 for line in elf.splitlines():
@@ -19,7 +20,7 @@ out = collections.defaultdict(lambda: collections.Counter()); base = None; nk = 
 for r in rows:
     if r and r[0] == "Kernel Name":
         nk += 1; base = None; continue
-    if nk != 1 or not r or not r[0].startswith("0x"): 
+    if nk != which or not r or not r[0].startswith("0x"): 
         if r and r[0] == "Address": hdr = r; ix = {h: i for i, h in enumerate(hdr)}
         continue
     a = int(r[0], 16)

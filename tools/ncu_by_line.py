@@ -4,6 +4,7 @@ usage: ncu_by_line.py sass.csv lib.so kernel_substring [topN]"""
 import csv, collections, subprocess, sys, re, os, tempfile, glob
 rep_csv, so, kernel = sys.argv[1], sys.argv[2], sys.argv[3]
 topn = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+which = int(sys.argv[5]) if len(sys.argv) > 5 else 1      # 1-based index of the kernel header inside the report page
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, capture_output=True)
 cubin = glob.glob(os.path.join(tmp, "*.cubin"))[0]
@@ -24,7 +25,7 @@ agg = collections.defaultdict(lambda: [0, 0]); base = None; nk = 0
 for r in rows:
     if r and r[0] == "Kernel Name": nk += 1; base = None; continue
     if r and r[0] == "Address": hdr = r; ix = {h: i for i, h in enumerate(hdr)}; continue
-    if nk != 1 or not r or not r[0].startswith("0x"): continue
+    if nk != which or not r or not r[0].startswith("0x"): continue
     a = int(r[0], 16)
     if base is None: base = a
     k = line_of.get(a - base, ("?", 0)); agg[k][0] += int(r[ix["Instructions Executed"]]); agg[k][1] += int(r[ix["# Samples"]])
