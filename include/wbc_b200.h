@@ -82,6 +82,17 @@ int wbc_set_reference(wbc_handle* h, const double* pose, const double* vel, cons
 int wbc_update_state(wbc_handle* h);
 int wbc_solve_qp(wbc_handle* h);
 int wbc_compute_joint_torques(wbc_handle* h);   /* the recovery itself runs as the epilogue of the solve kernel (x is still on chip); this call orders after it */
+/* No counterpart in the reference.  solveQP() for callers that must not allocate (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc): wbc_solve_qp allocates its 22 KB-per-robot warm-start hand-over buffer
+ * with cudaMalloc at the first hot-started tick; this variant launches the same kernels with that scratch (and the work counter) in a file-scope
+ * static __device__ array of the library, and calls no cudaMalloc / cudaFree / allocating routine.  Limit: handles of at most
+ * WBC_STATIC_MAX_ROBOTS = 1024 robots (22.5 MB held by every GPU that loads the library until exit); a larger handle is refused with
+ * WBC_ERR_ARG and a text in wbc_last_error.  Inputs and outputs are the caller's, exactly as for wbc_solve_qp (wbc_set_state / wbc_set_reference
+ * + wbc_update_state before, wbc_get_outputs after -- none of them allocates); results are bit-identical to wbc_solve_qp.  ALL calls on one
+ * device share the array, which keeps the last call's contents (the call clears the one word that must start at zero): calls that overlap on
+ * the GPU -- two handles on different streams of one device -- race; serialise them. */
+#define WBC_STATIC_MAX_ROBOTS 1024
+int wbc_solve_qp_static(wbc_handle* h);
 int wbc_step(wbc_handle* h);                                     /* the three calls above, asynchronous on the stream */
 int wbc_synchronize(wbc_handle* h);
 

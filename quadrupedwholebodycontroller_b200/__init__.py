@@ -15,7 +15,7 @@ NUM_JOINTS, NUM_LEGS, QP_NV, QP_NC = 12, 4, 42, 70          # whole_body_control
 _libs = {}
 
 EXPORTS = ["wbc_default_params", "wbc_create", "wbc_destroy", "wbc_reset", "wbc_set_state", "wbc_set_reference", "wbc_update_state",
-           "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
+           "wbc_solve_qp", "wbc_solve_qp_static", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize", "wbc_get_outputs", "wbc_get_dense_qp",
            "wbc_planner_default_params", "wbc_planner_create", "wbc_planner_reset", "wbc_planner_set_cmd_vel", "wbc_planner_tick", "wbc_get_reference",
            "wbc_get_state", "wbc_plant_enable", "wbc_plant_step", "wbc_rollout", "wbc_rollout_stats", "wbc_num_robots", "wbc_launch_count", "wbc_last_kernel_ms", "wbc_profile", "wbc_measure_fp64_peak", "wbc_last_error", "wbc_get_duals", "wbc_warm_start_split", "wbc_set_option", "wbc_debug_counters", "wbc_measure_smem_peak",
            "wbc_multi_create", "wbc_multi_destroy", "wbc_multi_num_devices", "wbc_multi_num_robots", "wbc_multi_shard", "wbc_multi_handle", "wbc_multi_reset", "wbc_multi_set_state",
@@ -44,7 +44,7 @@ def load_library(profiling=False, exact=False, fp32=False):
                                "The controller has no CPU fallback.")
         lib = C.CDLL(path)
         lib.wbc_create.argtypes = [C.c_int, C.c_int, C.POINTER(WbcParams), C.c_void_p, C.POINTER(C.c_void_p)]
-        for name in ("wbc_destroy", "wbc_update_state", "wbc_solve_qp", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize"):
+        for name in ("wbc_destroy", "wbc_update_state", "wbc_solve_qp", "wbc_solve_qp_static", "wbc_compute_joint_torques", "wbc_step", "wbc_synchronize"):
             getattr(lib, name).argtypes = [C.c_void_p]
         lib.wbc_reset.argtypes = [C.c_void_p, C.c_int, C.c_int]
         lib.wbc_set_state.argtypes = [C.c_void_p] + [C.c_void_p] * 5
@@ -150,6 +150,10 @@ class WholeBodyController:
 
     def solveQP(self):
         self._ck(self._lib.wbc_solve_qp(self._h))
+
+    def solveQPStatic(self):
+        """wbc_solve_qp_static: solveQP without any allocation (scratch in a static device array of the library; at most 1024 robots)"""
+        self._ck(self._lib.wbc_solve_qp_static(self._h))
 
     def computeJointTorques(self):
         self._ck(self._lib.wbc_compute_joint_torques(self._h))

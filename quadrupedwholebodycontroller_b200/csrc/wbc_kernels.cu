@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "../../include/wbc_b200.h"
@@ -352,6 +353,7 @@ struct wbc_handle {
     QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false; size_t setupPad=0;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     // closed-loop rollout as a CUDA graph: one planner period (planner tick + graphPeriod control ticks incl. the plant) captured once, replayed per period
     cudaGraph_t graph=nullptr; cudaGraphExec_t graphExec=nullptr; int graphPeriod=0; long long graphLaunches=0; bool capturing=false, useGraph=true;
+    void* staticScratch=nullptr;                    // device address of g_wbc_static_scratch on this handle's device (wbc_solve_qp_static)
     long long launches=0;
     std::string err;
 };
@@ -383,6 +385,7 @@ extern "C" void wbc_default_params(wbc_params* p){
 
 template<class T> static cudaError_t dalloc(T*& p,size_t n){ return cudaMalloc((void**)&p,n*sizeof(T)); }
 
+static cudaError_t wbc_static_scratch_address(int device,void** out);      // device address of the static scratch of wbc_solve_qp_static (defined with it, below)
 extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream,wbc_handle** out){
     if(!out||n<=0) return WBC_ERR_ARG;
     *out=nullptr;
@@ -421,6 +424,7 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
     h->devParams=P;
     if(cudaMemcpyToSymbol(c_model,&mc,sizeof(mc))!=cudaSuccess){
         h->err=std::string("cudaMemcpyToSymbol: ")+cudaGetErrorString(cudaGetLastError())+" (library built for sm_100a only)"; return fail(WBC_ERR_CUDA); }
+    wbc_static_scratch_address(device,&h->staticScratch);                           // set-up of wbc_solve_qp_static (a failure is reported by that call, not here)
     h->updSmem=sizeof(ModelConst)+UPD_GROUPS*sizeof(UpdSmem);
     if(cudaFuncSetAttribute(wbc_update_state_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->updSmem)!=cudaSuccess
        ||cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->updBlocksPerSM,wbc_update_state_kernel,32,h->updSmem)!=cudaSuccess||h->updBlocksPerSM<1){
@@ -503,6 +507,59 @@ extern "C" int wbc_update_state(wbc_handle* h){
     wbc_update_state_kernel<<<grid,32,h->updSmem,h->stream>>>(h->N,h->devParams,batch_in(h),h->legs,h->ctrl,h->qpd,h->first,h->com,h->plantAux);
     h->launches++; CK(cudaGetLastError());
     if(!h->capturing) CK(cudaEventRecord(h->ev[1],h->stream));
+    return WBC_OK;
+}
+// ---------------------------------------------------------------- no-allocation variant of solveQP (no counterpart in the reference)
+// wbc_solve_qp allocates the hand-over buffer between kernels 2a and 2 (QPPre, 22 KB per robot) with cudaMalloc at the first hot-started tick.  Callers that
+// cannot allocate (CUDA graph capture, tight serving loops) use wbc_solve_qp_static: the same two kernels with that scratch -- and the work counter -- in this
+// file-scope array, for batches of at most WBC_STATIC_MAX_ROBOTS (include/wbc_b200.h: 1024) robots.  Every GPU that loads the library holds the array (22.5 MB) until exit; every call on a
+// device shares it, so calls that overlap on the GPU race.  Nothing in it has to start at zero except the work counter, which each call clears: kernel 2a
+// rewrites all of a robot's record that kernel 2 goes on to use (the bulk copy also moves stale T entries beyond tri(nAC), which are never read -- exactly
+// as with the uninitialised cudaMalloc buffer of wbc_solve_qp).
+constexpr size_t WBC_STATIC_PRE_BYTES=sizeof(QPPre)*(size_t)WBC_STATIC_MAX_ROBOTS;
+static __device__ __align__(256) unsigned char g_wbc_static_scratch[WBC_STATIC_PRE_BYTES+256];      // [QPPre x 1024 | work counter]
+// In host code the array's name is only a stand-in: the device address is asked for once per device, with that device current, and cached here.
+constexpr int WBC_STATIC_MAX_DEVICES=64;
+static void* g_wbc_static_addr[WBC_STATIC_MAX_DEVICES]={};
+static std::mutex g_wbc_static_mutex;
+static cudaError_t wbc_static_scratch_address(int device,void** out){            // the caller has made `device` current
+    *out=nullptr;
+    if(device<0||device>=WBC_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_wbc_static_mutex);
+    if(!g_wbc_static_addr[device]){
+        void* p=nullptr; const cudaError_t e=cudaGetSymbolAddress(&p,g_wbc_static_scratch);
+        if(e!=cudaSuccess){ cudaGetLastError(); return e; }
+        g_wbc_static_addr[device]=p;
+    }
+    *out=g_wbc_static_addr[device];
+    return cudaSuccess;
+}
+extern "C" int wbc_solve_qp_static(wbc_handle* h){
+    if(!h) return WBC_ERR_ARG;
+    if(h->N>WBC_STATIC_MAX_ROBOTS){
+        h->err="wbc_solve_qp_static: "+std::to_string(h->N)+" robots exceed the static scratch of "+std::to_string(WBC_STATIC_MAX_ROBOTS)+" robots (WBC_STATIC_MAX_ROBOTS); use wbc_solve_qp";
+        return WBC_ERR_ARG; }
+    CK(cudaSetDevice(h->device));
+    void* base=h->staticScratch;                                                  // resolved at set-up (wbc_create)
+    if(!base){ const cudaError_t e=wbc_static_scratch_address(h->device,&base);
+               if(e!=cudaSuccess||!base){ h->err=std::string("wbc_solve_qp_static: cudaGetSymbolAddress: ")+cudaGetErrorString(e); return WBC_ERR_CUDA; }
+               h->staticScratch=base; }
+    QPPre* pre=reinterpret_cast<QPPre*>(base);
+    int* counter=reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(base)+WBC_STATIC_PRE_BYTES);
+    int grid=h->smCount*h->qpBlocksPerSM;
+    if(grid>(h->N+WBC_GANG-1)/WBC_GANG) grid=(h->N+WBC_GANG-1)/WBC_GANG;
+    const int cohort= h->cohortMode<0 ? (h->maybeWarm?0:1) : h->cohortMode;
+    CK(cudaMemsetAsync(counter,0,sizeof(int),h->stream));                         // the one thing that must start at zero
+    if(!h->capturing) CK(cudaEventRecord(h->ev[1],h->stream));
+    const bool two=h->maybeWarm;                                                  // hot-started robots: kernel 2a rebuilds their factorisation into the static scratch
+    if(two){
+        wbc_warm_setup_kernel<<<h->N,32,(h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad,h->stream>>>(h->N,h->qpd,h->qps,h->first,pre,h->setupCanary?1:0);
+        h->launches++; CK(cudaGetLastError());
+    }
+    wbc_solve_qp_kernel<<<grid,WBC_QP_THREADS,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),counter,100 /* nWSR, wbc.cpp:517 */,h->prof,cohort,two?pre:nullptr,h->stats);
+    h->launches++; CK(cudaGetLastError());
+    h->maybeWarm=true;
+    if(!h->capturing) CK(cudaEventRecord(h->ev[2],h->stream));
     return WBC_OK;
 }
 extern "C" int wbc_solve_qp(wbc_handle* h){
