@@ -39,6 +39,23 @@
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" :: "r"(dst),"l"(__cvta_generic_to_global(src)),"r"(bytes),"r"(bar) : "memory"); }
   WBC_DEV void wbc_mbar_wait(unsigned bar,unsigned parity){
       unsigned ok; do{ asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar),"r"(parity) : "memory"); }while(!ok); }
+  // Tensor memory as a LANE-PRIVATE scratchpad (WBC_TMEM): thread t of warp w owns TMEM lane 32*(w%4)+t; one `real` is one (fp32) or two (fp64) 32-bit
+  // columns, moved by tcgen05.ld / tcgen05.st 32x32b (SASS LDTM / STTM).  A load's registers are valid after tcgen05.wait::ld (wbc_tm_wait_ld, then
+  // wbc_tm_use on each value so the compiler keeps every use behind the wait); stores are complete after tcgen05.wait::st.  All of them are .sync.aligned:
+  // every lane of the warp executes them together.
+#if defined(WBC_FP32)
+  WBC_DEV void wbc_tm_ld(unsigned a,float& v){ unsigned x; asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(x) : "r"(a)); v=__uint_as_float(x); }
+  WBC_DEV void wbc_tm_st(unsigned a,float v){ asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" :: "r"(a),"r"(__float_as_uint(v)) : "memory"); }
+  WBC_DEV void wbc_tm_use(float& v){ asm volatile("" : "+f"(v)); }
+  constexpr unsigned WBC_TM_COLS_PER_REAL=1u;
+#else
+  WBC_DEV void wbc_tm_ld(unsigned a,double& v){ unsigned lo,hi; asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(lo),"=r"(hi) : "r"(a)); v=__hiloint2double((int)hi,(int)lo); }
+  WBC_DEV void wbc_tm_st(unsigned a,double v){ asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" :: "r"(a),"r"((unsigned)__double2loint(v)),"r"((unsigned)__double2hiint(v)) : "memory"); }
+  WBC_DEV void wbc_tm_use(double& v){ asm volatile("" : "+d"(v)); }
+  constexpr unsigned WBC_TM_COLS_PER_REAL=2u;
+#endif
+  WBC_DEV void wbc_tm_wait_ld(){ asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+  WBC_DEV void wbc_tm_wait_st(){ asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
   WBC_DEV unsigned wbc_ballot(bool p){ return __ballot_sync(0xffffffffu,p); }
   WBC_DEV double wbc_max(double v){ for(int o=16;o>0;o>>=1){ double t=__shfl_xor_sync(0xffffffffu,v,o); v = t>v?t:v; } return v; }
   WBC_DEV double wbc_bcast(double v,int src){ return __shfl_sync(0xffffffffu,v,src); }

@@ -13,7 +13,9 @@
 #include "../../include/wbc_b200.h"
 #ifndef WBC_GANG                /* solver warps (= robots in flight) per CTA, one CTA per SM: as many as the 227 KB of shared memory hold */
   #if defined(WBC_FP32)
-    #define WBC_GANG 11         /* 11 x 19.0 KB */
+    #define WBC_GANG 11         /* 11 x 19.0 KB (vectors in shared memory) */
+  #elif !defined(WBC_NO_TMEM)
+    #define WBC_GANG 7          /* 7 x 32.4 KB, element-wise vectors in tensor memory */
   #else
     #define WBC_GANG 6          /* 6 x 37.6 KB */
   #endif
@@ -132,7 +134,7 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
     unsigned long long* guard=reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(smem)+QPWORK_TQ_BYTES);
     constexpr int NGUARD=(int)((sizeof(QPWork)-QPWORK_TQ_BYTES)/8);
     if(canary){ LANE_FOR(i,NGUARD) guard[i]=0xFFFFFFFFFFFFFFFFull; WBC_SYNC(); }
-    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
+    QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r]; c.tm=0u; c.tqBar=0u; c.tqParity=0u;
 #if defined(WBC_PROFILE)
     c.flops=0.0;
 #endif
@@ -152,11 +154,17 @@ __global__ void __launch_bounds__(32) wbc_warm_setup_kernel(int N,const QPData* 
 }
 
 // ---------------------------------------------------------------- kernel 2: active-set QP solve (init / hotstart) + torque recovery
-// One robot per warp; WBC_GANG warps per CTA (one CTA per SM: 6 x 37.6 KB of shared memory in fp64, 11 x 19.0 KB in fp32) walk the iterations of their robots in
+// One robot per warp; WBC_GANG warps per CTA (one CTA per SM: 7 x 32.4 KB of shared memory + 7 x 7.3 KB of tensor memory in fp64, 11 x 19.0 KB in fp32) walk the iterations of their robots in
 // step (wbc_qp.cuh "gang mode").  Robots are pulled from an atomic work counter.  cohort = 0: a warp fetches its next robot as soon as
 // it is done (hot-started ticks: iteration counts 0..100); cohort = 1: the gang fetches together and waits for its slowest member (cold
 // batches: all members then sit at the same iteration index with matrices of the same size, which keeps the barrier waits short).
 #define WBC_QP_THREADS (32*WBC_GANG)
+#if WBC_LV_TMEM
+constexpr int WBC_TM_NEED_COLS=((WBC_GANG+3)/4)*LV_SLOTS*(int)WBC_TM_COLS_PER_REAL;      // column blocks of the robots that share a lane quarter
+constexpr int WBC_TM_ALLOC_COLS= WBC_TM_NEED_COLS<=32?32 : WBC_TM_NEED_COLS<=64?64 : WBC_TM_NEED_COLS<=128?128 : WBC_TM_NEED_COLS<=256?256 : 512;
+static_assert(WBC_TM_NEED_COLS<=512&&WBC_GANG<=16,"tensor memory: 512 columns, 4 lane quarters");
+static_assert((size_t)WBC_GANG*(sizeof(QPWork)+16)+16<=232448,"gang workspace exceeds the 227 KB of shared memory a CTA can have");
+#endif
 __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int cohort,const QPPre* pre,int* stats){
     extern __shared__ double smem[];
     QPWork& w=*reinterpret_cast<QPWork*>(reinterpret_cast<char*>(smem)+(size_t)(threadIdx.x>>5)*sizeof(QPWork));
@@ -166,6 +174,19 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
     unsigned parH=0u, parQ=0u;
     if(lane==0){ wbc_mbar_init(barH,1u); wbc_mbar_init(barQ,1u); wbc_mbar_init_fence(); wbc_fence_proxy_async(); }
     WBC_SYNC();
+#if WBC_LV_TMEM
+    // tensor memory for the lane-owned vectors of the gang's robots: warp w uses lane quarter w % 4 (the only one its tcgen05.ld / st can reach) and the
+    // column block w / 4.  One CTA per SM: the allocation cannot contend.
+    unsigned* tmBaseS=reinterpret_cast<unsigned*>(reinterpret_cast<char*>(smem)+(size_t)WBC_GANG*sizeof(QPWork)+16*WBC_GANG);
+    if((threadIdx.x>>5)==0){
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(wbc_saddr(tmBaseS)),"n"(WBC_TM_ALLOC_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmRobot=*tmBaseS+((((unsigned)(threadIdx.x>>5)&3u)*32u)<<16)+(unsigned)(threadIdx.x>>7)*(unsigned)(LV_SLOTS*WBC_TM_COLS_PER_REAL);
+#endif
     for(;;){
         int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
         if(cohort){ if(gang_bar(r>=N)) break; }                      // the whole gang is out of work
@@ -173,6 +194,11 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
         const bool isFirst=first[r]!=0;
         QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
         c.tqBar=0u; c.tqParity=0u;
+#if WBC_LV_TMEM
+        c.tm=tmRobot;
+#else
+        c.tm=0u;
+#endif
         // Bulk asynchronous copies first (cp.async.bulk -> mbarrier): the robot's QP blocks and, for a hot-started robot whose factorisation kernel 2a
         // rebuilt, Q and T (21.7 KB in fp64) -- the latter is not needed before qp_hotstart has formed A x and the auxiliary gradient, so its
         // flight time is hidden.  WBC_SYNC + proxy fence: every lane has finished with the previous robot's workspace before the async proxy writes it.
@@ -216,11 +242,12 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
             for(int k=0;k<3;k++){ const int i=lane+32*k; const bool in=i<70; ta[k]=in?S.Ax_l[i]:real(0); tb[k]=in?S.Ax_u[i]:real(0); sc[k]=in?S.cstat[i]:(signed char)0; }
             c.rampOffset=S.rampOffset; c.status=S.status;
             #pragma unroll
-            for(int k=0;k<2;k++){ const int i=lane+32*k; if(i<42){ w.x[i]=tx[k]; w.lb[i]=tl[k]; w.ub[i]=tu[k]; w.bstat[i]=sb[k]; } }
+            for(int k=0;k<2;k++){ const int i=lane+32*k; if(i<42){ w.x[i]=tx[k]; w.bstat[i]=sb[k]; } if(WBC_LV_TMEM||i<42){ LV_ST(lb,i,k,tl[k]); LV_ST(ub,i,k,tu[k]); } }
             #pragma unroll
             for(int k=0;k<4;k++){ const int i=lane+32*k; if(i<112) w.y[i]=ty[k]; }
             #pragma unroll
-            for(int k=0;k<3;k++){ const int i=lane+32*k; if(i<70){ w.Ax_l[i]=ta[k]; w.Ax_u[i]=tb[k]; w.cstat[i]=sc[k]; } }
+            for(int k=0;k<3;k++){ const int i=lane+32*k; if(i<70) w.cstat[i]=sc[k]; if(WBC_LV_TMEM||i<70){ LV_ST(Ax_l,i,k,ta[k]); LV_ST(Ax_u,i,k,tb[k]); } }
+            LV_DONE();
         }
 #if !defined(WBC_FP32)
         if(lane<6) ((real*)&w.qp)[QPHOT_HEAD+lane]=tailv;
@@ -234,9 +261,11 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
         // QProblemB::getPrimalSolution (QProblemB.cpp:774-793) hands x out only in these three states; otherwise the caller's qpSolution_ keeps
         // its previous value (wbc.cpp:536) -- and so does out.x.  The solver's own iterate S.x is stored regardless (it IS the SQProblem member).
         const bool haveSol=(c.status==QPS_AUXILIARYQPSOLVED||c.status==QPS_HOMOTOPYQPSOLVED||c.status==QPS_SOLVED);
-        LANE_FOR(i,42){ S.x[i]=w.x[i]; S.lb[i]=w.lb[i]; S.ub[i]=w.ub[i]; S.bstat[i]=w.bstat[i]; if(haveSol) out.x[i*N+r]=w.x[i]; else w.x[i]=(real)out.x[i*N+r]; out.ws[i*N+r]=w.bstat[i]; }
+        LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
+            if(LV_IN(i,42)){ S.x[i]=w.x[i]; S.lb[i]=lbi; S.ub[i]=ubi; S.bstat[i]=w.bstat[i]; if(haveSol) out.x[i*N+r]=w.x[i]; else w.x[i]=(real)out.x[i*N+r]; out.ws[i*N+r]=w.bstat[i]; } }
         LANE_FOR(i,112) S.y[i]=w.y[i];
-        LANE_FOR(i,70){ S.Ax_l[i]=w.Ax_l[i]; S.Ax_u[i]=w.Ax_u[i]; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; }
+        LV_FOR(i,sl,70){ LV_LD(al,Ax_l,i,sl); LV_LD(au,Ax_u,i,sl); LV_WAIT(); LV_USE(al); LV_USE(au);
+            if(LV_IN(i,70)){ S.Ax_l[i]=al; S.Ax_u[i]=au; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; } }
         WBC_SYNC();
         // computeJointTorques (wbc.cpp:553-577) on the solution still in shared memory: tau = M_c,jj qdd* + bias_c,j - Jst_c,j^T f*, f* = x[18:30];
         // a robot whose solve did not return 0 publishes zero torques (terminate(), :626-635).  w.x = qpSolution_ here (see above).
@@ -254,6 +283,11 @@ __global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,cons
         WBC_SYNC();
         if(cohort){ while(!gang_bar(1)){} }                           // drain until every member of the gang is done
     }
+#if WBC_LV_TMEM
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();                                                  // every warp left the loop at the same barrier: nobody uses tensor memory any more
+    if((threadIdx.x>>5)==0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(*tmBaseS),"n"(WBC_TM_ALLOC_COLS) : "memory");
+#endif
 }
 
 // ---------------------------------------------------------------- kernel 3 (torque recovery, wbc.cpp:553-577) is the epilogue of kernel 2:
@@ -430,7 +464,7 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
        ||cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->updBlocksPerSM,wbc_update_state_kernel,32,h->updSmem)!=cudaSuccess||h->updBlocksPerSM<1){
         h->err=std::string("update-state kernel geometry: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     // solver launch geometry: one warp per CTA, as many CTAs per SM as shared memory allows
-    h->qpSmem=sizeof(QPWork)*WBC_GANG+16*WBC_GANG;                                  // + two mbarriers per warp
+    h->qpSmem=sizeof(QPWork)*WBC_GANG+16*WBC_GANG+(WBC_LV_TMEM?16:0);                                  // + two mbarriers per warp
     if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,WBC_QP_THREADS,h->qpSmem)!=cudaSuccess||nb<1){

@@ -68,6 +68,7 @@ constexpr int OPT_numRefinementSteps=2;
 constexpr real LI_SURE=real(1.0e-6), LI_NONE=real(1.0e-12);
 #endif
 
+constexpr int HZLD=42;                // row length of the (HZ)_force block (the 4-wide tiles of zhz_tiles may read up to 2 elements past a row's end and discard them)
 constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
 constexpr int SIZET=42;               // sizeT = min(nV,nC)
 #define WQP (w.qp)
@@ -134,9 +135,42 @@ struct QPState {
     int rampOffset, status, pad_;
 };
 
-// per-instance shared-memory workspace (37.6 KB in fp64 -> 6 instances per SM; 19.0 KB in fp32 -> 11).  The members up to and including `arow` are all the warm-start
+// per-instance shared-memory workspace (32.4 KB in fp64 with the lane-owned vectors in tensor memory -> 7 instances per SM; 19.0 KB in fp32 -> 11).  The members up to and including `arow` are all the warm-start
 // TQ rebuild touches (rebuild_TQ): the kernel that runs only that phase allocates just this prefix (QPWORK_TQ_BYTES, 9 instances per SM).
-struct QPWork {
+// ---------------------------------------------------------------- lane-owned vectors
+// g, lb, ub, lbA, ubA, Ax, Ax - lbA, ubA - Ax, the data shift of lbA / ubA and the dual step of the fixed variables are only ever touched element by element, element i by
+// lane i % 32 (loops over a list are written as loops over the element number with the status as a guard).  The device build keeps them in TENSOR MEMORY instead of
+// shared memory: 256 KB per SM that nothing else in this library uses, private to a lane.  That takes the workspace of a robot from 37.6 to 32.4 KB, i.e. from
+// 6 to 7 robots per SM.  Slot s of a vector = its elements 32 s .. 32 s + 31; a slot is one (fp32) or two (fp64) TMEM columns.
+//   LV_FOR(i,sl,n)      loop over the elements: warp-uniform trip count with WBC_TMEM (every lane executes the tcgen05 instructions; LV_IN(i,n) guards the rest)
+//   LV_LD(v,name,i,sl)  declare v and request element i (no wait); LV_WAIT(); then LV_USE(v) for every requested value before its first use
+//   LV_ST(name,i,sl,v)  store (no wait); LV_DONE() at the end of the loop body
+// The fp32 build keeps them in shared memory: its 11 robots per SM already saturate the instruction supply (measured: 12 robots with tensor memory = same
+// speed, 13 = 10 % slower; profiles/r02_gang_variants.txt).  -DWBC_NO_TMEM: development variant of the fp64 build with the vectors in shared memory (6 robots per SM).
+#if defined(__CUDACC__) && !defined(WBC_NO_TMEM) && !defined(WBC_FP32)
+  #define WBC_LV_TMEM 1
+#else
+  #define WBC_LV_TMEM 0
+#endif
+enum { LV_g=0, LV_lb=2, LV_ub=4, LV_dyFX=6, LV_lbA=8, LV_ubA=11, LV_Ax=14, LV_Ax_l=17, LV_Ax_u=20, LV_dlbA=23, LV_dubA=26, LV_SLOTS=29 };
+#if WBC_LV_TMEM
+  #define LV_FOR(i,sl,n) _Pragma("unroll") for(int sl=0,i=lane;sl<((n)+31)/32;sl++,i+=32)
+  #define LV_IN(i,n) ((i)<(n))
+  #define LV_LD(v,name,i,sl) real v; wbc_tm_ld(c.tm+WBC_TM_COLS_PER_REAL*(unsigned)(LV_##name+(sl)),v)
+  #define LV_WAIT() wbc_tm_wait_ld()
+  #define LV_USE(v) wbc_tm_use(v)
+  #define LV_ST(name,i,sl,v) wbc_tm_st(c.tm+WBC_TM_COLS_PER_REAL*(unsigned)(LV_##name+(sl)),(v))
+  #define LV_DONE() wbc_tm_wait_st()
+#else
+  #define LV_FOR(i,sl,n) LANE_FOR(i,n)
+  #define LV_IN(i,n) true
+  #define LV_LD(v,name,i,sl) real v=w.name[i]
+  #define LV_WAIT() do{}while(0)
+  #define LV_USE(v) do{}while(0)
+  #define LV_ST(name,i,sl,v) w.name[i]=(v)
+  #define LV_DONE() do{}while(0)
+#endif
+struct alignas(16) QPWork {
     real Q[42*LD];
     real RT[TRI42+1];                         // packed R and T (see RR / TT)
     signed char FR[42], FX[42], AC[70], IAC[70], bstat[42], cstat[70], posAC[70], pad_[10];     // 416 B: Q, RT, the scratch block and qp all start on 16-byte boundaries (bulk copies)
@@ -150,12 +184,17 @@ struct QPWork {
             union { struct { real num[70], den[70], dAx[70]; }; struct { real tA[42], tB[42], xTMP[42], yTMP[42], vm[42]; }; struct { real wv[42], cs_c[42], cs_s[42]; }; };
             real xFRy[42], xFRz[42], Zdz[42], ym[70];
         };
-        real HZf[12*LD];
+        real HZf[12*HZLD];
     };
     QPHotR qp;                                  // the matrix blocks of the compact QP (H, A); lbA / ubA / bias_j are read from HBM through QPCtx::qg
-    real x[42], y[112], g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
-    real dlbA[70], dubA[70];                                     // data shift of the constraint bounds (the shifts of g, lb, ub are re-evaluated where used: shift_dg / shift_dlb / shift_dub)
-    real dx[42], dyAC[42], dyFX[42];                           // step (dx, dyFX by variable number; dyAC by AC position)
+    real x[42], y[112];
+#if !WBC_LV_TMEM
+    // the element-wise ("lane-owned") vectors: every access is element i by the lane i % 32 -- see LV_* above; with WBC_TMEM they live in tensor memory
+    real g[42], lb[42], ub[42], lbA[70], ubA[70], Ax[70], Ax_l[70], Ax_u[70];
+    real dlbA[70], dubA[70];                                     // data shift of the constraint bounds (the shifts of g, lb, ub are re-evaluated where used)
+    real dyFX[42];                                               // dual step of the fixed variables, by variable number
+#endif
+    real dx[42], dyAC[42];                                     // step (dx by variable number; dyAC by AC position)
     real rdR[42], rdT[42];                                     // reciprocal diagonals of R and T
 };
 constexpr size_t QPWORK_TQ_BYTES=(42*LD+TRI42+1)*sizeof(real)+416+5*42*sizeof(real);
@@ -182,6 +221,7 @@ struct QPCtx {
     real farbound;     // far bound of the current homotopy (QProblem::updateFarBounds)
     real tau;
     const QPData* qg;    // this robot's compact QP in HBM (fp64): new lbA / ubA targets, bias_j
+    unsigned tm;                // WBC_TMEM: tensor-memory address (lane quarter of this warp, first column of its robot) of the lane-owned vectors
     unsigned tqBar, tqParity;   // != 0: a bulk copy of the rebuilt Q / T into w.Q, w.RT is in flight on this mbarrier (shared-space address) with this phase parity
 #if defined(WBC_PROFILE)
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
@@ -521,7 +561,7 @@ WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
             for(int b=0;b<TS;b++) zj[b]=QQ(v,TS*tj+b);
             if(v>=18&&v<30){
                 #pragma unroll
-                for(int a=0;a<TS;a++) wk[a]=w.HZf[(v-18)*LD+TS*ti+a];
+                for(int a=0;a<TS;a++) wk[a]=w.HZf[(v-18)*HZLD+TS*ti+a];
             } else { const real dv=(v>=30)?WQP.rho:real(1.0);
                 #pragma unroll
                 for(int a=0;a<TS;a++) wk[a]=dv*QQ(v,TS*ti+a); }
@@ -564,7 +604,7 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
         WBC_SYNC();
         LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; real s=0;
             for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
-            w.HZf[a*LD+k]=s; }
+            w.HZf[a*HZLD+k]=s; }
         WBC_SYNC();
         zhz_tiles(w,c,nFR,nZ);
     }
@@ -590,12 +630,12 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
     WBC_SYNC();
     LANE_FOR(e,12*nZ){ const int k=e/12, a=e-12*k; real s=0;
         for(int i=0;i<nff;i++){ const int u=ffl[i]; s+=WQP.Hff[12*u+a]*QQ(18+u,k); }
-        w.HZf[a*LD+k]=s; }
+        w.HZf[a*HZLD+k]=s; }
     WBC_SYNC();
     real* col=w.dx;                                           // the step direction is dead between performStep and the next determineStepDirection
     LANE_FOR(i,nZ){ real s=real(0.0);
         for(int ii=0;ii<nFR;ii++){ const int v=(int)w.FR[ii]; const real z=QQ(v,n);
-            const real hk=(v>=18&&v<30)? w.HZf[(v-18)*LD+i] : ((v>=30)?WQP.rho:real(1.0))*QQ(v,i);
+            const real hk=(v>=18&&v<30)? w.HZf[(v-18)*HZLD+i] : ((v>=30)?WQP.rho:real(1.0))*QQ(v,i);
             s+=z*hk; }
         col[i]=s; }
     WBC_SYNC();
@@ -618,9 +658,10 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
 // functions of the current g / lb / ub, the new gradient and the far bound, so they are re-evaluated where they are used instead of being kept in
 // 1 KB of shared memory (what decides whether an SM holds 5 or 6 robots); g, lb and ub only change in the update of performStep, which reads them last.
 WBC_DEV real far_rv(const QPCtx& c,int idx);
-WBC_DEV real shift_dg(const QPWork& w,int i){ const real gn=(i>=18&&i<30)?WQP.gf[i-18]:real(0.0); return gn-w.g[i]; }
-WBC_DEV real shift_dlb(const QPWork& w,const QPCtx& c,int i){ return -far_rv(c,i)-w.lb[i]; }
-WBC_DEV real shift_dub(const QPWork& w,const QPCtx& c,int i){ return far_rv(c,i)-w.ub[i]; }
+WBC_DEV real g_target(const QPWork& w,int i){ return (i>=18&&i<30)?WQP.gf[i-18]:real(0.0); }
+#define SHIFT_DG(i,gi)   (g_target(w,i)-(gi))        /* gi, lbi, ubi = the current g[i], lb[i], ub[i] (lane-owned vectors: loaded by the caller) */
+#define SHIFT_DLB(i,lbi) (-far_rv(c,i)-(lbi))
+#define SHIFT_DUB(i,ubi) (far_rv(c,i)-(ubi))
 
 // ---------------------------------------------------------------- step direction
 // QProblem::determineStepDirection (QProblem.cpp:4637-4975), HST_POSDEF branch.
@@ -633,10 +674,20 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
     if(!prepare_T(w,c)) return QP_RET_STEPDIRECTION_FAILED_TQ;
     const unsigned ffm=force_mask(w,c,0), fxm=force_mask(w,c,1);
     // I) delta_xFX
-    const bool shift=(dg==nullptr); const real* dlbA=shift?w.dlbA:nullptr; const real* dubA=shift?w.dubA:nullptr;
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.dx[ii]= (bBzero||!shift)?real(0.0):((w.bstat[ii]==ST_LOWER)?shift_dlb(w,c,ii):shift_dub(w,c,ii)); }
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=shift?shift_dg(w,ii):dg[ii]; w.dx[ii]=real(0.0); }
-    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.dyAC[i]=real(0.0); w.tB[i]= (bCzero||!dlbA)?real(0.0):((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]); }
+    // homotopy step: the gradient shift goes by variable number into w.tmpv (dead outside the working-set changes) so that both modes read dg[]; the
+    // shift of the active constraints' bounds is in w.arow by AC position (determineDataShift)
+    const bool shift=(dg==nullptr);
+    if(shift){
+        LV_FOR(v,sl,42){ LV_LD(gv,g,v,sl); LV_LD(lbv,lb,v,sl); LV_LD(ubv,ub,v,sl); LV_WAIT(); LV_USE(gv); LV_USE(lbv); LV_USE(ubv);
+            if(LV_IN(v,42)){ const int bs=w.bstat[v]; const real dgv=SHIFT_DG(v,gv); w.tmpv[v]=dgv;
+                if(bs!=0) w.dx[v]= bBzero?real(0.0):((bs==ST_LOWER)?SHIFT_DLB(v,lbv):SHIFT_DUB(v,ubv));
+                else { w.tA[v]=dgv; w.dx[v]=real(0.0); } } }
+        dg=w.tmpv;
+    } else {
+        LANE_FOR(i,nFX) w.dx[(int)w.FX[i]]=real(0.0);
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.tA[ii]=dg[ii]; w.dx[ii]=real(0.0); }
+    }
+    LANE_FOR(i,nAC){ w.dyAC[i]=real(0.0); w.tB[i]= (bCzero||!shift)?real(0.0):w.arow[i]; }
     WBC_SYNC();
     int nref=0;
     for(int r=0;r<=OPT_numRefinementSteps;r++){
@@ -678,10 +729,10 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
         // residuals for the next refinement pass
         real rnrm=real(0.0);
         scatter_yAC(w,c,w.dyAC);
-        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; real t=shift?shift_dg(w,ii):dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
+        LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; real t=dg[ii]; t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); w.tA[ii]=t; rnrm=fmax(rnrm,fabs(t)); }
         // bA - A_FR dx_FR - A_FX dx_FX: the free columns first, then the fixed ones, each accumulated onto tempB (QProblem.cpp:4934-4935)
         mask_vars(w,c,w.dx,0);
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real t= (bCzero||!dlbA)?real(0.0):((w.cstat[ii]==ST_LOWER)?dlbA[ii]:dubA[ii]);
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real t= (bCzero||!shift)?real(0.0):w.arow[i];
             w.tB[i]=Arow_acc(WQP,ii,w.vm,t,-real(1.0)); }
         if(!bBzero&&shift){ mask_vars(w,c,w.dx,1); LANE_FOR(i,nAC) w.tB[i]=Arow_acc(WQP,(int)w.AC[i],w.vm,w.tB[i],-real(1.0)); }
         LANE_FOR(i,nAC) rnrm=fmax(rnrm,fabs(w.tB[i]));
@@ -697,9 +748,13 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
     WBC_FLOPS((1.0+nref)*(2.0*nAC*nAC+4.0*nFR*nAC+4.0*nFR*nZ+4.0*nFR*nFR+4.0*nZ*nZ)+nref*(2.0*nFR*nFR+4.0*nAC*42.0)); (void)nref;
     // IV) delta_yFX
     scatter_yAC(w,c,w.dyAC);
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; real t=shift?shift_dg(w,ii):dg[ii]; t=Acol_acc(WQP,ii,w.ym,t,-real(1.0)); t=Hrow_acc(w,ii,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,ii,w.dx,1,fxm,t,real(1.0)); w.dyFX[ii]=t; }
+    if(nFX>0){
+        LV_FOR(v,sl,42){ real t=real(0.0);
+            if(LV_IN(v,42)&&w.bstat[v]!=0){ t=dg[v]; t=Acol_acc(WQP,v,w.ym,t,-real(1.0)); t=Hrow_acc(w,v,w.dx,0,ffm,t,real(1.0)); t=Hrow_acc(w,v,w.dx,1,fxm,t,real(1.0)); }
+            LV_ST(dyFX,v,sl,t); LV_DONE(); }
+    }
     WBC_SYNC();
-    WBC_DBG_VEC("dxFR",w.dx[(int)w.FR[i]],nFR); WBC_DBG_VEC("dyAC",w.dyAC[i],nAC); WBC_DBG_VEC("dyFX",w.dyFX[(int)w.FX[i]],nFX); WBC_DBG_VEC("dxFX",w.dx[(int)w.FX[i]],nFX);
+    WBC_DBG_VEC("dxFR",w.dx[(int)w.FR[i]],nFR); WBC_DBG_VEC("dyAC",w.dyAC[i],nAC); WBC_DBG_VEC("dxFX",w.dx[(int)w.FX[i]],nFX);
     return QP_OK;
 }
 
@@ -708,6 +763,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
 // list sequentially, replacing the candidate whenever num_i < t*den_i with the CURRENT t.  Exactly the same chain of
 // winners is produced here: a ballot finds the first later entry that beats the current t, t is updated, repeat.
 // stat == 0: plain test (performPlainRatioTest, QProblem.cpp:4256-4275: num > epsNum, den > epsDen, t*den > num).
+// num / den are indexed by the NUMBER of the variable / constraint (idx[i]); the scan runs in list order.
 WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const real* num,const real* den,
                               real& t,int& BC_idx){
     const int lane=c.lane; BC_idx=-1; int pos=0;
@@ -717,8 +773,8 @@ WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const s
         for(int base=(pos/WBC_NL)*WBC_NL; base<n; base+=WBC_NL){
             int i=base+lane; bool f=false;
             if(i>=pos&&i<n){
-                real nu=num[i], de=den[i];
-                if(stat){ if(stat[(int)idx[i]]==ST_UPPER){ nu=-nu; de=-de; }
+                const int ii=(int)idx[i]; real nu=num[ii], de=den[ii];
+                if(stat){ if(stat[ii]==ST_UPPER){ nu=-nu; de=-de; }
                           f=(de>=OPT_epsDen)&&(nu>=OPT_epsNum)&&(nu<t*de); }
                 else f=(nu>OPT_epsNum)&&(de>OPT_epsDen)&&(t*de>nu);
             }
@@ -726,7 +782,7 @@ WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const s
             if(m){ found=base+wbc_ffs(m); break; }
         }
         if(found<0) break;
-        t=num[found]/den[found]; BC_idx=(int)idx[found]; pos=found+1;
+        BC_idx=(int)idx[found]; t=num[BC_idx]/den[BC_idx]; pos=found+1;
     }
 }
 
@@ -743,27 +799,37 @@ WBC_DEV real tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c
 // QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are WQP.gf (g_new) and the far-bounded data
 WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,70){ const real rv=far_rv(c,42+i); w.dlbA[i]=fmax(-rv,(real)c.qg->lbA[i])-w.lbA[i]; w.dubA[i]=fmin(rv,(real)c.qg->ubA[i])-w.ubA[i]; }
+    bool nzC=false, nzB=false;
+    // the shift of an ACTIVE constraint's bound is also left by AC position in w.arow (dead between two working-set changes): what determineStepDirection reads
+    LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi);
+        real dl=real(0.0), du=real(0.0);
+        if(LV_IN(i,70)){ const real rv=far_rv(c,42+i); dl=fmax(-rv,(real)c.qg->lbA[i])-lbAi; du=fmin(rv,(real)c.qg->ubA[i])-ubAi;
+            const int cs=w.cstat[i];
+            if(cs!=0){ if(fabs(dl)>QEPS||fabs(du)>QEPS) nzC=true; w.arow[(int)w.posAC[i]]=(cs==ST_LOWER)?dl:du; } }
+        LV_ST(dlbA,i,sl,dl); LV_ST(dubA,i,sl,du); LV_DONE(); }
+    LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
+        if(LV_IN(i,42)&&w.bstat[i]!=0){ if(fabs(SHIFT_DLB(i,lbi))>QEPS||fabs(SHIFT_DUB(i,ubi))>QEPS) nzB=true; } }
     WBC_SYNC();
-    bool nz=false; LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; if(fabs(shift_dlb(w,c,ii))>QEPS||fabs(shift_dub(w,c,ii))>QEPS) nz=true; }
-    bBzero=(wbc_ballot(nz)==0u);
-    nz=false; LANE_FOR(i,c.nAC){ int ii=(int)w.AC[i]; if(fabs(w.dlbA[ii])>QEPS||fabs(w.dubA[ii])>QEPS) nz=true; }
-    bCzero=(wbc_ballot(nz)==0u);
+    bBzero=(wbc_ballot(nzB)==0u);
+    bCzero=(wbc_ballot(nzC)==0u);
 }
 // QProblem::getRelativeHomotopyLength (QProblem.cpp:5372-5410, QProblemB.cpp:2113-2157) is only ever compared with the termination
 // tolerance: max_i |d_i|/s_i <= tol  <=>  no |d_i| > tol*s_i -- evaluated in that form (no fp64 divisions), s_i = max(|target_i|,1).
 WBC_FN bool homotopyFinished(const QPWork& w,const QPCtx& c){
     const int lane=c.lane; const real tol=OPT_terminationTolerance; bool over=false;
-    LANE_FOR(i,42){ const real gn=(i>=18&&i<30)?WQP.gf[i-18]:real(0.0); if(fabs(gn-w.g[i])>tol*fmax(fabs(gn),real(1.0))) over=true;
-                    const real rv=far_rv(c,i), s=tol*fmax(rv,real(1.0)); if(fabs(-rv-w.lb[i])>s||fabs(rv-w.ub[i])>s) over=true; }
-    LANE_FOR(i,70){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(fabs(l-w.lbA[i])>tol*fmax(fabs(l),real(1.0))||fabs(u-w.ubA[i])>tol*fmax(fabs(u),real(1.0))) over=true; }
+    LV_FOR(i,sl,42){ LV_LD(gi,g,i,sl); LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(gi); LV_USE(lbi); LV_USE(ubi);
+        if(LV_IN(i,42)){ const real gn=g_target(w,i); if(fabs(gn-gi)>tol*fmax(fabs(gn),real(1.0))) over=true;
+                         const real rv=far_rv(c,i), s=tol*fmax(rv,real(1.0)); if(fabs(-rv-lbi)>s||fabs(rv-ubi)>s) over=true; } }
+    LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi);
+        if(LV_IN(i,70)){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(fabs(l-lbAi)>tol*fmax(fabs(l),real(1.0))||fabs(u-ubAi)>tol*fmax(fabs(u),real(1.0))) over=true; } }
     return wbc_ballot(over)==0u;
 }
 // QProblem::setupAuxiliaryQPgradient (QProblem.cpp:2602-2641): g = y_B - H x + A' y_C
 WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ real t=w.y[i]; t=Hrow_acc(w,i,w.x,2,0xfffu,t,-real(1.0));
-        w.g[i]=Acol_acc(WQP,i,w.y+42,t,real(1.0)); }
+    LV_FOR(i,sl,42){ real t=real(0.0);
+        if(LV_IN(i,42)){ t=w.y[i]; t=Hrow_acc(w,i,w.x,2,0xfffu,t,-real(1.0)); t=Acol_acc(WQP,i,w.y+42,t,real(1.0)); }
+        LV_ST(g,i,sl,t); LV_DONE(); }
     WBC_SYNC();
 }
 // QProblem::performStep (QProblem.cpp:4981-5278)
@@ -773,32 +839,38 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     WBC_FLOPS(2.0*nIAC*42.0+10.0*(42+70));
     WBC_SYNC();
     // I.1 active constraints' duals
-    LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=-w.dyAC[i]; }
+    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.num[ii]=w.y[42+ii]; w.den[ii]=-w.dyAC[i]; }
     performRatioTest(c,nAC,w.AC,w.cstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=false; }
     WBC_SYNC();
     // I.2 fixed variables' duals
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.num[i]=w.y[ii]; w.den[i]=-w.dyFX[ii]; }
-    performRatioTest(c,nFX,w.FX,w.bstat,w.num,w.den,c.tau,tmp);
-    if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
-    WBC_SYNC();
+    if(nFX>0){
+        LV_FOR(v,sl,42){ LV_LD(dyv,dyFX,v,sl); LV_WAIT(); LV_USE(dyv); if(LV_IN(v,42)&&w.bstat[v]!=0){ w.num[v]=w.y[v]; w.den[v]=-dyv; } }
+        performRatioTest(c,nFX,w.FX,w.bstat,w.num,w.den,c.tau,tmp);
+        if(tmp>=0){ BC_idx=tmp; BC_status=ST_INACTIVE; BC_isBound=true; }
+        WBC_SYNC();
+    }
     // II.1 inactive constraints
     LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.dAx[ii]=Arow_acc(WQP,ii,w.dx,real(0.0),real(1.0)); }
     WBC_SYNC();
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_l[ii],real(0.0)); w.den[i]=w.dlbA[ii]-w.dAx[ii]; }
+    LV_FOR(i,sl,70){ LV_LD(al,Ax_l,i,sl); LV_LD(dl,dlbA,i,sl); LV_WAIT(); LV_USE(al); LV_USE(dl);
+        if(LV_IN(i,70)&&w.cstat[i]==0){ w.num[i]=fmax(al,real(0.0)); w.den[i]=dl-w.dAx[i]; } }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=false; }
     WBC_SYNC();
-    LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; w.num[i]=fmax(w.Ax_u[ii],real(0.0)); w.den[i]=w.dAx[ii]-w.dubA[ii]; }
+    LV_FOR(i,sl,70){ LV_LD(au,Ax_u,i,sl); LV_LD(du,dubA,i,sl); LV_WAIT(); LV_USE(au); LV_USE(du);
+        if(LV_IN(i,70)&&w.cstat[i]==0){ w.num[i]=fmax(au,real(0.0)); w.den[i]=w.dAx[i]-du; } }
     performRatioTest(c,nIAC,w.IAC,w.cstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=false; }
     WBC_SYNC();
     // II.2 free variables
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.x[ii]-w.lb[ii],real(0.0)); w.den[i]=shift_dlb(w,c,ii)-w.dx[ii]; }
+    LV_FOR(v,sl,42){ LV_LD(lbv,lb,v,sl); LV_WAIT(); LV_USE(lbv);
+        if(LV_IN(v,42)&&w.bstat[v]==0){ w.num[v]=fmax(w.x[v]-lbv,real(0.0)); w.den[v]=SHIFT_DLB(v,lbv)-w.dx[v]; } }
     performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_LOWER; BC_isBound=true; }
     WBC_SYNC();
-    LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.num[i]=fmax(w.ub[ii]-w.x[ii],real(0.0)); w.den[i]=w.dx[ii]-shift_dub(w,c,ii); }
+    LV_FOR(v,sl,42){ LV_LD(ubv,ub,v,sl); LV_WAIT(); LV_USE(ubv);
+        if(LV_IN(v,42)&&w.bstat[v]==0){ w.num[v]=fmax(ubv-w.x[v],real(0.0)); w.den[v]=w.dx[v]-SHIFT_DUB(v,ubv); } }
     performRatioTest(c,nFR,w.FR,w.bstat,w.num,w.den,c.tau,tmp);
     if(tmp>=0){ BC_idx=tmp; BC_status=ST_UPPER; BC_isBound=true; }
     WBC_SYNC();
@@ -806,55 +878,72 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
     if(c.tau>QZERO){
         const real tau=c.tau;
         LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; w.x[ii]+=tau*w.dx[ii]; }
-        LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.x[ii]+=tau*w.dx[ii]; w.y[ii]+=tau*w.dyFX[ii]; }
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]+=tau*w.dyAC[i]; }
-        LANE_FOR(i,42){ const real rv=far_rv(c,i); w.g[i]+=tau*shift_dg(w,i); w.lb[i]+=tau*(-rv-w.lb[i]); w.ub[i]+=tau*(rv-w.ub[i]); }
-        LANE_FOR(i,70){ w.lbA[i]+=tau*w.dlbA[i]; w.ubA[i]+=tau*w.dubA[i]; }
+        LV_FOR(v,sl,42){ LV_LD(gv,g,v,sl); LV_LD(lbv,lb,v,sl); LV_LD(ubv,ub,v,sl); LV_LD(dyv,dyFX,v,sl); LV_WAIT(); LV_USE(gv); LV_USE(lbv); LV_USE(ubv); LV_USE(dyv);
+            if(LV_IN(v,42)){ if(w.bstat[v]!=0){ w.x[v]+=tau*w.dx[v]; w.y[v]+=tau*dyv; }
+                const real rv=far_rv(c,v); gv+=tau*SHIFT_DG(v,gv); lbv+=tau*(-rv-lbv); ubv+=tau*(rv-ubv); }
+            LV_ST(g,v,sl,gv); LV_ST(lb,v,sl,lbv); LV_ST(ub,v,sl,ubv); LV_DONE(); }
         WBC_SYNC();
-        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; real ax=Arow_acc(WQP,ii,w.x,real(0.0),real(1.0)); w.Ax[ii]=ax; w.Ax_u[ii]=w.ubA[ii]-ax; w.Ax_l[ii]=ax-w.lbA[ii]; }
-        LANE_FOR(i,nIAC){ int ii=(int)w.IAC[i]; real da=w.dAx[ii];
-            w.Ax[ii]+=tau*da; w.Ax_l[ii]+=tau*(da-w.dlbA[ii]); w.Ax_u[ii]+=tau*(w.dubA[ii]-da); }
+        // A x of the active constraints by number into w.num (the ratio tests are over), then one pass over the 70 constraints
+        LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.num[ii]=Arow_acc(WQP,ii,w.x,real(0.0),real(1.0)); }
+        WBC_SYNC();
+        LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_LD(dl,dlbA,i,sl); LV_LD(du,dubA,i,sl); LV_LD(axi,Ax,i,sl); LV_LD(al,Ax_l,i,sl); LV_LD(au,Ax_u,i,sl);
+            LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi); LV_USE(dl); LV_USE(du); LV_USE(axi); LV_USE(al); LV_USE(au);
+            if(LV_IN(i,70)){ lbAi+=tau*dl; ubAi+=tau*du;
+                if(w.cstat[i]!=0){ const real ax=w.num[i]; axi=ax; au=ubAi-ax; al=ax-lbAi; }
+                else { const real da=w.dAx[i]; axi+=tau*da; al+=tau*(da-dl); au+=tau*(du-da); } }
+            LV_ST(lbA,i,sl,lbAi); LV_ST(ubA,i,sl,ubAi); LV_ST(Ax,i,sl,axi); LV_ST(Ax_l,i,sl,al); LV_ST(Ax_u,i,sl,au); LV_DONE(); }
         WBC_SYNC();
     }
 }
 // QProblem::performRamping (QProblem.cpp:5416-5492); all bounds and constraints are typed ST_BOUNDED on this path
 WBC_FN void performRamping(QPWork& w,QPCtx& c){
     const int lane=c.lane, nRamp=42+70+70+42; WBC_SYNC();
-    LANE_FOR(i,42){
-        real tP=(real)((i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
-        real tD=(real)((42+70+70+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rD=(real(1.0)-tD)*OPT_ramp0+tD*OPT_ramp1;
-        int bs=w.bstat[i]; real xi=w.x[i], sca=fmax(fabs(xi),real(1.0));
-        if(bs!=ST_LOWER) w.lb[i]=xi-sca*rP;
-        if(bs!=ST_UPPER) w.ub[i]=xi+sca*rP;
-        if(bs==ST_LOWER){ w.lb[i]=xi; w.y[i]=+rD; }
-        if(bs==ST_UPPER){ w.ub[i]=xi; w.y[i]=-rD; }
-        if(bs==ST_INACTIVE) w.y[i]=real(0.0);
-    }
-    LANE_FOR(i,70){
-        real tP=(real)((42+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
-        real tD=(real)((42+70+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rD=(real(1.0)-tD)*OPT_ramp0+tD*OPT_ramp1;
-        int cs=w.cstat[i]; real ax=w.Ax[i], sca=fmax(fabs(ax),real(1.0));
-        if(cs!=ST_LOWER) w.lbA[i]=ax-sca*rP;
-        if(cs!=ST_UPPER) w.ubA[i]=ax+sca*rP;
-        if(cs==ST_LOWER){ w.lbA[i]=ax; w.y[42+i]=+rD; }
-        if(cs==ST_UPPER){ w.ubA[i]=ax; w.y[42+i]=-rD; }
-        if(cs==ST_INACTIVE) w.y[42+i]=real(0.0);
-        w.Ax_l[i]=ax-w.lbA[i]; w.Ax_u[i]=w.ubA[i]-ax;
-    }
+    LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
+        if(LV_IN(i,42)){
+            real tP=(real)((i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
+            real tD=(real)((42+70+70+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rD=(real(1.0)-tD)*OPT_ramp0+tD*OPT_ramp1;
+            int bs=w.bstat[i]; real xi=w.x[i], sca=fmax(fabs(xi),real(1.0));
+            if(bs!=ST_LOWER) lbi=xi-sca*rP;
+            if(bs!=ST_UPPER) ubi=xi+sca*rP;
+            if(bs==ST_LOWER){ lbi=xi; w.y[i]=+rD; }
+            if(bs==ST_UPPER){ ubi=xi; w.y[i]=-rD; }
+            if(bs==ST_INACTIVE) w.y[i]=real(0.0);
+        }
+        LV_ST(lb,i,sl,lbi); LV_ST(ub,i,sl,ubi); LV_DONE(); }
+    LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_LD(ax,Ax,i,sl); LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi); LV_USE(ax);
+        real al=real(0.0), au=real(0.0);
+        if(LV_IN(i,70)){
+            real tP=(real)((42+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
+            real tD=(real)((42+70+i+c.rampOffset)%nRamp)/(real)(nRamp-1), rD=(real(1.0)-tD)*OPT_ramp0+tD*OPT_ramp1;
+            int cs=w.cstat[i]; real sca=fmax(fabs(ax),real(1.0));
+            if(cs!=ST_LOWER) lbAi=ax-sca*rP;
+            if(cs!=ST_UPPER) ubAi=ax+sca*rP;
+            if(cs==ST_LOWER){ lbAi=ax; w.y[42+i]=+rD; }
+            if(cs==ST_UPPER){ ubAi=ax; w.y[42+i]=-rD; }
+            if(cs==ST_INACTIVE) w.y[42+i]=real(0.0);
+            al=ax-lbAi; au=ubAi-ax;
+        }
+        LV_ST(lbA,i,sl,lbAi); LV_ST(ubA,i,sl,ubAi); LV_ST(Ax_l,i,sl,al); LV_ST(Ax_u,i,sl,au); LV_DONE(); }
     setupAuxiliaryQPgradient(w,c);
     c.rampOffset++;
 }
 // QProblem::performDriftCorrection (QProblem.cpp:5559-5652)
 WBC_FN void performDriftCorrection(QPWork& w,QPCtx& c){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ int bs=w.bstat[i]; real xi=w.x[i];
-        if(bs==ST_LOWER){ w.lb[i]=xi; w.ub[i]=fmax(w.ub[i],xi); w.y[i]=fmax(w.y[i],real(0.0)); }
-        else if(bs==ST_UPPER){ w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=xi; w.y[i]=fmin(w.y[i],real(0.0)); }
-        else { w.lb[i]=fmin(w.lb[i],xi); w.ub[i]=fmax(w.ub[i],xi); w.y[i]=real(0.0); } }
-    LANE_FOR(i,70){ int cs=w.cstat[i]; real ax=w.Ax[i];
-        if(cs==ST_LOWER){ w.lbA[i]=ax; w.Ax_l[i]=real(0.0); w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=fmax(w.y[42+i],real(0.0)); }
-        else if(cs==ST_UPPER){ w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=ax; w.Ax_u[i]=real(0.0); w.y[42+i]=fmin(w.y[42+i],real(0.0)); }
-        else { w.lbA[i]=fmin(w.lbA[i],ax); w.Ax_l[i]=ax-w.lbA[i]; w.ubA[i]=fmax(w.ubA[i],ax); w.Ax_u[i]=w.ubA[i]-ax; w.y[42+i]=real(0.0); } }
+    LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
+        if(LV_IN(i,42)){ int bs=w.bstat[i]; real xi=w.x[i];
+            if(bs==ST_LOWER){ lbi=xi; ubi=fmax(ubi,xi); w.y[i]=fmax(w.y[i],real(0.0)); }
+            else if(bs==ST_UPPER){ lbi=fmin(lbi,xi); ubi=xi; w.y[i]=fmin(w.y[i],real(0.0)); }
+            else { lbi=fmin(lbi,xi); ubi=fmax(ubi,xi); w.y[i]=real(0.0); } }
+        LV_ST(lb,i,sl,lbi); LV_ST(ub,i,sl,ubi); LV_DONE(); }
+    LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_LD(ax,Ax,i,sl); LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi); LV_USE(ax);
+        real al=real(0.0), au=real(0.0);
+        if(LV_IN(i,70)){ int cs=w.cstat[i];
+            if(cs==ST_LOWER){ lbAi=ax; al=real(0.0); ubAi=fmax(ubAi,ax); au=ubAi-ax; w.y[42+i]=fmax(w.y[42+i],real(0.0)); }
+            else if(cs==ST_UPPER){ lbAi=fmin(lbAi,ax); al=ax-lbAi; ubAi=ax; au=real(0.0); w.y[42+i]=fmin(w.y[42+i],real(0.0)); }
+            else { lbAi=fmin(lbAi,ax); al=ax-lbAi; ubAi=fmax(ubAi,ax); au=ubAi-ax; w.y[42+i]=real(0.0); } }
+        LV_ST(lbA,i,sl,lbAi); LV_ST(ubA,i,sl,ubAi); LV_ST(Ax_l,i,sl,al); LV_ST(Ax_u,i,sl,au); LV_DONE(); }
     setupAuxiliaryQPgradient(w,c);
 }
 
@@ -964,7 +1053,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         if(rv!=QP_OK) return false;
         real weight=real(0.0), zero=real(0.0);
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
-        LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; weight=fmax(weight,fabs(w.dyFX[ii])); zero=fmax(zero,fabs(w.dx[ii])); }
+        if(c.nFX>0){ LV_FOR(v,sl,42){ LV_LD(dyv,dyFX,v,sl); LV_WAIT(); LV_USE(dyv); if(LV_IN(v,42)&&w.bstat[v]!=0){ weight=fmax(weight,fabs(dyv)); zero=fmax(zero,fabs(w.dx[v])); } } }
         LANE_FOR(i,nFR) zero=fmax(zero,fabs(w.dx[(int)w.FR[i]]));
         weight=wbc_max(weight); zero=wbc_max(zero);
 #if !defined(__CUDACC__) && defined(WBC_LI_STATS)
@@ -1006,7 +1095,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
         if(rv!=QP_OK) return false;
         real weight=real(0.0), zero=real(0.0);
         LANE_FOR(i,c.nAC) weight=fmax(weight,fabs(w.dyAC[i]));
-        LANE_FOR(i,c.nFX){ int ii=(int)w.FX[i]; weight=fmax(weight,fabs(w.dyFX[ii])); zero=fmax(zero,fabs(w.dx[ii])); }
+        if(c.nFX>0){ LV_FOR(v,sl,42){ LV_LD(dyv,dyFX,v,sl); LV_WAIT(); LV_USE(dyv); if(LV_IN(v,42)&&w.bstat[v]!=0){ weight=fmax(weight,fabs(dyv)); zero=fmax(zero,fabs(w.dx[v])); } } }
         LANE_FOR(i,c.nFR) zero=fmax(zero,fabs(w.dx[(int)w.FR[i]]));
         weight=wbc_max(weight); zero=wbc_max(zero);
 #if !defined(__CUDACC__) && defined(WBC_LI_STATS)
@@ -1027,10 +1116,10 @@ WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBou
     const int lane=c.lane, nAC=c.nAC, nFX=c.nFX;
     real y_min=OPT_maxDualJump; int ymn=-1, ymnb=-1;
     WBC_SYNC();
-    LANE_FOR(i,nAC){ w.num[i]=w.y[42+(int)w.AC[i]]; w.den[i]=w.xFRy[i]; }
+    LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.num[ii]=w.y[42+ii]; w.den[ii]=w.xFRy[i]; }
     performRatioTest(c,nAC,w.AC,w.cstat,w.num,w.den,y_min,ymn);
     WBC_SYNC();
-    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.num[i]=w.y[ii]; w.den[i]=w.Zdz[ii]; }
+    LANE_FOR(i,nFX){ int ii=(int)w.FX[i]; w.num[ii]=w.y[ii]; w.den[ii]=w.Zdz[ii]; }
     performRatioTest(c,nFX,w.FX,w.bstat,w.num,w.den,y_min,ymnb);
     bool ymIsBound=false; if(ymnb>=0){ ymn=ymnb; ymIsBound=true; }
     if(ymn<0){ c.infeasible=1; return QP_RET_HOTSTART_STOPPED_INFEASIBILITY; }
@@ -1266,7 +1355,8 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
         } else if(c.status==QPS_SOLVED){
             const real tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
             LANE_FOR(i,42){ if(fabs(tgt_lb(c,i)-w.x[i])<tol) na++; if(fabs(tgt_ub(c,i)-w.x[i])<tol) na++; }
-            LANE_FOR(i,70){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>(real)c.qg->lbA[i]&&fabs(l-w.Ax[i])<tol) na++; if(u<(real)c.qg->ubA[i]&&fabs(u-w.Ax[i])<tol) na++; }
+            LV_FOR(i,sl,70){ LV_LD(axi,Ax,i,sl); LV_WAIT(); LV_USE(axi);
+                if(LV_IN(i,70)){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>(real)c.qg->lbA[i]&&fabs(l-axi)<tol) na++; if(u<(real)c.qg->ubA[i]&&fabs(u-axi)<tol) na++; } }
             if(wbc_ballot(na>0)==0u) break;
             c.status=QPS_HOMOTOPYQPSOLVED;
             if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
@@ -1280,9 +1370,10 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
 // fixed at its (far) lower bound (initialStatusBounds = ST_LOWER) and no active constraint.
 WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=c.lane; WBC_SYNC();
-    LANE_FOR(i,42){ w.x[i]=real(0.0); w.y[i]=real(0.0); w.g[i]=real(0.0); w.lb[i]=real(0.0); w.ub[i]=OPT_boundRelaxation; w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
-    LANE_FOR(i,70){ w.y[42+i]=real(0.0); w.Ax[i]=real(0.0); w.lbA[i]=-OPT_boundRelaxation; w.ubA[i]=OPT_boundRelaxation; w.Ax_l[i]=OPT_boundRelaxation; w.Ax_u[i]=OPT_boundRelaxation;
-                    w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
+    LANE_FOR(i,42){ w.x[i]=real(0.0); w.y[i]=real(0.0); w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
+    LV_FOR(i,sl,42){ LV_ST(g,i,sl,real(0.0)); LV_ST(lb,i,sl,real(0.0)); LV_ST(ub,i,sl,OPT_boundRelaxation); LV_DONE(); }
+    LANE_FOR(i,70){ w.y[42+i]=real(0.0); w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
+    LV_FOR(i,sl,70){ LV_ST(Ax,i,sl,real(0.0)); LV_ST(lbA,i,sl,-OPT_boundRelaxation); LV_ST(ubA,i,sl,OPT_boundRelaxation); LV_ST(Ax_l,i,sl,OPT_boundRelaxation); LV_ST(Ax_u,i,sl,OPT_boundRelaxation); LV_DONE(); }
     c.nFR=0; c.nFX=42; c.nAC=0; c.nIAC=70; c.frIdentity=0; c.rampOffset=0; c.infeasible=0; c.unbounded=0; c.tau=real(0.0);
     setupTQfactorisation(w,c);
     c.status=QPS_AUXILIARYQPSOLVED;
@@ -1376,7 +1467,10 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
     WBC_FLOPS(4.0*42*42+4.0*70*42);
-    LANE_FOR(i,70){ real ax=Arow_acc(WQP,i,w.x,real(0.0),real(1.0)); w.Ax[i]=ax; real l=-w.Ax_l[i]+ax, u=w.Ax_u[i]+ax; w.lbA[i]=l; w.ubA[i]=u; w.Ax_u[i]=u-ax; w.Ax_l[i]=ax-l; }
+    LV_FOR(i,sl,70){ LV_LD(al,Ax_l,i,sl); LV_LD(au,Ax_u,i,sl); LV_WAIT(); LV_USE(al); LV_USE(au);
+        real ax=real(0.0), l=real(0.0), u=real(0.0);
+        if(LV_IN(i,70)){ ax=Arow_acc(WQP,i,w.x,real(0.0),real(1.0)); l=-al+ax; u=au+ax; au=u-ax; al=ax-l; }
+        LV_ST(Ax,i,sl,ax); LV_ST(lbA,i,sl,l); LV_ST(ubA,i,sl,u); LV_ST(Ax_u,i,sl,au); LV_ST(Ax_l,i,sl,al); LV_DONE(); }
     setupAuxiliaryQPgradient(w,c);
     // old working set (statuses), then everything free / inactive again
     bool anyFixed=false; LANE_FOR(i,42) if(w.bstat[i]!=0) anyFixed=true;
