@@ -165,7 +165,7 @@ constexpr int WBC_TM_ALLOC_COLS= WBC_TM_NEED_COLS<=32?32 : WBC_TM_NEED_COLS<=64?
 static_assert(WBC_TM_NEED_COLS<=512&&WBC_GANG<=16,"tensor memory: 512 columns, 4 lane quarters");
 static_assert((size_t)WBC_GANG*(sizeof(QPWork)+16)+16<=232448,"gang workspace exceeds the 227 KB of shared memory a CTA can have");
 #endif
-__global__ void __launch_bounds__(WBC_QP_THREADS) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int cohort,const QPPre* pre,int* stats){
+__global__ void __launch_bounds__(WBC_QP_THREADS,1) wbc_solve_qp_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int cohort,const QPPre* pre,int* stats){
     extern __shared__ double smem[];
     QPWork& w=*reinterpret_cast<QPWork*>(reinterpret_cast<char*>(smem)+(size_t)(threadIdx.x>>5)*sizeof(QPWork));
     const int lane=threadIdx.x&31;
