@@ -241,6 +241,7 @@ __global__ void __launch_bounds__(WBC_QP_THREADS,1) wbc_solve_qp_kernel(int N,co
             #pragma unroll
             for(int k=0;k<3;k++){ const int i=lane+32*k; const bool in=i<70; ta[k]=in?S.Ax_l[i]:real(0); tb[k]=in?S.Ax_u[i]:real(0); sc[k]=in?S.cstat[i]:(signed char)0; }
             c.rampOffset=S.rampOffset; c.status=S.status;
+            LV_HOIST();
             #pragma unroll
             for(int k=0;k<2;k++){ const int i=lane+32*k; if(i<42){ w.x[i]=tx[k]; w.bstat[i]=sb[k]; } if(WBC_LV_TMEM||i<42){ LV_ST(lb,i,k,tl[k]); LV_ST(ub,i,k,tu[k]); } }
             #pragma unroll

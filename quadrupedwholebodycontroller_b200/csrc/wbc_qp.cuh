@@ -152,17 +152,21 @@ struct QPState {
 #else
   #define WBC_LV_TMEM 0
 #endif
+// What the loops over the lane-owned vectors need from the solver context, copied out once per loop (LV_FOR declares it): the context lives in local memory
+// (its address is passed to non-inlined functions) and every tcgen05.wait / st is a compiler memory barrier, so `c.tm`, `c.farbound`, ... themselves would
+// be re-read (LDL) ahead of every access.
+#define LV_HOIST() const LVHoist lv_h_{c.tm,c.farRampOffset,c.farbound,c.qg}
 enum { LV_g=0, LV_lb=2, LV_ub=4, LV_dyFX=6, LV_lbA=8, LV_ubA=11, LV_Ax=14, LV_Ax_l=17, LV_Ax_u=20, LV_dlbA=23, LV_dubA=26, LV_SLOTS=29 };
 #if WBC_LV_TMEM
-  #define LV_FOR(i,sl,n) _Pragma("unroll") for(int sl=0,i=lane;sl<((n)+31)/32;sl++,i+=32)
+  #define LV_FOR(i,sl,n) if(LV_HOIST(); true) _Pragma("unroll") for(int sl=0,i=lane;sl<((n)+31)/32;sl++,i+=32)
   #define LV_IN(i,n) ((i)<(n))
-  #define LV_LD(v,name,i,sl) real v; wbc_tm_ld(c.tm+WBC_TM_COLS_PER_REAL*(unsigned)(LV_##name+(sl)),v)
+  #define LV_LD(v,name,i,sl) real v; wbc_tm_ld(lv_h_.tm+WBC_TM_COLS_PER_REAL*(unsigned)(LV_##name+(sl)),v)
   #define LV_WAIT() wbc_tm_wait_ld()
   #define LV_USE(v) wbc_tm_use(v)
-  #define LV_ST(name,i,sl,v) wbc_tm_st(c.tm+WBC_TM_COLS_PER_REAL*(unsigned)(LV_##name+(sl)),(v))
+  #define LV_ST(name,i,sl,v) wbc_tm_st(lv_h_.tm+WBC_TM_COLS_PER_REAL*(unsigned)(LV_##name+(sl)),(v))
   #define LV_DONE() wbc_tm_wait_st()
 #else
-  #define LV_FOR(i,sl,n) LANE_FOR(i,n)
+  #define LV_FOR(i,sl,n) if(LV_HOIST(); true) LANE_FOR(i,n)
   #define LV_IN(i,n) true
   #define LV_LD(v,name,i,sl) real v=w.name[i]
   #define LV_WAIT() do{}while(0)
@@ -211,7 +215,15 @@ struct alignas(16) QPPre {
 };
 static_assert(sizeof(QPPre)%16==0&&offsetof(QPPre,T)==42*LD*sizeof(real),"QPPre: Q and T contiguous like QPWork's Q and RT, records 16-byte aligned");
 
+struct LVHoist { unsigned tm; int farRampOffset; real farbound; const QPData* qg; };
 // scalar solver state, replicated in every lane
+// The context is reached by reference from non-inlined functions, so it lives in local memory and every field read is an LDL; the lane number at least
+// comes from the thread index instead (every kernel that runs the solver has lane = threadIdx.x % 32).
+#if defined(__CUDACC__)
+  #define WBC_LANE(c) ((int)(threadIdx.x&31u))
+#else
+  #define WBC_LANE(c) ((c).lane)
+#endif
 struct QPCtx {
     int lane;
     int nFR,nFX,nAC,nIAC;
@@ -304,7 +316,7 @@ WBC_DEV unsigned force_mask(const QPWork& w,const QPCtx& c,int sel){
 #if WBC_NL==1
     (void)c; unsigned m=0u; for(int u=0;u<12;u++) if(sel==2||((w.bstat[18+u]!=0)==(sel==1))) m|=1u<<u; return m;
 #else
-    return wbc_ballot(c.lane<12&&(sel==2||((w.bstat[18+(c.lane<12?c.lane:0)]!=0)==(sel==1))));
+    return wbc_ballot(WBC_LANE(c)<12&&(sel==2||((w.bstat[18+(WBC_LANE(c)<12?WBC_LANE(c):0)]!=0)==(sel==1))));
 #endif
 }
 WBC_FN real Hrow_acc(const QPWork& w,int i,const real* v,int sel,unsigned fm,real y,real sgn){
@@ -316,15 +328,15 @@ WBC_FN real Hrow_acc(const QPWork& w,int i,const real* v,int sel,unsigned fm,rea
     return y+(sgn*((i>=30)?WQP.rho:real(1.0)))*v[i];
 }
 // masked copies: vm = v restricted to free (sel 0) / fixed (sel 1) variables; ym = yAC scattered to constraint numbers
-WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const real* v,int sel){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:real(0.0); WBC_SYNC(); }
-WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const real* yAC){ const int lane=c.lane; WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:real(0.0); WBC_SYNC(); }
+WBC_FN void mask_vars(QPWork& w,const QPCtx& c,const real* v,int sel){ const int lane=WBC_LANE(c); WBC_SYNC(); LANE_FOR(j,42) w.vm[j]=((w.bstat[j]!=0)==(sel==1))?v[j]:real(0.0); WBC_SYNC(); }
+WBC_FN void scatter_yAC(QPWork& w,const QPCtx& c,const real* yAC){ const int lane=WBC_LANE(c); WBC_SYNC(); LANE_FOR(i,70) w.ym[i]=(w.cstat[i]!=0)?yAC[(int)w.posAC[i]]:real(0.0); WBC_SYNC(); }
 
 // ---------------------------------------------------------------- products with Q = [Z Y] (one copy each: instruction cache)
 // out[i] = sgn * sum_j Q(FR[j], col0+i) t[FR[j]],  i < ncols   (t by variable number; lane per column; FR-list order like the reference).
 // A lane owns columns i and i+32 and walks both in the same loop (two independent chains, t loaded once).  While the free list is
 // the identity (c.frIdentity) the list indirection is skipped -- same terms, same order.
 WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const real* t,real sgn,real* out){
-    const int lane=c.lane, nFR=c.nFR;
+    const int lane=WBC_LANE(c), nFR=c.nFR;
 #if WBC_NL==1
     for(int i=0;i<ncols;i++){ const real* q=&w.Q[LD*(col0+i)]; real s=real(0.0); for(int j=0;j<nFR;j++){ const int jj=(int)w.FR[j]; s+=q[jj]*t[jj]; } out[i]=sgn*s; }
 #else
@@ -354,7 +366,7 @@ WBC_FN void Qt_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const rea
 // v = sum_j Q(FR[i], col0+j) x[j] for every free variable FR[i]:  acc[FR[i]] += v,  and keep[FR[i]] = v if keep != null   (lane per row,
 // rows i and i+32 of the list in one loop)
 WBC_FN void Q_times(const QPWork& w,const QPCtx& c,int col0,int ncols,const real* x,real* acc,real* keep){
-    const int lane=c.lane, nFR=c.nFR;
+    const int lane=WBC_LANE(c), nFR=c.nFR;
 #if WBC_NL==1
     for(int i=0;i<nFR;i++){ const int ii=(int)w.FR[i]; const real* q=&w.Q[ii+LD*col0]; real s=real(0.0); for(int j=0;j<ncols;j++) s+=q[LD*j]*x[j]; if(keep) keep[ii]=s; acc[ii]+=s; }
 #else
@@ -393,15 +405,15 @@ WBC_DEV void list_remove(signed char* L,int& n,int number,int lane){
     n--; WBC_SYNC();
 }
 WBC_DEV void list_append(signed char* L,int& n,int number,int lane){ if(lane==0) L[n]=(signed char)number; n++; WBC_SYNC(); }
-WBC_DEV void rebuild_posAC(QPWork& w,const QPCtx& c){ const int lane=c.lane; LANE_FOR(k,c.nAC) w.posAC[(int)w.AC[k]]=(signed char)k; WBC_SYNC(); }
+WBC_DEV void rebuild_posAC(QPWork& w,const QPCtx& c){ const int lane=WBC_LANE(c); LANE_FOR(k,c.nAC) w.posAC[(int)w.AC[k]]=(signed char)k; WBC_SYNC(); }
 
 // Bounds::moveFreeToFixed / moveFixedToFree, Constraints::moveInactiveToActive / moveActiveToInactive (Bounds.cpp, Constraints.cpp)
-WBC_DEV void moveFreeToFixed(QPWork& w,QPCtx& c,int number,int st){ c.frIdentity=0; WBC_SYNC(); list_remove(w.FR,c.nFR,number,c.lane); list_append(w.FX,c.nFX,number,c.lane); if(c.lane==0) w.bstat[number]=(signed char)st; WBC_SYNC(); }
-WBC_DEV void moveFixedToFree(QPWork& w,QPCtx& c,int number){ c.frIdentity=0; WBC_SYNC(); list_remove(w.FX,c.nFX,number,c.lane); list_append(w.FR,c.nFR,number,c.lane); if(c.lane==0) w.bstat[number]=0; WBC_SYNC(); }
-WBC_DEV void moveInactiveToActive(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.IAC,c.nIAC,number,c.lane); if(c.lane==0){ w.cstat[number]=(signed char)st; w.posAC[number]=(signed char)c.nAC; } list_append(w.AC,c.nAC,number,c.lane); }
-WBC_DEV void moveActiveToInactive(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); list_remove(w.AC,c.nAC,number,c.lane); list_append(w.IAC,c.nIAC,number,c.lane); if(c.lane==0) w.cstat[number]=0; WBC_SYNC(); rebuild_posAC(w,c); }
+WBC_DEV void moveFreeToFixed(QPWork& w,QPCtx& c,int number,int st){ c.frIdentity=0; WBC_SYNC(); list_remove(w.FR,c.nFR,number,WBC_LANE(c)); list_append(w.FX,c.nFX,number,WBC_LANE(c)); if(WBC_LANE(c)==0) w.bstat[number]=(signed char)st; WBC_SYNC(); }
+WBC_DEV void moveFixedToFree(QPWork& w,QPCtx& c,int number){ c.frIdentity=0; WBC_SYNC(); list_remove(w.FX,c.nFX,number,WBC_LANE(c)); list_append(w.FR,c.nFR,number,WBC_LANE(c)); if(WBC_LANE(c)==0) w.bstat[number]=0; WBC_SYNC(); }
+WBC_DEV void moveInactiveToActive(QPWork& w,QPCtx& c,int number,int st){ WBC_SYNC(); list_remove(w.IAC,c.nIAC,number,WBC_LANE(c)); if(WBC_LANE(c)==0){ w.cstat[number]=(signed char)st; w.posAC[number]=(signed char)c.nAC; } list_append(w.AC,c.nAC,number,WBC_LANE(c)); }
+WBC_DEV void moveActiveToInactive(QPWork& w,QPCtx& c,int number){ WBC_SYNC(); list_remove(w.AC,c.nAC,number,WBC_LANE(c)); list_append(w.IAC,c.nIAC,number,WBC_LANE(c)); if(WBC_LANE(c)==0) w.cstat[number]=0; WBC_SYNC(); rebuild_posAC(w,c); }
 // Indexlist::swapNumbers on the free list (Bounds::swapFree)
-WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ c.frIdentity=0; WBC_SYNC(); if(c.lane==0){ int a=0,b=0; while(w.FR[a]!=n1) a++; while(w.FR[b]!=n2) b++; signed char t=w.FR[a]; w.FR[a]=w.FR[b]; w.FR[b]=t; } WBC_SYNC(); }
+WBC_DEV void swapFree(QPWork& w,QPCtx& c,int n1,int n2){ c.frIdentity=0; WBC_SYNC(); if(WBC_LANE(c)==0){ int a=0,b=0; while(w.FR[a]!=n1) a++; while(w.FR[b]!=n2) b++; signed char t=w.FR[a]; w.FR[a]=w.FR[b]; w.FR[b]=t; } WBC_SYNC(); }
 
 // ---------------------------------------------------------------- triangular solves
 // Forward substitution L u = b,  u_k = (b[k*bs] - sum_{j<k} L(k,j) u_j) * rd[k*rs],  a[k*as] = u_k, for the four triangular
@@ -462,7 +474,7 @@ WBC_FN void trisolve(int lane,int kind,int n,const real* RT,const real* b,int bs
 }
 // reciprocals of T's diagonal TT(k, sizeT-1-k); false if a pivot fails the |.| > EPS test of QProblem::backsolveT
 WBC_FN bool prepare_T(QPWork& w,const QPCtx& c){
-    const int lane=c.lane; bool bad=false; WBC_SYNC();
+    const int lane=WBC_LANE(c); bool bad=false; WBC_SYNC();
     LANE_FOR(k,c.nAC){ const real d=TT(k,SIZET-1-k); if(!(fabs(d)>QEPS)) bad=true; w.rdT[k]=WBC_RDIAG(d); }
     WBC_SYNC();
     return wbc_ballot(bad)==0u;
@@ -472,28 +484,28 @@ WBC_FN bool prepare_T(QPWork& w,const QPCtx& c){
 WBC_DEV void backsolveT(QPWork& w,const QPCtx& c,const real* b,bool transposed,real* a){
     const int nT=c.nAC;
     if(nT<=0) return;
-    if(!transposed) trisolve(c.lane,0,nT,w.RT,b,1,a+nT-1,-1,w.rdT,1);
-    else            trisolve(c.lane,1,nT,w.RT,b,1,a+nT-1,-1,w.rdT+nT-1,-1);
+    if(!transposed) trisolve(WBC_LANE(c),0,nT,w.RT,b,1,a+nT-1,-1,w.rdT,1);
+    else            trisolve(WBC_LANE(c),1,nT,w.RT,b,1,a+nT-1,-1,w.rdT+nT-1,-1);
 }
 // QProblemB::backsolveR (QProblemB.cpp:1635-1688) on the nR x nR upper-triangular R; a may alias b.  w.rdR = 1/diag(R).
 WBC_DEV void backsolveR(QPWork& w,const QPCtx& c,const real* b,bool transposed,real* a,int nR){
     if(nR<=0) return;
-    if(transposed){ trisolve(c.lane,2,nR,w.RT,b,1,a,1,w.rdR,1); return; }
+    if(transposed){ trisolve(WBC_LANE(c),2,nR,w.RT,b,1,a,1,w.rdR,1); return; }
 #if defined(WBC_EXACT_BACKSUB)
     // The reference's back substitution subtracts the terms of row i in ASCENDING column order j = i+1 .. nR-1, i.e. starting with the unknown
     // it has only just computed: a serial chain of nR^2/2 operations that the streaming form below (terms in the order the unknowns become
     // available: j = nR-1 down to i+1) re-orders.  Exact build: the serial form, every lane redundantly, lane 0 stores.
-    { const int lane=c.lane; WBC_SYNC();
+    { const int lane=WBC_LANE(c); WBC_SYNC();
       for(int i=nR-1;i>=0;--i){ real sum=b[i]; for(int j=i+1;j<nR;++j) sum-=RR(i,j)*a[j]; const real v=WBC_BYDIAG(sum,w.rdR[i]); WBC_SYNC(); if(lane==0) a[i]=v; WBC_SYNC(); } }
 #else
-    trisolve(c.lane,3,nR,w.RT,b+nR-1,-1,a+nR-1,-1,w.rdR+nR-1,-1);
+    trisolve(WBC_LANE(c),3,nR,w.RT,b+nR-1,-1,a+nR-1,-1,w.rdR+nR-1,-1);
 #endif
 }
 
 // ---------------------------------------------------------------- factorisations
 // QProblem::setupTQfactorisation (QProblem.cpp:2169-2193)
 WBC_DEV void setupTQfactorisation(QPWork& w,const QPCtx& c){
-    const int lane=c.lane; WBC_SYNC();
+    const int lane=WBC_LANE(c); WBC_SYNC();
     LANE_FOR(e,42*LD) w.Q[e]=real(0.0);                     // packed T needs no clearing: every entry of a row is written when the row is created
     WBC_SYNC();
     LANE_FOR(i,c.nFR) QQ((int)w.FR[i],i)=real(1.0);
@@ -503,7 +515,7 @@ WBC_DEV void setupTQfactorisation(QPWork& w,const QPCtx& c){
 // inner product runs k = i-1 .. 0 like the reference; the diagonal's sum travels by one shuffle from the lane that owns column i.
 // returns false if not SPD.
 WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     WBC_SYNC();
 #if WBC_NL==1
     for(int i=0;i<n;i++){
@@ -546,7 +558,7 @@ WBC_DEV bool potrf_R(QPWork& w,const QPCtx& c,int n){
 // summation order as the scalar loops of SymDenseMat::bilinear (Matrices.cpp:630-667).
 WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
     constexpr int TS=4;
-    const int lane=c.lane, nt=(nZ+TS-1)/TS, ntiles=nt*(nt+1)/2;
+    const int lane=WBC_LANE(c), nt=(nZ+TS-1)/TS, ntiles=nt*(nt+1)/2;
     LANE_FOR(t,ntiles){
         int ti=0, rem=t; while(rem>=nt-ti){ rem-=nt-ti; ti++; } const int tj=ti+rem;
         real acc[TS][TS];
@@ -578,12 +590,12 @@ WBC_DEV void zhz_tiles(QPWork& w,const QPCtx& c,int nFR,int nZ){
 }
 // the two cases without an active constraint (first iterations of a cold start): R'R = H_FR,FR directly
 WBC_FN void fill_R_with_H(QPWork& w,const QPCtx& c){
-    const int lane=c.lane, nFR=c.nFR;
+    const int lane=WBC_LANE(c), nFR=c.nFR;
     LANE_FOR(j,nFR) for(int i=0;i<=j;i++) RR(i,j)=Hel(WQP,(int)w.FR[i],(int)w.FR[j]);
 }
 // QProblem::computeProjectedCholesky (QProblem.cpp:2036-2129) incl. the QProblemB::computeCholesky fallback (:1366-1446)
 WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
-    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_FLOPS(2.0*nFR*nFR*nZ+2.0*nFR*nZ*nZ+(double)nZ*nZ*nZ/3.0);
     WBC_SYNC();
     if(nZ==0&&c.nFX+c.nAC!=0) return QP_OK;
@@ -621,7 +633,7 @@ WBC_FN int computeProjectedCholesky(QPWork& w,QPCtx& c){
 // same values (a lane only ever reads back what it wrote itself: no synchronisation inside the chain).  Saves the (nZ^2/2) x nFR tile products of Z'HZ and
 // nZ-1 square roots / divisions on more than half of the iterations of a cold start.  Needs nAC > 0 (with nAC == 0 the reference re-trivialises Z).
 WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
-    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC, n=nZ-1;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nZ=c.nFR-c.nAC, n=nZ-1;
     WBC_FLOPS(2.0*nFR*nFR*nZ+2.0*nFR*nZ*nZ+(double)nZ*nZ*nZ/3.0);      // algorithmic count of the reference, which recomputes everything
     WBC_SYNC();
     int nff=0; int* ffl=reinterpret_cast<int*>(w.rdT);
@@ -657,11 +669,11 @@ WBC_FN int extendProjectedCholesky(QPWork& w,QPCtx& c){
 // Data shift of the gradient and of the (far) bounds on x, QProblemB::determineDataShift (QProblemB.cpp:1694-1750): delta = target - current.  They are
 // functions of the current g / lb / ub, the new gradient and the far bound, so they are re-evaluated where they are used instead of being kept in
 // 1 KB of shared memory (what decides whether an SM holds 5 or 6 robots); g, lb and ub only change in the update of performStep, which reads them last.
-WBC_DEV real far_rv(const QPCtx& c,int idx);
+template<class C> WBC_DEV real far_rv(const C& c,int idx);
 WBC_DEV real g_target(const QPWork& w,int i){ return (i>=18&&i<30)?WQP.gf[i-18]:real(0.0); }
 #define SHIFT_DG(i,gi)   (g_target(w,i)-(gi))        /* gi, lbi, ubi = the current g[i], lb[i], ub[i] (lane-owned vectors: loaded by the caller) */
-#define SHIFT_DLB(i,lbi) (-far_rv(c,i)-(lbi))
-#define SHIFT_DUB(i,ubi) (far_rv(c,i)-(ubi))
+#define SHIFT_DLB(i,lbi) (-far_rv(lv_h_,i)-(lbi))
+#define SHIFT_DUB(i,ubi) (far_rv(lv_h_,i)-(ubi))
 
 // ---------------------------------------------------------------- step direction
 // QProblem::determineStepDirection (QProblem.cpp:4637-4975), HST_POSDEF branch.
@@ -670,7 +682,7 @@ WBC_DEV real g_target(const QPWork& w,int i){ return (i>=18&&i<30)?WQP.gf[i-18]:
 // `dg` != null: the given gradient shift and no shift of bounds / constraint bounds (linear-independence tests); `dg` == null: the homotopy's own data shift
 WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
                                   bool bCzero,bool bBzero){
-    const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nZ=nFR-nAC;
     if(!prepare_T(w,c)) return QP_RET_STEPDIRECTION_FAILED_TQ;
     const unsigned ffm=force_mask(w,c,0), fxm=force_mask(w,c,1);
     // I) delta_xFX
@@ -766,7 +778,7 @@ WBC_FN int determineStepDirection(QPWork& w,QPCtx& c,const real* dg,
 // num / den are indexed by the NUMBER of the variable / constraint (idx[i]); the scan runs in list order.
 WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const signed char* stat,const real* num,const real* den,
                               real& t,int& BC_idx){
-    const int lane=c.lane; BC_idx=-1; int pos=0;
+    const int lane=WBC_LANE(c); BC_idx=-1; int pos=0;
     WBC_SYNC();
     for(;;){
         int found=-1;
@@ -790,20 +802,20 @@ WBC_FN void performRatioTest(const QPCtx& c,int n,const signed char* idx,const s
 // Targets of the current homotopy = the user's data with every infinite side replaced by a far bound (QProblem::updateFarBounds,
 // QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246: +-farbound*(1+ramp(i)), ramp offset as of the call).  There are no user bounds on
 // x; the targets are functions of (index, farbound, offset) and are evaluated where needed instead of being stored.
-WBC_DEV real far_rv(const QPCtx& c,int idx){ const int nRamp=42+70; const real t=(real)((idx+c.farRampOffset)%nRamp)/(real)(nRamp-1);
+template<class C> WBC_DEV real far_rv(const C& c,int idx){ const int nRamp=42+70; const real t=(real)((idx+c.farRampOffset)%nRamp)/(real)(nRamp-1);
     return c.farbound*(real(1.0)+(real(1.0)-t)*OPT_ramp0+t*OPT_ramp1); }
 WBC_DEV real tgt_lb(const QPCtx& c,int i){ return -far_rv(c,i); }
 WBC_DEV real tgt_ub(const QPCtx& c,int i){ return far_rv(c,i); }
-WBC_DEV real tgt_lbA(const QPWork& w,const QPCtx& c,int i){ return fmax(-far_rv(c,42+i),(real)c.qg->lbA[i]); }
-WBC_DEV real tgt_ubA(const QPWork& w,const QPCtx& c,int i){ return fmin(far_rv(c,42+i),(real)c.qg->ubA[i]); }
+template<class C> WBC_DEV real tgt_lbA(const QPWork& w,const C& c,int i){ return fmax(-far_rv(c,42+i),(real)c.qg->lbA[i]); }
+template<class C> WBC_DEV real tgt_ubA(const QPWork& w,const C& c,int i){ return fmin(far_rv(c,42+i),(real)c.qg->ubA[i]); }
 // QProblem::determineDataShift (QProblem.cpp:4571-4631) + QProblemB (:1694-1750); targets are WQP.gf (g_new) and the far-bounded data
 WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzero){
-    const int lane=c.lane; WBC_SYNC();
+    const int lane=WBC_LANE(c); WBC_SYNC();
     bool nzC=false, nzB=false;
     // the shift of an ACTIVE constraint's bound is also left by AC position in w.arow (dead between two working-set changes): what determineStepDirection reads
     LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi);
         real dl=real(0.0), du=real(0.0);
-        if(LV_IN(i,70)){ const real rv=far_rv(c,42+i); dl=fmax(-rv,(real)c.qg->lbA[i])-lbAi; du=fmin(rv,(real)c.qg->ubA[i])-ubAi;
+        if(LV_IN(i,70)){ const real rv=far_rv(lv_h_,42+i); dl=fmax(-rv,(real)lv_h_.qg->lbA[i])-lbAi; du=fmin(rv,(real)lv_h_.qg->ubA[i])-ubAi;
             const int cs=w.cstat[i];
             if(cs!=0){ if(fabs(dl)>QEPS||fabs(du)>QEPS) nzC=true; w.arow[(int)w.posAC[i]]=(cs==ST_LOWER)?dl:du; } }
         LV_ST(dlbA,i,sl,dl); LV_ST(dubA,i,sl,du); LV_DONE(); }
@@ -816,17 +828,17 @@ WBC_FN void determineDataShift(QPWork& w,const QPCtx& c,bool& bCzero,bool& bBzer
 // QProblem::getRelativeHomotopyLength (QProblem.cpp:5372-5410, QProblemB.cpp:2113-2157) is only ever compared with the termination
 // tolerance: max_i |d_i|/s_i <= tol  <=>  no |d_i| > tol*s_i -- evaluated in that form (no fp64 divisions), s_i = max(|target_i|,1).
 WBC_FN bool homotopyFinished(const QPWork& w,const QPCtx& c){
-    const int lane=c.lane; const real tol=OPT_terminationTolerance; bool over=false;
+    const int lane=WBC_LANE(c); const real tol=OPT_terminationTolerance; bool over=false;
     LV_FOR(i,sl,42){ LV_LD(gi,g,i,sl); LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(gi); LV_USE(lbi); LV_USE(ubi);
         if(LV_IN(i,42)){ const real gn=g_target(w,i); if(fabs(gn-gi)>tol*fmax(fabs(gn),real(1.0))) over=true;
-                         const real rv=far_rv(c,i), s=tol*fmax(rv,real(1.0)); if(fabs(-rv-lbi)>s||fabs(rv-ubi)>s) over=true; } }
+                         const real rv=far_rv(lv_h_,i), s=tol*fmax(rv,real(1.0)); if(fabs(-rv-lbi)>s||fabs(rv-ubi)>s) over=true; } }
     LV_FOR(i,sl,70){ LV_LD(lbAi,lbA,i,sl); LV_LD(ubAi,ubA,i,sl); LV_WAIT(); LV_USE(lbAi); LV_USE(ubAi);
-        if(LV_IN(i,70)){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(fabs(l-lbAi)>tol*fmax(fabs(l),real(1.0))||fabs(u-ubAi)>tol*fmax(fabs(u),real(1.0))) over=true; } }
+        if(LV_IN(i,70)){ const real l=tgt_lbA(w,lv_h_,i), u=tgt_ubA(w,lv_h_,i); if(fabs(l-lbAi)>tol*fmax(fabs(l),real(1.0))||fabs(u-ubAi)>tol*fmax(fabs(u),real(1.0))) over=true; } }
     return wbc_ballot(over)==0u;
 }
 // QProblem::setupAuxiliaryQPgradient (QProblem.cpp:2602-2641): g = y_B - H x + A' y_C
 WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
-    const int lane=c.lane; WBC_SYNC();
+    const int lane=WBC_LANE(c); WBC_SYNC();
     LV_FOR(i,sl,42){ real t=real(0.0);
         if(LV_IN(i,42)){ t=w.y[i]; t=Hrow_acc(w,i,w.x,2,0xfffu,t,-real(1.0)); t=Acol_acc(WQP,i,w.y+42,t,real(1.0)); }
         LV_ST(g,i,sl,t); LV_DONE(); }
@@ -834,7 +846,7 @@ WBC_FN void setupAuxiliaryQPgradient(QPWork& w,const QPCtx& c){
 }
 // QProblem::performStep (QProblem.cpp:4981-5278)
 WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_isBound){
-    const int lane=c.lane, nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nIAC=c.nIAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nFX=c.nFX, nAC=c.nAC, nIAC=c.nIAC;
     c.tau=real(1.0); BC_idx=-1; BC_status=2 /*ST_UNDEFINED*/; BC_isBound=false; int tmp;
     WBC_FLOPS(2.0*nIAC*42.0+10.0*(42+70));
     WBC_SYNC();
@@ -881,7 +893,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
         LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.y[42+ii]+=tau*w.dyAC[i]; }
         LV_FOR(v,sl,42){ LV_LD(gv,g,v,sl); LV_LD(lbv,lb,v,sl); LV_LD(ubv,ub,v,sl); LV_LD(dyv,dyFX,v,sl); LV_WAIT(); LV_USE(gv); LV_USE(lbv); LV_USE(ubv); LV_USE(dyv);
             if(LV_IN(v,42)){ if(w.bstat[v]!=0){ w.x[v]+=tau*w.dx[v]; w.y[v]+=tau*dyv; }
-                const real rv=far_rv(c,v); gv+=tau*SHIFT_DG(v,gv); lbv+=tau*(-rv-lbv); ubv+=tau*(rv-ubv); }
+                const real rv=far_rv(lv_h_,v); gv+=tau*SHIFT_DG(v,gv); lbv+=tau*(-rv-lbv); ubv+=tau*(rv-ubv); }
             LV_ST(g,v,sl,gv); LV_ST(lb,v,sl,lbv); LV_ST(ub,v,sl,ubv); LV_DONE(); }
         WBC_SYNC();
         // A x of the active constraints by number into w.num (the ratio tests are over), then one pass over the 70 constraints
@@ -898,7 +910,7 @@ WBC_FN void performStep(QPWork& w,QPCtx& c,int& BC_idx,int& BC_status,bool& BC_i
 }
 // QProblem::performRamping (QProblem.cpp:5416-5492); all bounds and constraints are typed ST_BOUNDED on this path
 WBC_FN void performRamping(QPWork& w,QPCtx& c){
-    const int lane=c.lane, nRamp=42+70+70+42; WBC_SYNC();
+    const int lane=WBC_LANE(c), nRamp=42+70+70+42; WBC_SYNC();
     LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
         if(LV_IN(i,42)){
             real tP=(real)((i+c.rampOffset)%nRamp)/(real)(nRamp-1), rP=(real(1.0)-tP)*OPT_ramp0+tP*OPT_ramp1;
@@ -930,7 +942,7 @@ WBC_FN void performRamping(QPWork& w,QPCtx& c){
 }
 // QProblem::performDriftCorrection (QProblem.cpp:5559-5652)
 WBC_FN void performDriftCorrection(QPWork& w,QPCtx& c){
-    const int lane=c.lane; WBC_SYNC();
+    const int lane=WBC_LANE(c); WBC_SYNC();
     LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
         if(LV_IN(i,42)){ int bs=w.bstat[i]; real xi=w.x[i];
             if(bs==ST_LOWER){ lbi=xi; ubi=fmax(ubi,xi); w.y[i]=fmax(w.y[i],real(0.0)); }
@@ -960,7 +972,7 @@ WBC_DEV void computeGivens(real xold,real yold,real& xnew,real& ynew,real& cc,re
 WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
     // The recurrence t_j = hypot(w[j+1], t_{j-1}) of the reference's loop is t_j = sgn(w[j+1]) |w[0..j+1]|_2, so every
     // rotation follows from prefix sums of squares: one lane per rotation, no serial sqrt/divide chain.
-    const int lane=c.lane; WBC_SYNC();
+    const int lane=WBC_LANE(c); WBC_SYNC();
 #if defined(WBC_EXACT_GIVENS)
     { // the reference's serial recurrence (QProblem.cpp:2909-2925, 3401-3450): rotation j is computed from (wv[j+1], result of rotation j-1); every lane
       // evaluates it redundantly, lane 0 stores
@@ -987,7 +999,7 @@ WBC_FN void givens_chain(QPWork& w,const QPCtx& c,int nrot){
     WBC_SYNC();
 }
 WBC_FN void apply_chain_Q(QPWork& w,const QPCtx& c,int nrot,int nrows){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
 #if WBC_NL==1
     for(int i=0;i<nrows;i++){ int ii=(int)w.FR[i]; real qa=QQ(ii,0);
         for(int j=0;j<nrot;j++){ real qb=QQ(ii,j+1), cc=w.cs_c[j], ss=w.cs_s[j]; QQ(ii,j)=-ss*qb+cc*qa; qa=cc*qb+ss*qa; }
@@ -1028,7 +1040,7 @@ WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number);
 
 // QProblem::addConstraint_checkLI (QProblem.cpp:2982-3106): returns true if linearly independent
 WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
-    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_SYNC();
     if(fullTest){
         int shortcut=-1; (void)shortcut;
@@ -1075,7 +1087,7 @@ WBC_FN bool addConstraint_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
 }
 // QProblem::addBound_checkLI (QProblem.cpp:3487-3590)
 WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
-    const int lane=c.lane, nZ=c.nFR-c.nAC;
+    const int lane=WBC_LANE(c), nZ=c.nFR-c.nAC;
     WBC_SYNC();
     if(fullTest){
         int shortcut=-1; (void)shortcut;
@@ -1113,7 +1125,7 @@ WBC_FN bool addBound_checkLI(QPWork& w,QPCtx& c,int number,bool fullTest){
 // common tail of addConstraint_ensureLI / addBound_ensureLI (QProblem.cpp:3178-3300, 3658-3775): xiC in w.xFRy (AC position),
 // xiB in w.Zdz (variable number).  returns QP_OK, or QP_RET_HOTSTART_STOPPED_INFEASIBILITY if no index can leave.
 WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBound){
-    const int lane=c.lane, nAC=c.nAC, nFX=c.nFX;
+    const int lane=WBC_LANE(c), nAC=c.nAC, nFX=c.nFX;
     real y_min=OPT_maxDualJump; int ymn=-1, ymnb=-1;
     WBC_SYNC();
     LANE_FOR(i,nAC){ int ii=(int)w.AC[i]; w.num[ii]=w.y[42+ii]; w.den[ii]=w.xFRy[i]; }
@@ -1137,7 +1149,7 @@ WBC_FN int ensureLI_exchange(QPWork& w,QPCtx& c,int number,int status,bool isBou
 }
 // QProblem::addConstraint_ensureLI (QProblem.cpp:3117-3300)
 WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     if(addConstraint_checkLI(w,c,number,true)) return QP_OK;
     const int nFR=c.nFR, nAC=c.nAC, nFX=c.nFX, nZ=nFR-nAC; const real sg=(C_status==ST_LOWER)?real(1.0):-real(1.0);
     WBC_SYNC();
@@ -1155,7 +1167,7 @@ WBC_FN int addConstraint_ensureLI(QPWork& w,QPCtx& c,int number,int C_status){
 }
 // QProblem::addBound_ensureLI (QProblem.cpp:3596-3780)
 WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     if(addBound_checkLI(w,c,number,true)) return QP_OK;
     const int nAC=c.nAC, nFX=c.nFX, nZ=c.nFR-nAC; const real sg=(B_status==ST_LOWER)?real(1.0):-real(1.0);
     WBC_SYNC();
@@ -1172,7 +1184,7 @@ WBC_FN int addBound_ensureLI(QPWork& w,QPCtx& c,int number,int B_status){
 
 // QProblem::addConstraint (QProblem.cpp:2819-2975), second half: w.wv = aFR' [Z Y] is given; new row of T, Givens chain on Z, index lists
 WBC_FN void addConstraint_tail(QPWork& w,QPCtx& c,int number,int C_status){
-    const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     LANE_FOR(j,nAC) TT(nAC,tcol+j)=w.wv[nZ+j];
     WBC_SYNC();
@@ -1184,7 +1196,7 @@ WBC_FN void addConstraint_tail(QPWork& w,QPCtx& c,int number,int C_status){
     moveInactiveToActive(w,c,number,C_status);
 }
 WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateCholesky,bool ensureLI){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     if(updateCholesky&&ensureLI){ int rv=addConstraint_ensureLI(w,c,number,C_status); if(rv!=QP_OK) return rv; }
     WBC_SYNC();
     // row [wZ wY] = aFR' [Z Y]
@@ -1198,7 +1210,7 @@ WBC_FN int addConstraint(QPWork& w,QPCtx& c,int number,int C_status,bool updateC
 // (addConstraint_checkLI, QProblem.cpp:3081-3105) and addConstraint without LI exchange.  Both need aFR'Z; it is computed once
 // (the first nZ entries of aFR'[Z Y] are the very same sums).
 template<class QD> WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,const QD& qd,int number,int C_status){
-    const int lane=c.lane, nFR=c.nFR, nZ=c.nFR-c.nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nZ=c.nFR-c.nAC;
     WBC_SYNC();
     LANE_FOR(j,42) w.arow[j]=Ael_dev(qd,number,j);
     WBC_SYNC();
@@ -1214,7 +1226,7 @@ template<class QD> WBC_FN void setup_readd_constraint(QPWork& w,QPCtx& c,const Q
 }
 // QProblem::addBound (QProblem.cpp:3307-3480)
 WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholesky,bool ensureLI){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     if(updateCholesky&&ensureLI){ int rv=addBound_ensureLI(w,c,number,B_status); if(rv!=QP_OK) return rv; }
     const int nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
@@ -1239,7 +1251,7 @@ WBC_FN int addBound(QPWork& w,QPCtx& c,int number,int B_status,bool updateCholes
 }
 // QProblem::removeConstraint (QProblem.cpp:3782-4012) without NZC test / flipper / R update (see file header)
 WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
-    const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     WBC_SYNC();
     const int number_idx=(int)w.posAC[number];
@@ -1262,7 +1274,7 @@ WBC_FN int removeConstraint(QPWork& w,QPCtx& c,int number){
 }
 // QProblem::removeBound (QProblem.cpp:4018-4252) without NZC test / flipper / R update (see file header)
 WBC_FN int removeBound(QPWork& w,QPCtx& c,int number){
-    const int lane=c.lane, nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
+    const int lane=WBC_LANE(c), nFR=c.nFR, nAC=c.nAC, nZ=nFR-nAC, tcol=SIZET-nAC;
     WBC_FLOPS(6.0*nFR*nZ+3.0*nZ*nZ+2.0*nFR*42.0);
     moveFixedToFree(w,c,number);
     LANE_FOR(i,nFR){ int ii=(int)w.FR[i]; QQ(ii,nFR)=real(0.0); QQ(number,i)=real(0.0); }
@@ -1289,8 +1301,8 @@ WBC_FN int changeActiveSet(QPWork& w,QPCtx& c,int BC_idx,int BC_status,bool BC_i
     int rv=QP_OK;
     if(BC_status==2) return QP_OK;
     if(BC_status==ST_INACTIVE){
-        if(BC_isBound){ rv=removeBound(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[BC_idx]=real(0.0); }
-        else { rv=removeConstraint(w,c,BC_idx); if(rv!=QP_OK) return rv; if(c.lane==0) w.y[42+BC_idx]=real(0.0); }
+        if(BC_isBound){ rv=removeBound(w,c,BC_idx); if(rv!=QP_OK) return rv; if(WBC_LANE(c)==0) w.y[BC_idx]=real(0.0); }
+        else { rv=removeConstraint(w,c,BC_idx); if(rv!=QP_OK) return rv; if(WBC_LANE(c)==0) w.y[42+BC_idx]=real(0.0); }
         WBC_SYNC();
     } else {
         if(BC_isBound) rv=addBound(w,c,BC_idx,BC_status,true,true);
@@ -1339,7 +1351,7 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
 }
 // QProblem::hotstart (QProblem.cpp:446-640): far-bound outer loop
 WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
-    const int lane=c.lane; const int nWSR_max=nWSR; int nWSR_performed=0;
+    const int lane=WBC_LANE(c); const int nWSR_max=nWSR; int nWSR_performed=0;
     real farbound=OPT_initialFarBounds;
     { real m=real(0.0); LANE_FOR(i,70){ real u=(real)c.qg->ubA[i], l=(real)c.qg->lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
     updateFarBounds(w,c,farbound);
@@ -1356,7 +1368,7 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
             const real tol=farbound/OPT_growFarBounds*OPT_boundTolerance; int na=0;
             LANE_FOR(i,42){ if(fabs(tgt_lb(c,i)-w.x[i])<tol) na++; if(fabs(tgt_ub(c,i)-w.x[i])<tol) na++; }
             LV_FOR(i,sl,70){ LV_LD(axi,Ax,i,sl); LV_WAIT(); LV_USE(axi);
-                if(LV_IN(i,70)){ const real l=tgt_lbA(w,c,i), u=tgt_ubA(w,c,i); if(l>(real)c.qg->lbA[i]&&fabs(l-axi)<tol) na++; if(u<(real)c.qg->ubA[i]&&fabs(u-axi)<tol) na++; } }
+                if(LV_IN(i,70)){ const real l=tgt_lbA(w,lv_h_,i), u=tgt_ubA(w,lv_h_,i); if(l>(real)lv_h_.qg->lbA[i]&&fabs(l-axi)<tol) na++; if(u<(real)lv_h_.qg->ubA[i]&&fabs(u-axi)<tol) na++; } }
             if(wbc_ballot(na>0)==0u) break;
             c.status=QPS_HOMOTOPYQPSOLVED;
             if(farbound>=QINFTY){ c.unbounded=1; rv=QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS; break; }
@@ -1369,7 +1381,7 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
 // SQProblem/QProblem::init -> solveInitialQP (QProblem.cpp:316-368, 1301-1471): cold start from x = y = 0 with every variable
 // fixed at its (far) lower bound (initialStatusBounds = ST_LOWER) and no active constraint.
 WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
-    const int lane=c.lane; WBC_SYNC();
+    const int lane=WBC_LANE(c); WBC_SYNC();
     LANE_FOR(i,42){ w.x[i]=real(0.0); w.y[i]=real(0.0); w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
     LV_FOR(i,sl,42){ LV_ST(g,i,sl,real(0.0)); LV_ST(lb,i,sl,real(0.0)); LV_ST(ub,i,sl,OPT_boundRelaxation); LV_DONE(); }
     LANE_FOR(i,70){ w.y[42+i]=real(0.0); w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
@@ -1391,7 +1403,7 @@ WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
 // cheap LI test and no LI exchange.  Touches only the prefix of the workspace (Q, T, lists, Givens vectors, arow) and reads the QP
 // data through `qd`, so it also runs as a kernel of its own with 9 robots per SM (wbc_warm_setup_kernel).
 template<class QD> WBC_FN void rebuild_TQ(QPWork& w,QPCtx& c,const QD& qd,const signed char* old){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     LANE_FOR(i,42){ w.FR[i]=(signed char)i; }
     LANE_FOR(i,70){ w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; }
     WBC_SYNC();
@@ -1406,7 +1418,7 @@ template<class QD> WBC_FN void rebuild_TQ(QPWork& w,QPCtx& c,const QD& qd,const 
 // store / load of the rebuilt factorisation (HBM, coalesced: consecutive lanes, consecutive doubles).  Loads are issued in batches ahead of the
 // shared stores (see the prologue of wbc_solve_qp_kernel).
 WBC_DEV void store_prebuilt_TQ(const QPWork& w,const QPCtx& c,QPPre& p){
-    const int lane=c.lane, nT=tri(c.nAC);
+    const int lane=WBC_LANE(c), nT=tri(c.nAC);
     LANE_FOR(i,42*LD) p.Q[i]=w.Q[i];
     LANE_FOR(i,nT) p.T[i]=w.RT[i];
     LANE_FOR(i,70){ p.AC[i]=w.AC[i]; p.IAC[i]=w.IAC[i]; p.cstat[i]=w.cstat[i]; p.posAC[i]=w.posAC[i]; }
@@ -1417,7 +1429,7 @@ WBC_DEV void store_prebuilt_TQ(const QPWork& w,const QPCtx& c,QPPre& p){
     }
 }
 WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     c.nFR=42; c.nFX=0; c.nAC=p.nAC; c.nIAC=p.nIAC; c.frIdentity=1; WBC_FLOPS(p.flops);
     const int nT=tri(c.nAC);
 #if WBC_NL==1
@@ -1463,7 +1475,7 @@ WBC_DEV void load_prebuilt_TQ(QPWork& w,QPCtx& c,const QPPre& p){
 // SQProblem::hotstart -> setupNewAuxiliaryQP (SQProblem.cpp:153-197, 340-515) then QProblem::hotstart.
 // On entry w.x, w.y, w.lb, w.ub, w.Ax_l, w.Ax_u, w.bstat, w.cstat hold the previous tick's solver state.
 WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
-    const int lane=c.lane;
+    const int lane=WBC_LANE(c);
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PREPARINGAUXILIARYQP; WBC_SYNC();
     WBC_FLOPS(4.0*42*42+4.0*70*42);
