@@ -417,7 +417,12 @@ def main():
     torch.cuda.set_device(local); dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout when the communicator is created: keep stdout for the ONE JSON line
+        sys.stdout.flush(); saved = os.dup(1); os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev); dist.barrier()
+        finally:
+            os.dup2(saved, 1); os.close(saved)
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     ncu_path = os.path.join(ROOT, "profiles", "r02_ncu_summary.json")
     ncu = json.load(open(ncu_path)) if os.path.exists(ncu_path) else {}
