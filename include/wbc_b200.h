@@ -110,7 +110,9 @@ int wbc_get_duals(wbc_handle* h, double* y);
 int wbc_warm_start_split(const wbc_handle* h);
 /* Explicit switches for tests and measurements; every setting gives bit-identical results.  Keys: "warm_start_split" (0 = rebuild the
  * TQ factorisation inside the solve kernel), "cohort" (-1 auto, 0 never, 1 always: gang scheduling of the solve kernel),
- * "setup_canary" (1 = guard the workspace prefix of the warm-start kernel), "rollout_graph" (0 = wbc_rollout never replays a CUDA graph). */
+ * "setup_canary" (1 = guard the workspace prefix of the warm-start kernel), "rollout_graph" (0 = wbc_rollout never replays a CUDA graph),
+ * "park" (0 = an all-cold batch runs as one launch of the general solve kernel instead of the two launches that park and resume solves; the parking buffer is 40 KB per
+ * robot of a chunk of at most 65536 robots, allocated at the first all-cold solve), "park_chunk" (robots per chunk; before the first cold solve). */
 int wbc_set_option(wbc_handle* h, const char* key, int value);
 
 /* Test / inspection hook: the dense QP of robot i as the reference would hand it to qpOASES (row-major H[42*42], g[42],

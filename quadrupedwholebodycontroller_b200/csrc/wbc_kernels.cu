@@ -20,6 +20,7 @@
     #define WBC_GANG 6          /* 6 x 37.6 KB */
   #endif
 #endif
+#define WBC_PARK_CHUNK 65536      /* robots per pair of launches of a parked cold batch: bounds the parking buffer at 2.7 GB */
 #include "wbc_assembly.cuh"
 #include "wbc_qp.cuh"
 #include "wbc_planner.cuh"
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(WBC_QP_THREADS,1) wbc_solve_qp_kernel(int N,co
 #endif
         WBC_SYNC();
         int nWSR=nWSRmax;
-        const int rcv= isFirst? qp_init(w,c,nWSR) : qp_hotstart(w,c,nWSR,pre?&pre[r]:nullptr);
+        const int rcv= isFirst? qp_init<false>(w,c,nWSR) : qp_hotstart(w,c,nWSR,pre?&pre[r]:nullptr);
         if(c.tqBar){ wbc_mbar_wait(c.tqBar,c.tqParity); c.tqBar=0u; }            // qp_hotstart returned before it needed Q / T: the copy must still land before the workspace is reused
         WBC_SYNC();
         // QProblemB::getPrimalSolution (QProblemB.cpp:774-793) hands x out only in these three states; otherwise the caller's qpSolution_ keeps
@@ -287,6 +288,143 @@ __global__ void __launch_bounds__(WBC_QP_THREADS,1) wbc_solve_qp_kernel(int N,co
 #if WBC_LV_TMEM
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();                                                  // every warp left the loop at the same barrier: nobody uses tensor memory any more
+    if((threadIdx.x>>5)==0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(*tmBaseS),"n"(WBC_TM_ALLOC_COLS) : "memory");
+#endif
+}
+
+// ---------------------------------------------------------------- kernel 2c: all-cold batches, with PARKING
+// When every robot of the batch cold-starts, kernel 2 fetches gang by gang (all members then sit at the same iteration index, which keeps the barrier waits short) -- and
+// every gang idles until its slowest member is done: iteration counts 62..100 inside a gang of 7 cost 11 % of the barrier rounds of cold4096.  This kernel runs such a
+// batch as two launches over the robots [rBase, rEnd):
+//   PHASE 1: gang fetch; as soon as the first member of a gang has finished (and the cheap early iterations are over, PARK_MIN_ITER) the others stop at the top of their
+//            next iteration and PARK: workspace, lane-owned vectors and context go to park[k] (k from parkCtl[0]), the robot's number to parkList[k];
+//   PHASE 2: per-warp fetch over the parked solves (counter = parkCtl[1]); each is restored and continued from exactly where it stopped.
+// Results are bit-identical to kernel 2.  It is a kernel of its own (cold starts only: no hot-start code below it) so that kernel 2 and the functions ptxas compiles
+// under it stay exactly what they were: register allocation runs over a kernel's whole call tree, and growing kernel 2's body by the parking code made 25 of its 45
+// device functions longer and every launch 3 % slower (profiles/r02_gang_variants.txt, r02p).
+WBC_DEV bool gang_all(int done){ return gang_count(done)==(int)blockDim.x; }
+__device__ __noinline__ void park_store(const QPWork& w,const QPCtx& c,QPPark* park,int* parkCtl,int* parkList,int r,int lane){
+    int slot=0; if(lane==0) slot=atomicAdd(&parkCtl[0],1); slot=__shfl_sync(0xffffffffu,slot,0);
+    QPPark& P=park[slot];
+    WBC_SYNC();
+    { const double* src=reinterpret_cast<const double*>(&w); double* dst=reinterpret_cast<double*>(&P.w);
+      for(int i=lane;i<(int)(sizeof(QPWork)/sizeof(double));i+=32) dst[i]=src[i]; }
+#if WBC_LV_TMEM
+    { real v[LV_SLOTS];
+      #pragma unroll
+      for(int s2=0;s2<LV_SLOTS;s2++) wbc_tm_ld(c.tm+WBC_TM_COLS_PER_REAL*(unsigned)s2,v[s2]);
+      wbc_tm_wait_ld();
+      #pragma unroll
+      for(int s2=0;s2<LV_SLOTS;s2++){ wbc_tm_use(v[s2]); P.lv[s2*32+lane]=v[s2]; } }
+#endif
+    if(lane==0){ P.c=c; parkList[slot]=r; }
+    WBC_SYNC();
+}
+// the workspace by one bulk copy (issued here, completed on `bar` by the caller), the lane-owned vectors into tensor memory, the context into every lane
+__device__ __noinline__ void park_restore(QPWork& w,QPCtx& c,const QPPark& P,unsigned bar,int lane,const QPData* qg,unsigned tm){
+    if(lane==0){ wbc_fence_proxy_async(); wbc_mbar_expect_tx(bar,(unsigned)sizeof(QPWork)); wbc_bulk_g2s(wbc_saddr(&w),&P.w,(unsigned)sizeof(QPWork),bar); }
+    c=P.c; c.lane=lane; c.qg=qg; c.tqBar=0u; c.tqParity=0u; c.parkOK=0; c.resuming=1; c.tm=tm;
+#if WBC_LV_TMEM
+    { real v[LV_SLOTS];
+      #pragma unroll
+      for(int s2=0;s2<LV_SLOTS;s2++) v[s2]=P.lv[s2*32+lane];
+      #pragma unroll
+      for(int s2=0;s2<LV_SLOTS;s2++) wbc_tm_st(tm+WBC_TM_COLS_PER_REAL*(unsigned)s2,v[s2]);
+      wbc_tm_wait_st(); }
+#endif
+}
+template<int PHASE> __global__ void __launch_bounds__(WBC_QP_THREADS,1) wbc_solve_cold_kernel(int N,const QPData* qpd,QPState* qs,unsigned char* first,BatchOut out,int* counter,int nWSRmax,long long* prof,int* stats,
+                                                                                          int rBase,int rEnd,QPPark* park,int* parkCtl,int* parkList){
+    extern __shared__ double smem[];
+    QPWork& w=*reinterpret_cast<QPWork*>(reinterpret_cast<char*>(smem)+(size_t)(threadIdx.x>>5)*sizeof(QPWork));
+    const int lane=threadIdx.x&31;
+    const unsigned barH=wbc_saddr(reinterpret_cast<char*>(smem)+(size_t)WBC_GANG*sizeof(QPWork)+16*(threadIdx.x>>5));
+    unsigned parH=0u;
+    if(lane==0){ wbc_mbar_init(barH,1u); wbc_mbar_init(barH+8u,1u); wbc_mbar_init_fence(); wbc_fence_proxy_async(); }
+    WBC_SYNC();
+    unsigned tmRobot=0u;
+#if WBC_LV_TMEM
+    unsigned* tmBaseS=reinterpret_cast<unsigned*>(reinterpret_cast<char*>(smem)+(size_t)WBC_GANG*sizeof(QPWork)+16*WBC_GANG);
+    if((threadIdx.x>>5)==0){
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(wbc_saddr(tmBaseS)),"n"(WBC_TM_ALLOC_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    tmRobot=*tmBaseS+((((unsigned)(threadIdx.x>>5)&3u)*32u)<<16)+(unsigned)(threadIdx.x>>7)*(unsigned)(LV_SLOTS*WBC_TM_COLS_PER_REAL);
+#endif
+    constexpr bool cohort=(PHASE==1);
+    for(;;){
+        int r=0; if(lane==0) r=atomicAdd(counter,1); r=__shfl_sync(0xffffffffu,r,0);
+        int pk=-1;
+        if(PHASE==2){ pk=r; r= pk<parkCtl[0] ? parkList[pk] : N; }
+        else { r+=rBase; if(r>=rEnd) r=N; }
+        if(cohort){ if(gang_all(r>=N)) break; }
+        if(r>=N){ while(!gang_all(1)){} if(cohort) continue; break; }
+        QPCtx c; c.lane=lane; c.nFR=c.nFX=c.nAC=c.nIAC=0; c.frIdentity=0; c.infeasible=c.unbounded=0; c.tau=0.0; c.rampOffset=0; c.status=QPS_NOTINITIALISED; c.qg=&qpd[r];
+        c.tqBar=0u; c.tqParity=0u; c.tm=tmRobot; c.parkOK=(PHASE==1)?1:0; c.resuming=0; c.park_iter=0; c.park_nWSRmax=0; c.park_farbound=real(0.0);
+        WBC_SYNC();                                                   // every lane has finished with the previous robot's workspace
+        if(PHASE==2){
+            park_restore(w,c,park[pk],barH,lane,&qpd[r],tmRobot);
+            wbc_mbar_wait(barH,parH); parH^=1u;
+        } else {
+            // the robot's QP blocks: bulk copy (fp64) / conversion (fp32), like kernel 2
+#if defined(WBC_FP32)
+            { const double* src=(const double*)&qpd[r]; real* dst=(real*)&w.qp; constexpr int K=(QPHOT_HEAD+6+31)/32; double t[K];
+              #pragma unroll
+              for(int k=0;k<K;k++){ const int i=lane+32*k; t[k]=(i<QPHOT_HEAD)?__ldg(src+i):((i<QPHOT_HEAD+6)?__ldg(src+(QPDATA_DOUBLES-6)+(i-QPHOT_HEAD)):0.0); }
+              #pragma unroll
+              for(int k=0;k<K;k++){ const int i=lane+32*k; if(i<QPHOT_HEAD+6) dst[i]=(real)t[k]; } }
+#else
+            if(lane==0){ wbc_fence_proxy_async(); wbc_mbar_expect_tx(barH,(unsigned)(QPHOT_HEAD*sizeof(double))); wbc_bulk_g2s(wbc_saddr(&w.qp),&qpd[r],(unsigned)(QPHOT_HEAD*sizeof(double)),barH); }
+            const double tailv=(lane<6)?__ldg((const double*)&qpd[r]+(QPDATA_DOUBLES-6)+lane):0.0;
+            if(lane<6) ((real*)&w.qp)[QPHOT_HEAD+lane]=tailv;
+            wbc_mbar_wait(barH,parH); parH^=1u;
+#endif
+        }
+#if defined(WBC_PROFILE)
+        if(PHASE!=2){ for(int k=0;k<8;k++) c.prof[k]=0; c.flops=0.0; }      // a resumed solve keeps what it had counted when it was parked
+        const long long tstart=clock64();
+#endif
+        WBC_SYNC();
+        int nWSR=nWSRmax;
+        const int rcv=qp_init<true>(w,c,nWSR);
+        if(PHASE==1&&rcv==QP_SUSPENDED){
+#if defined(WBC_PROFILE)
+            c.prof[6]=clock64()-tstart;
+#endif
+            park_store(w,c,park,parkCtl,parkList,r,lane);     // nothing of this robot is published yet; first[r] stays set
+            while(!gang_all(1)){}
+            continue;
+        }
+        WBC_SYNC();
+        // epilogue of kernel 2 for a cold-started robot
+        QPState& S=qs[r];
+        const bool haveSol=(c.status==QPS_AUXILIARYQPSOLVED||c.status==QPS_HOMOTOPYQPSOLVED||c.status==QPS_SOLVED);
+        LV_FOR(i,sl,42){ LV_LD(lbi,lb,i,sl); LV_LD(ubi,ub,i,sl); LV_WAIT(); LV_USE(lbi); LV_USE(ubi);
+            if(LV_IN(i,42)){ S.x[i]=w.x[i]; S.lb[i]=lbi; S.ub[i]=ubi; S.bstat[i]=w.bstat[i]; if(haveSol) out.x[i*N+r]=w.x[i]; else w.x[i]=(real)out.x[i*N+r]; out.ws[i*N+r]=w.bstat[i]; } }
+        LANE_FOR(i,112) S.y[i]=w.y[i];
+        LV_FOR(i,sl,70){ LV_LD(al,Ax_l,i,sl); LV_LD(au,Ax_u,i,sl); LV_WAIT(); LV_USE(al); LV_USE(au);
+            if(LV_IN(i,70)){ S.Ax_l[i]=al; S.Ax_u[i]=au; S.cstat[i]=w.cstat[i]; out.ws[(42+i)*N+r]=w.cstat[i]; } }
+        WBC_SYNC();
+        if(lane<12){ const int i=lane; const QPHotR& q=WQP;
+            real s=0; for(int j=0;j<12;j++) s+=q.Mjj[12*i+j]*w.x[6+j];
+            real t=0; for(int j=0;j<12;j++) t+=(q.cmask[j/3]*q.Jc[18*j+6+i])*w.x[18+j];
+            out.tau[i*N+r]= (rcv==0)? (double)(s+(real)c.qg->biasj[i]-t) : 0.0;
+            out.grf[i*N+r]= w.x[18+i]; }
+        if(lane==0){ S.rampOffset=c.rampOffset; S.status=c.status; out.rc[r]=rcv; out.nwsr[r]=nWSR; first[r]=0;
+                     if(stats){ stats[r]+=1; if(rcv!=0) stats[N+r]+=1; stats[2*N+r]+=nWSR; if(nWSR>stats[3*N+r]) stats[3*N+r]=nWSR; }
+#if defined(WBC_PROFILE)
+                     if(prof){ c.prof[6]=(PHASE==2?c.prof[6]:0)+(clock64()-tstart); for(int k=0;k<8;k++) prof[10*(size_t)r+k]=c.prof[k]; prof[10*(size_t)r+8]=(long long)c.flops; prof[10*(size_t)r+9]=1; }
+#endif
+        }
+        WBC_SYNC();
+        if(cohort){ while(!gang_all(1)){} }
+    }
+#if WBC_LV_TMEM
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
     if((threadIdx.x>>5)==0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(*tmBaseS),"n"(WBC_TM_ALLOC_COLS) : "memory");
 #endif
 }
@@ -388,6 +526,8 @@ struct wbc_handle {
     QPPre* pre=nullptr; bool split=true, maybeWarm=false, setupCanary=false; size_t setupPad=0;            // two-kernel warm start (kernel 2a); maybeWarm: some robot may hold a previous solution
     // closed-loop rollout as a CUDA graph: one planner period (planner tick + graphPeriod control ticks incl. the plant) captured once, replayed per period
     cudaGraph_t graph=nullptr; cudaGraphExec_t graphExec=nullptr; int graphPeriod=0; long long graphLaunches=0; bool capturing=false, useGraph=true;
+    // parking of cold solves (wbc_solve_cold_kernel): 40 KB per robot of the chunk in flight, allocated at the first all-cold solve
+    QPPark* park=nullptr; int* parkList=nullptr; int* parkCtl=nullptr; int parkCap=0, parkChunk=WBC_PARK_CHUNK; bool parkMode=true;
     void* staticScratch=nullptr;                    // device address of g_wbc_static_scratch on this handle's device (wbc_solve_qp_static)
     long long launches=0;
     std::string err;
@@ -466,7 +606,9 @@ extern "C" int wbc_create(int n,int device,const wbc_params* params,void* stream
         h->err=std::string("update-state kernel geometry: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     // solver launch geometry: one warp per CTA, as many CTAs per SM as shared memory allows
     h->qpSmem=sizeof(QPWork)*WBC_GANG+16*WBC_GANG+(WBC_LV_TMEM?16:0);                                  // + two mbarriers per warp
-    if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
+    if(cudaFuncSetAttribute(wbc_solve_qp_kernel,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess
+       ||cudaFuncSetAttribute(wbc_solve_cold_kernel<1>,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess
+       ||cudaFuncSetAttribute(wbc_solve_cold_kernel<2>,cudaFuncAttributeMaxDynamicSharedMemorySize,(int)h->qpSmem)!=cudaSuccess){
         h->err=std::string("cudaFuncSetAttribute: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
     int nb=0; if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb,wbc_solve_qp_kernel,WBC_QP_THREADS,h->qpSmem)!=cudaSuccess||nb<1){
         h->err=std::string("occupancy query: ")+cudaGetErrorString(cudaGetLastError()); return fail(WBC_ERR_CUDA); }
@@ -490,7 +632,7 @@ extern "C" int wbc_destroy(wbc_handle* h){
     if(h->stream) cudaStreamSynchronize(h->stream);
     drop_graph(h);
     void* ptrs[]={h->q,h->qd,h->pos,h->quat,h->twist,h->pose,h->vel,h->acc,h->swp,h->swv,h->swa,h->contacts,h->prevc,h->switching,h->first,h->ctrl,h->qpd,h->qps,
-                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre,h->duals,h->legs};
+                  h->counter,h->tau,h->grf,h->x,h->com,h->rc,h->nwsr,h->ws,h->prof,h->planner,h->plannerCmd,h->published,h->plantAux,h->stats,h->pre,h->duals,h->legs,h->park,h->parkList,h->parkCtl};
     for(void* p:ptrs) if(p) cudaFree(p);
     for(int i=0;i<4;i++) if(h->ev[i]) cudaEventDestroy(h->ev[i]);
     if(h->ownStream&&h->stream) cudaStreamDestroy(h->stream);
@@ -614,8 +756,32 @@ extern "C" int wbc_solve_qp(wbc_handle* h){
         wbc_warm_setup_kernel<<<h->N,32,(h->setupCanary?sizeof(QPWork):QPWORK_TQ_BYTES)+h->setupPad,h->stream>>>(h->N,h->qpd,h->qps,h->first,h->pre,h->setupCanary?1:0);
         h->launches++; CK(cudaGetLastError());
     }
+    // an all-cold batch in gang mode: two launches of wbc_solve_cold_kernel per chunk of robots (gang fetch with parking, then per-warp fetch over the parked solves);
+    // bit-identical to the single launch of kernel 2, without the idle warps at the end of every gang's round
+    bool parking=cohort==1&&!h->maybeWarm&&h->parkMode;
+    if(parking&&!h->park){
+        const int cap= h->N<h->parkChunk ? h->N : h->parkChunk;
+        if(cudaMalloc(&h->park,sizeof(QPPark)*(size_t)cap)!=cudaSuccess||cudaMalloc(&h->parkList,sizeof(int)*(size_t)cap)!=cudaSuccess||cudaMalloc(&h->parkCtl,4*sizeof(int))!=cudaSuccess){
+            cudaGetLastError(); if(h->park) cudaFree(h->park); if(h->parkList) cudaFree(h->parkList); if(h->parkCtl) cudaFree(h->parkCtl);
+            h->park=nullptr; h->parkList=nullptr; h->parkCtl=nullptr; h->parkMode=false; parking=false;
+            h->err="parking buffer (40 KB per robot of a chunk) could not be allocated: cold batches run as one launch of the general kernel (same results, slower)"; }
+        else h->parkCap=cap;
+    }
+    if(parking){
+        for(int base=0;base<h->N;base+=h->parkCap){
+            const int end= base+h->parkCap<h->N ? base+h->parkCap : h->N;
+            int g1=h->smCount*h->qpBlocksPerSM; if(g1>(end-base+WBC_GANG-1)/WBC_GANG) g1=(end-base+WBC_GANG-1)/WBC_GANG;
+            if(base>0) CK(cudaMemsetAsync(h->counter,0,sizeof(int),h->stream));
+            CK(cudaMemsetAsync(h->parkCtl,0,4*sizeof(int),h->stream));
+            wbc_solve_cold_kernel<1><<<g1,WBC_QP_THREADS,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,h->stats,base,end,h->park,h->parkCtl,h->parkList);
+            h->launches++; CK(cudaGetLastError());
+            wbc_solve_cold_kernel<2><<<g1,WBC_QP_THREADS,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->parkCtl+1,100,h->prof,h->stats,base,end,h->park,h->parkCtl,h->parkList);
+            h->launches++; CK(cudaGetLastError());
+        }
+    } else {
     wbc_solve_qp_kernel<<<grid,WBC_QP_THREADS,h->qpSmem,h->stream>>>(h->N,h->qpd,h->qps,h->first,batch_out(h),h->counter,100 /* nWSR, wbc.cpp:517 */,h->prof,cohort,two?h->pre:nullptr,h->stats);
     h->launches++; CK(cudaGetLastError());
+    }
     h->maybeWarm=true;
     if(!h->capturing) CK(cudaEventRecord(h->ev[2],h->stream));
     return WBC_OK;
@@ -831,6 +997,10 @@ extern "C" int wbc_set_option(wbc_handle* h,const char* key,int value){
     drop_graph(h);                                                            // every switch below changes what a captured period would launch
     if(k=="rollout_graph"){ h->useGraph=value!=0; return WBC_OK; }            // 0: wbc_rollout issues plain launches every tick
     if(k=="warm_start_split"){ h->split=value!=0; return WBC_OK; }            // 0: rebuild the TQ factorisation inside the solve kernel
+    if(k=="park_chunk"){                                                      // robots per pair of launches of a parked cold batch (tests; before the first cold solve)
+        if(value<1||h->park){ h->err="wbc_set_option: park_chunk needs a positive value and must come before the first cold solve"; return WBC_ERR_ARG; }
+        h->parkChunk=value; return WBC_OK; }
+    if(k=="park"){ h->parkMode=value!=0; return WBC_OK; }                       // 0: all-cold batches run as one launch of the general kernel (no parking of solves)
     if(k=="cohort"){ h->cohortMode=value; return WBC_OK; }                    // -1 auto, 0 never, 1 always (gang scheduling of kernel 2)
     if(k=="setup_canary"){                                                    // guard the prefix allocation of kernel 2a (tests)
         h->setupCanary=value!=0;

@@ -42,7 +42,8 @@ enum : int { QP_OK=0, QP_RET_DIV_BY_ZERO=1, QP_RET_INIT_FAILED=33, QP_RET_INIT_F
              QP_RET_INIT_FAILED_INFEASIBILITY=37, QP_RET_INIT_FAILED_UNBOUNDEDNESS=38, QP_RET_SETUP_AUXILIARYQP_FAILED=43,
              QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED=54, QP_RET_STEPDIRECTION_DETERMINATION_FAILED=57, QP_RET_HOMOTOPY_STEP_FAILED=60,
              QP_RET_HOTSTART_STOPPED_INFEASIBILITY=61, QP_RET_HOTSTART_STOPPED_UNBOUNDEDNESS=62, QP_RET_MAX_NWSR_REACHED=64, QP_RET_STEPDIRECTION_FAILED_TQ=68, QP_RET_STEPDIRECTION_FAILED_CHOLESKY=69,
-             QP_RET_HESSIAN_NOT_SPD=99, QP_RET_UNSUPPORTED_PATH=1001 };
+             QP_RET_HESSIAN_NOT_SPD=99, QP_RET_UNSUPPORTED_PATH=1001,
+             QP_SUSPENDED=2001 };   // not a qpOASES code, never published: the solve was parked at the top of an iteration (cold batches, "parking" below) and continues later, bit for bit
 enum : int { QPS_NOTINITIALISED=0, QPS_PREPARINGAUXILIARYQP=1, QPS_AUXILIARYQPSOLVED=2, QPS_PERFORMINGHOMOTOPY=3, QPS_HOMOTOPYQPSOLVED=4, QPS_SOLVED=5 };
 enum : int { ST_LOWER=-1, ST_INACTIVE=0, ST_UPPER=1 };     // Types.hpp:272-280
 
@@ -68,6 +69,10 @@ constexpr int OPT_numRefinementSteps=2;
 constexpr real LI_SURE=real(1.0e-6), LI_NONE=real(1.0e-12);
 #endif
 
+#ifndef WBC_PARK_MIN_ITER
+  #define WBC_PARK_MIN_ITER 40
+#endif
+constexpr int PARK_MIN_ITER=WBC_PARK_MIN_ITER;     // a cold solve is not parked before this iteration (the early iterations are cheap: mixing them with late ones wastes the gang's barrier rounds)
 constexpr int HZLD=42;                // row length of the (HZ)_force block (the 4-wide tiles of zhz_tiles may read up to 2 elements past a row's end and discard them)
 constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
 constexpr int SIZET=42;               // sizeT = min(nV,nC)
@@ -235,11 +240,24 @@ struct QPCtx {
     const QPData* qg;    // this robot's compact QP in HBM (fp64): new lbA / ubA targets, bias_j
     unsigned tm;                // WBC_TMEM: tensor-memory address (lane quarter of this warp, first column of its robot) of the lane-owned vectors
     unsigned tqBar, tqParity;   // != 0: a bulk copy of the rebuilt Q / T into w.Q, w.RT is in flight on this mbarrier (shared-space address) with this phase parity
+    // parking (wbc_solve_cold_kernel: cold batches run gang by gang; when the first member of a gang is done, the others stop at the top of their next iteration, their
+    // whole state goes to HBM and a second launch finishes them with per-warp fetching -- no warp idles while the slowest member of its gang finishes)
+    int parkOK;                                          // 1: this launch may park the solve (phase 1); 0 in the launch that finishes the parked ones
+    int resuming;                                        // 1: the state was restored from a parked solve; qp_init / hotstartFar / solveQP skip their prologues once
+    int park_iter, park_nWSRmax; real park_farbound;     // loop state of solveQP / hotstartFar at the suspension
 #if defined(WBC_PROFILE)
     long long prof[8];   // clock64 ticks: 0 data shift, 1 step direction, 2 perform step, 3 change active set, 4 projected Cholesky, 5 ramp/drift, 6 whole solve, 7 iterations
     double flops;        // ALGORITHMIC flops of the qpOASES method on dense data (SURVEY.md section 8d formulas), not what this kernel executes
 #endif
 };
+
+// a parked solve: the whole workspace, the lane-owned vectors (tensor-memory build) and the context
+struct alignas(16) QPPark {
+    QPWork w;
+    real lv[LV_SLOTS*32];
+    QPCtx c;
+};
+static_assert(offsetof(QPPark,w)==0&&sizeof(QPWork)%16==0,"QPPark: the workspace is restored by one bulk copy");
 
 // ---------------------------------------------------------------- gang mode (WBC_GANG = warps per CTA, one robot per warp)
 // The solver is instruction-SUPPLY bound when its warps run independently: 193 KB of code, ~90 KB touched per working-set change, a 32 KB
@@ -251,6 +269,8 @@ struct QPCtx {
 // (every warp done?) which the drain loops of the kernel use to leave together.
 #if defined(WBC_GANG) && defined(__CUDACC__)
   WBC_DEV bool gang_bar(int done){ return __syncthreads_and(done)!=0; }
+  // the same barrier with a count instead of a predicate (how many threads of the gang are done); a launch uses ONE of the two forms at every site
+  WBC_DEV int gang_count(int done){ return __syncthreads_count(done); }
   #define WBC_GANG_SYNC() gang_bar(0)
 #else
   #define WBC_GANG_SYNC() do{}while(0)
@@ -1313,14 +1333,22 @@ WBC_FN int changeActiveSet(QPWork& w,QPCtx& c,int BC_idx,int BC_status,bool BC_i
 // QProblem::updateFarBounds (QProblem.cpp:5498-5552, QProblemB.cpp:2202-2246): see far_rv
 WBC_DEV void updateFarBounds(QPWork&,QPCtx& c,real curFarBound){ c.farbound=curFarBound; c.farRampOffset=c.rampOffset; }
 // QProblem::solveQP (QProblem.cpp:1477-1747); nWSR in/out like the reference
-WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
+// PARK (wbc_solve_cold_kernel only): the gang's barrier also tells how many of its threads are done; as soon as a member has finished -- and the cheap early iterations
+// are over -- the solve returns QP_SUSPENDED from the top of the iteration, to be continued from exactly there (c.resuming) by another launch.
+template<bool PARK> WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
+    if(PARK&&c.resuming){ c.resuming=0; } else {
     if(c.status==QPS_NOTINITIALISED||c.status==QPS_PREPARINGAUXILIARYQP||c.status==QPS_PERFORMINGHOMOTOPY) return QP_RET_HOTSTART_FAILED_AS_QP_NOT_INITIALISED;
     c.status=QPS_PERFORMINGHOMOTOPY;                 // updateActivitiesForHotstart: nothing to do, every far bound is finite
     c.infeasible=0; c.unbounded=0;
+    }
     for(int iter=nWSRperformed;iter<nWSR;iter++){
         c.status=QPS_PERFORMINGHOMOTOPY;
 #if !defined(__CUDACC__) && defined(WBC_QP_DBG)
         g_dbg_iter=iter;
+#endif
+#if defined(WBC_GANG) && defined(__CUDACC__)
+        if(PARK){ if(gang_count(0)>0&&c.parkOK&&iter>=PARK_MIN_ITER){ c.park_iter=iter; nWSR=iter; return QP_SUSPENDED; } }
+        else
 #endif
         WBC_GANG_SYNC();
         WBC_TIC(t0);
@@ -1350,15 +1378,19 @@ WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperformed){
     return QP_RET_MAX_NWSR_REACHED;
 }
 // QProblem::hotstart (QProblem.cpp:446-640): far-bound outer loop
-WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
-    const int lane=WBC_LANE(c); const int nWSR_max=nWSR; int nWSR_performed=0;
+template<bool PARK> WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
+    const int lane=WBC_LANE(c); int nWSR_max=nWSR; int nWSR_performed=0;
     real farbound=OPT_initialFarBounds;
+    if(PARK&&c.resuming){ nWSR_max=c.park_nWSRmax; nWSR_performed=c.park_iter; farbound=c.park_farbound; }      // c.farbound / c.farRampOffset came back with the context
+    else {
     { real m=real(0.0); LANE_FOR(i,70){ real u=(real)c.qg->ubA[i], l=(real)c.qg->lbA[i]; if(u<QINFTY) m=fmax(m,u); if(l>-QINFTY) m=fmax(m,-l); } m=wbc_max(m); if(m>farbound) farbound=m; }
     updateFarBounds(w,c,farbound);
+    }
     int rv;
     for(;;){
         nWSR=nWSR_max;
-        rv=solveQP(w,c,nWSR,nWSR_performed);
+        rv=solveQP<PARK>(w,c,nWSR,nWSR_performed);
+        if(PARK&&rv==QP_SUSPENDED){ c.park_nWSRmax=nWSR_max; c.park_farbound=farbound; return rv; }
         nWSR_performed=nWSR;
         farbound*=OPT_growFarBounds;
         if(c.infeasible){
@@ -1380,8 +1412,10 @@ WBC_FN int hotstartFar(QPWork& w,QPCtx& c,int& nWSR){
 }
 // SQProblem/QProblem::init -> solveInitialQP (QProblem.cpp:316-368, 1301-1471): cold start from x = y = 0 with every variable
 // fixed at its (far) lower bound (initialStatusBounds = ST_LOWER) and no active constraint.
-WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
+template<bool PARK> WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     const int lane=WBC_LANE(c); WBC_SYNC();
+    int rv;
+    if(!(PARK&&c.resuming)){
     LANE_FOR(i,42){ w.x[i]=real(0.0); w.y[i]=real(0.0); w.FX[i]=(signed char)i; w.bstat[i]=ST_LOWER; }
     LV_FOR(i,sl,42){ LV_ST(g,i,sl,real(0.0)); LV_ST(lb,i,sl,real(0.0)); LV_ST(ub,i,sl,OPT_boundRelaxation); LV_DONE(); }
     LANE_FOR(i,70){ w.y[42+i]=real(0.0); w.IAC[i]=(signed char)i; w.cstat[i]=ST_INACTIVE; w.posAC[i]=0; }
@@ -1390,9 +1424,11 @@ WBC_FN int qp_init(QPWork& w,QPCtx& c,int& nWSR){
     setupTQfactorisation(w,c);
     c.status=QPS_AUXILIARYQPSOLVED;
     performRamping(w,c);
-    int rv=computeProjectedCholesky(w,c);                    // setupInitialCholesky
+    rv=computeProjectedCholesky(w,c);                        // setupInitialCholesky
     if(rv!=QP_OK) return QP_RET_INIT_FAILED_CHOLESKY;
-    rv=hotstartFar(w,c,nWSR);
+    }
+    rv=hotstartFar<PARK>(w,c,nWSR);
+    if(PARK&&rv==QP_SUSPENDED) return rv;
     if(c.infeasible) return QP_RET_INIT_FAILED_INFEASIBILITY;
     if(c.unbounded) return QP_RET_INIT_FAILED_UNBOUNDEDNESS;
     if(rv!=QP_OK&&rv!=QP_RET_MAX_NWSR_REACHED) return QP_RET_INIT_FAILED_HOTSTART;
@@ -1496,7 +1532,7 @@ WBC_FN int qp_hotstart(QPWork& w,QPCtx& c,int& nWSR,const QPPre* pre){
     int rv=computeProjectedCholesky(w,c);
     if(rv!=QP_OK) return QP_RET_UNSUPPORTED_PATH;
     c.status=QPS_AUXILIARYQPSOLVED;
-    return hotstartFar(w,c,nWSR);
+    return hotstartFar<false>(w,c,nWSR);
 }
 
 }  // namespace wbc

@@ -139,6 +139,34 @@ def test_two_kernel_warm_start_is_bit_identical_to_the_single_kernel_path(wbc, w
     assert (outs[0][2]["nwsr"][40:90] >= 40).all()                    # the reset robots did cold-start at tick 2
 
 
+@pytest.mark.parametrize("n,chunk", [(1, 0), (5, 0), (97, 0), (300, 128), (1500, 0)])
+def test_parked_cold_solves_are_bit_identical_to_the_single_launch(wbc, wl, n, chunk):
+    """All-cold batches run as two launches of wbc_solve_cold_kernel: gang fetch until the first member of a gang is done, the others PARK (workspace, tensor-memory
+    vectors and context to HBM), then per-warp fetch over the parked solves, each continued from the top of the iteration it stopped at.  wbc_set_option("park", 0)
+    keeps the single launch of the general kernel.  Same functions, same arithmetic: every output must be bit-identical -- robots that hit the nWSR limit (rc 64)
+    included, for batches smaller than a gang, not divisible by it, and larger than one chunk of the parking buffer -- and so must the hot-started tick that follows
+    (the parked solves hand over the same solver state)."""
+    st, ref = wl.randomised(n, seed=21, contacts="mixed", switching_frac=0.1)
+    outs = []
+    for park in (1, 0):
+        ctl = wbc.WholeBodyController(n); ctl.setOption("park", park)
+        if park and chunk:
+            ctl.setOption("park_chunk", chunk)
+        rec = []; s = st
+        for t in range(3):
+            if t == 1:
+                s = wl.advance_state(s)
+            if t == 2:
+                ctl.setInitialState()                                # a second cold batch on the same handle (the parking buffer is reused)
+            ctl.setJointAndBaseState(**s); ctl.setReference(**ref); ctl.step(); o = ctl.getOutputs(); o["y"] = ctl.getDuals(); rec.append(o)
+        ctl.close(); outs.append(rec)
+    for t in range(3):
+        for k in outs[0][t]:
+            assert np.array_equal(outs[0][t][k], outs[1][t][k]), (t, k)
+    if n >= 97:
+        assert (outs[0][0]["nwsr"] >= 40).all()                      # cold solves long enough to have been parked
+
+
 def test_warm_setup_kernel_stays_inside_its_workspace_prefix(wbc, wl):
     """wbc_warm_setup_kernel allocates only the first QPWORK_TQ_BYTES of the solver workspace.  With wbc_set_option("setup_canary", 1) it is launched with the whole
     workspace, the part past the prefix is filled with a NaN pattern and checked at the end: a read from there poisons the factorisation, a write

@@ -16,6 +16,9 @@ from quadrupedwholebodycontroller_b200 import workloads as wl
 N = int(os.environ.get("VAR_N", "4096")); contacts = os.environ.get("VAR_CONTACTS", "stance"); reps = int(os.environ.get("VAR_REPS", "3"))
 st, ref = wl.randomised(N, seed=1234, contacts=contacts); st1 = wl.advance_state(st)
 ctl = wbc.WholeBodyController(N)
+for kv in os.environ.get("VAR_OPTIONS", "").split(","):
+    if kv:
+        ctl.setOption(kv.split("=")[0], int(kv.split("=")[1]))
 cold, tick1 = [], []
 h = hashlib.sha256()
 for rep in range(reps):
@@ -36,6 +39,9 @@ if T:
     NR = int(os.environ.get("VAR_ROLLOUT_N", "4096"))
     st, ref, cmd = wl.rollout_start(NR)
     ctl = wbc.WholeBodyController(NR); ctl.plannerCreate(); ctl.plantEnable()
+    for kv in os.environ.get("VAR_OPTIONS", "").split(","):
+        if kv:
+            ctl.setOption(kv.split("=")[0], int(kv.split("=")[1]))
     ctl.setJointAndBaseState(**st); ctl.setReference(**ref); ctl.plannerSetCmdVel(cmd[0].copy(), cmd[1].copy(), cmd[2].copy())
     q = []
     for t in range(T):

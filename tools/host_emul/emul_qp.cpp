@@ -13,7 +13,7 @@ extern "C" int emulqp_solve(void* h,const double* qpdata,int first,int* nwsr,dou
     EmulQP* e=(EmulQP*)h; { real* dst=(real*)&e->w.qp; for(int i=0;i<QPHOT_HEAD;i++) dst[i]=(real)qpdata[i]; for(int i=0;i<6;i++) dst[QPHOT_HEAD+i]=(real)qpdata[QPDATA_DOUBLES-6+i];
       memcpy(&e->qg,qpdata,sizeof(QPData)); e->c.qg=&e->qg; }
     int n=*nwsr; int rc;
-    if(first) rc=qp_init(e->w,e->c,n);
+    if(first) rc=qp_init<false>(e->w,e->c,n);
     else if(getenv("EMUL_SPLIT")){          // the two-kernel warm start: rebuild in a second workspace, hand over through QPPre
         static EmulQP a; static QPPre pre; memset(&a,0,sizeof(a)); memset(&pre,0,sizeof(pre)); a.c.lane=0; a.c.qg=&e->qg;
         signed char old[70]; memcpy(old,e->w.cstat,70);
