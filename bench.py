@@ -371,9 +371,10 @@ def summarise(name, res, steps, warmup, world, peaks, ncu):
              gpu_launches=res["launches"],
              kernels_ms=dict(update_state=rbd_ms, solve_qp=qp_ms, solve_qp_share=qp_ms * max(1, ro) / float(res["ms_dev"].mean()),
                              note=("per launch; rollout: mean over the ticks of one extra step replayed tick by tick" if ro else "per launch, mean over the timed steps")
-                             + "; solve_qp = wbc_warm_setup_kernel (hot-started robots only) + wbc_solve_qp_kernel (incl. the torque-recovery epilogue), one event pair"),
+                             + "; solve_qp = wbc_warm_setup_kernel (hot-started robots only) + wbc_solve_qp_kernel (incl. the torque-recovery epilogue), one event pair"
+                             + ("; an all-cold batch runs as wbc_solve_cold_kernel<1> (gang launch, solves parked) + <2> (parked solves finished) instead, same event pair" if spec["cold"] else "")),
              # the binding resource of the dominant kernel is the FP64 pipe / its latency, not HBM (1.4 kFLOP per byte): the contractual object carries FP64
-             roofline=dict(bound="fp64", kernel="wbc_solve_qp_kernel", achieved=alg_flops / (qp_ms * 1e-3) / 1e12, peak=fp64_peak / 1e3, unit="TFLOP/s",
+             roofline=dict(bound="fp64", kernel="wbc_solve_cold_kernel<1> + <2> (one all-cold batch = two launches, timed together)" if spec["cold"] else "wbc_solve_qp_kernel", achieved=alg_flops / (qp_ms * 1e-3) / 1e12, peak=fp64_peak / 1e3, unit="TFLOP/s",
                            frac=alg_flops / (qp_ms * 1e-3) / 1e9 / fp64_peak, algorithmic_mflop_per_solve=res["flops_per_solve"] / 1e6,
                            achieved_source="ALGORITHMIC flops of the qpOASES method on dense data (SURVEY 8d formulas, counted per robot by the profiling build of the same kernel on "
                                            "an untimed sample) / CUDA-event time of the launch", peak_source="wbc_measure_fp64_peak (DFMA microbenchmark, this run; MEASURED_PEAKS.json has no FP64 entry)",

@@ -70,9 +70,15 @@ constexpr real LI_SURE=real(1.0e-6), LI_NONE=real(1.0e-12);
 #endif
 
 #ifndef WBC_PARK_MIN_ITER
-  #define WBC_PARK_MIN_ITER 40
+  #define WBC_PARK_MIN_ITER 80     /* measured: 0 / 20 / 40 / 50 / 60 / 70 / 80 / 90 / 100 -> 27.7 / 26.7 / 25.2 / 25.1 / 25.0 / 24.8 / 24.3 / 25.5 / 26.3 ms on cold4096 (profiles/r02_gang_variants.txt) */
 #endif
-constexpr int PARK_MIN_ITER=WBC_PARK_MIN_ITER;     // a cold solve is not parked before this iteration (the early iterations are cheap: mixing them with late ones wastes the gang's barrier rounds)
+#ifndef WBC_PARK_MIN_DONE
+  #define WBC_PARK_MIN_DONE 1
+#endif
+// A cold solve is parked at the top of iteration >= PARK_MIN_ITER once >= PARK_MIN_DONE members of its gang are done.  Cold solves of this QP family take 62..100
+// iterations (mean 81): up to iteration 80 the gang stays together even if a member or two idle (lock-step iterations are the cheapest way to run them), after it the
+// stragglers are parked and finished by the second launch.  A batch whose solves are all shorter never parks and runs exactly like kernel 2.
+constexpr int PARK_MIN_ITER=WBC_PARK_MIN_ITER, PARK_MIN_DONE=WBC_PARK_MIN_DONE;
 constexpr int HZLD=42;                // row length of the (HZ)_force block (the 4-wide tiles of zhz_tiles may read up to 2 elements past a row's end and discard them)
 constexpr int LD=43;                  // leading dimension of Q (odd: conflict-free row AND column sweeps)
 constexpr int SIZET=42;               // sizeT = min(nV,nC)
@@ -1347,7 +1353,7 @@ template<bool PARK> WBC_FN int solveQP(QPWork& w,QPCtx& c,int& nWSR,int nWSRperf
         g_dbg_iter=iter;
 #endif
 #if defined(WBC_GANG) && defined(__CUDACC__)
-        if(PARK){ if(gang_count(0)>0&&c.parkOK&&iter>=PARK_MIN_ITER){ c.park_iter=iter; nWSR=iter; return QP_SUSPENDED; } }
+        if(PARK){ if(gang_count(0)>=32*PARK_MIN_DONE&&c.parkOK&&iter>=PARK_MIN_ITER){ c.park_iter=iter; nWSR=iter; return QP_SUSPENDED; } }
         else
 #endif
         WBC_GANG_SYNC();

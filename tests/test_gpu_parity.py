@@ -164,7 +164,7 @@ def test_parked_cold_solves_are_bit_identical_to_the_single_launch(wbc, wl, n, c
         for k in outs[0][t]:
             assert np.array_equal(outs[0][t][k], outs[1][t][k]), (t, k)
     if n >= 97:
-        assert (outs[0][0]["nwsr"] >= 40).all()                      # cold solves long enough to have been parked
+        assert (outs[0][0]["nwsr"] > 80).any()                       # some cold solves were long enough to be parked (wbc_qp.cuh: PARK_MIN_ITER)
 
 
 def test_warm_setup_kernel_stays_inside_its_workspace_prefix(wbc, wl):
