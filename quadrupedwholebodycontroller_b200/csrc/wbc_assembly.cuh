@@ -36,7 +36,11 @@ WBC_DEV void eul_rpy(const double* R,double* rpy){
 // `first` != 0 resets the state like setInitialState (wbc.cpp:65-120): oldT = I, oldJ = 0, Tdot^-1 = 0, integral = 0.
 // `plant` (nullable, SoA with stride N): what wbc_plant_step needs to turn the QP's centroidal accelerations back into generalized
 // ones, nu_dot = T^-1 (a - Tdot nu):  d = p_com - p_base (3), B = Mbb^-1 Mbj (72), Tdot_top nu (6).
-WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,CtrlState& st,QPData& out,int lane,int switching,int first,double* plant,int N){
+// `out` is the robot's QPData record (global memory in the kernel: every element of it is written exactly once and never read back here); `stg` holds the three blocks
+// the assembly reads again after writing them -- Jc, Mbb, bias_j -- in shared memory (QPStage; the caller copies them to the record afterwards).  The host emulation
+// passes the record itself for both.  (The whole record used to be staged: 5.7 KB of the 14.4 KB of shared memory per robot.)
+struct QPStage { double Jc[12*18], Mbb[36], biasj[12]; };
+template<class STG> WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,CtrlState& st,QPData& out,STG& stg,int lane,int switching,int first,double* plant,int N){
     const double* R=s.Rwb;
     // the previous tick's T (finite difference of D5) is requested now and used ~100 lines further down: inside the loop that consumes it every load
     // would sit behind the shared-memory store of the trip before (the compiler cannot prove the two do not alias) and cost a memory round trip per trip
@@ -109,7 +113,7 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     // M_c,bb = X^T Mbb X
     ASM_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.Mbb[6*i+k]*s.X[6*k+j]; s.tmp66[e]=v; }
     WBC_SYNC();
-    ASM_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.X[6*k+i]*s.tmp66[6*k+j]; out.Mbb[e]=v; }
+    ASM_FOR(e,36){ int i=e/6,j=e%6; double v=0; for(int k=0;k<6;k++) v+=s.X[6*k+i]*s.tmp66[6*k+j]; stg.Mbb[e]=v; }
     // M_c,jj = Mjj - Mjb B   (Mjj is block diagonal per leg)
     ASM_FOR(e,144){ int i=e/12,j=e%12; double v=(i/3==j/3)?s.Hleg[i/3][3*(i%3)+(j%3)]:0.0;
         for(int k=0;k<6;k++) v-=s.Mbj[12*k+i]*s.B[12*k+j]; out.Mjj[e]=v; }
@@ -124,7 +128,7 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
         else { int jj=j-6; v=0;
             if(jj/3==l){ const double* c=s.jcol[jj]; v=R[3*r]*c[0]+R[3*r+1]*c[1]+R[3*r+2]*c[2]; }
             for(int k=0;k<6;k++) v-=jb[k]*s.B[12*k+jj]; }
-        out.Jc[e]=v; }
+        stg.Jc[e]=v; }
     // T top rows = [Xi, Xi B], Xi = [[1,-S(d)],[0,1]]
     ASM_FOR(e,108){ int i=e/18,j=e%18; double v;
         if(j<6) v=(i==j)?1.0:((i<3&&j>=3)?-s.X[6*i+j]:0.0);
@@ -136,14 +140,14 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     // ---- D4: bias_c (joint part) = v_j - B^T v_b,  v = C nu + M w   (wbc.cpp:289) ----
     ASM_FOR(i,6){ double v=s.Cb[i]; for(int k=0;k<6;k++) v+=s.Mbb[6*i+k]*s.w6[k]; s.vb6[i]=v; }
     WBC_SYNC();
-    ASM_FOR(j,12){ double v=s.tauC[j]; for(int k=0;k<6;k++) v+=s.Mbj[12*k+j]*s.w6[k]; for(int k=0;k<6;k++) v-=s.B[12*k+j]*s.vb6[k]; out.biasj[j]=v; }
+    ASM_FOR(j,12){ double v=s.tauC[j]; for(int k=0;k<6;k++) v+=s.Mbj[12*k+j]*s.w6[k]; for(int k=0;k<6;k++) v-=s.B[12*k+j]*s.vb6[k]; stg.biasj[j]=v; }
     // ---- D5: finite-difference terms -Jdot [v_c; qd] (wbc.cpp:384-402,504,507), then roll old <- current ----
     const double timeStep=1.0/P.loopRate;
     ASM_FOR(i,12){
         const double c=s.cmask[i/3]; double a=0,b=0;
         if(!switching){
             for(int k=0;k<18;k++){
-                double jc=out.Jc[18*i+k], vk=(k<6)?s.vcom[k]:s.qd[k-6];
+                double jc=stg.Jc[18*i+k], vk=(k<6)?s.vcom[k]:s.qd[k-6];
                 double ost=first?0.0:st.Jstold[18*i+k], osw=first?0.0:st.Jswold[18*i+k];
                 a+=((c*jc-ost)/timeStep)*vk; b+=(((1.0-c)*jc-osw)/timeStep)*vk; }
         }
@@ -167,12 +171,12 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
         s.Y[e]=v; }
     WBC_SYNC();
     ASM_FOR(e,108){ int i=e/18,j=e%18; double v=0; for(int k=0;k<6;k++) v+=s.X[6*i+k]*s.Y[18*k+j]; st.TdotInv[e]=-v; st.Told[e]=s.Ttop[e]; }
-    ASM_FOR(e,216){ const double c=s.cmask[e/54]; double jc=out.Jc[e]; st.Jstold[e]=c*jc; st.Jswold[e]=(1.0-c)*jc; }
+    ASM_FOR(e,216){ const double c=s.cmask[e/54]; double jc=stg.Jc[e]; st.Jstold[e]=c*jc; st.Jswold[e]=(1.0-c)*jc; }
     // ---- D6: desired wrench (wbc.cpp:426-445), swing command (wbc.cpp:447-464) ----
     #pragma unroll
     for(int kk=0;kk<KI;kk++){ const int i=lane+WBC_ASM_NL*kk; if(i<6){
         const double kp=(i==2)?P.kpValueZ:P.kpValue;
-        double mcb=0; for(int k=0;k<6;k++) mcb+=out.Mbb[6*i+k]*s.acc_d[k];     // needs out.Mbb: written before the D3 barrier
+        double mcb=0; for(int k=0;k<6;k++) mcb+=stg.Mbb[6*i+k]*s.acc_d[k];     // needs stg.Mbb: written before the D3 barrier
         const double gw=(i==2)?mc_.total_mass*GRAV:0.0;
         const double integ=integ_[kk];                                       // first tick: 0
         s.W[i]=-kp*(s.pose[i]-s.pose_d[i])-P.kdValue*(s.vcom[i]-s.vel_d[i])-P.kiValue*integ+gw+mcb;
@@ -185,16 +189,16 @@ WBC_FN void wbc_assemble(const ModelConst& mc_,const Params& P,RbdScratch& s,Ctr
     WBC_SYNC();
     // ---- D7: QP vectors and the only dense H block (wbc.cpp:468-515) ----
     ASM_FOR(e,144){ int i=e/12,j=e%12; double ci=s.cmask[i/3],cj=s.cmask[j/3]; double v=0;
-        for(int k=0;k<6;k++) v+=(ci*out.Jc[18*i+k])*(cj*out.Jc[18*j+k]);
+        for(int k=0;k<6;k++) v+=(ci*stg.Jc[18*i+k])*(cj*stg.Jc[18*j+k]);
         out.Hff[e]=v+((i==j)?1.0:0.0); }
-    ASM_FOR(i,12){ double ci=s.cmask[i/3]; double v=0; for(int k=0;k<6;k++) v+=(ci*out.Jc[18*i+k])*s.W[k]; out.gf[i]=-v; }
+    ASM_FOR(i,12){ double ci=s.cmask[i/3]; double v=0; for(int k=0;k<6;k++) v+=(ci*stg.Jc[18*i+k])*s.W[k]; out.gf[i]=-v; }
     const double INF=1.0e20;
     ASM_FOR(i,70){
         double lo,up;
         if(i<6){ const double gw=(i==2)?mc_.total_mass*GRAV:0.0; lo=-gw; up=-gw; }
         else if(i<18){ lo=-s.Jdv_st[i-6]; up=lo; }
         else if(i<34){ lo=-INF; up=0.0; }
-        else if(i<46){ lo=-P.maxTorque-out.biasj[i-34]; up=P.maxTorque-out.biasj[i-34]; }
+        else if(i<46){ lo=-P.maxTorque-stg.biasj[i-34]; up=P.maxTorque-stg.biasj[i-34]; }
         else if(i<58){ lo=-INF; up=s.rcmd[i-46]-s.Jdv_sw[i-46]; }
         else { lo=s.rcmd[i-58]-s.Jdv_sw[i-58]; up=INF; }
         out.lbA[i]=lo; out.ubA[i]=up;

@@ -67,14 +67,14 @@ __global__ void __launch_bounds__(128) wbc_rbd_legs_kernel(int N,BatchIn in,LegO
 // 16 lanes per robot (wbc_assembly.cuh); a warp takes consecutive robots, grid-stride.  Each group reads the four LegOut records of its robot
 // (268 consecutive doubles), runs the dense phase in its own slice of shared memory and writes the compact QP.  A group past the end of the batch
 // re-does the last robot in step with that robot's own group (same warp, same instructions, same values written): no divergent barriers.
-struct UpdSmem { RbdScratch s; QPData qp; };
+struct UpdSmem { RbdScratch s; QPStage stg; };
 constexpr int UPD_GROUPS=32/WBC_ASM_NL;
 __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,BatchIn in,const LegOut* legs,CtrlState* st,QPData* qpd,unsigned char* first,double* com,double* plantAux){
     extern __shared__ double smem[];
     ModelConst& mc=*reinterpret_cast<ModelConst*>(smem);
     const int lane=threadIdx.x&(WBC_ASM_NL-1), grp=threadIdx.x/WBC_ASM_NL;
     UpdSmem& u=reinterpret_cast<UpdSmem*>(reinterpret_cast<char*>(smem)+sizeof(ModelConst))[grp];
-    RbdScratch& s=u.s; QPData& qp=u.qp;
+    RbdScratch& s=u.s; QPStage& stg=u.stg;
     { const double* src=(const double*)&c_model; double* dst=(double*)&mc; for(int i=threadIdx.x;i<MODEL_DOUBLES;i+=32) dst[i]=src[i]; }
     WBC_SYNC();
     for(int r0=blockIdx.x*UPD_GROUPS;r0<N;r0+=gridDim.x*UPD_GROUPS){
@@ -112,8 +112,9 @@ __global__ void __launch_bounds__(32) wbc_update_state_kernel(int N,Params prm,B
         WBC_SYNC();
         if(lane==0){ mtv3(s.Rwb,s.twist,s.vbody); mtv3(s.Rwb,s.twist+3,s.vbody+3); }   // MIXED -> body-fixed (KDC.cpp:822-825)
         WBC_SYNC();
-        wbc_assemble(mc,prm,s,st[r],qp,lane,(int)in.switching[r],(int)first[r],plantAux?plantAux+r:nullptr,N);
-        { const double* src=(const double*)&qp; double* dst=(double*)&qpd[r]; ASM_FOR(i,QPDATA_DOUBLES) dst[i]=src[i]; }
+        wbc_assemble(mc,prm,s,st[r],qpd[r],stg,lane,(int)in.switching[r],(int)first[r],plantAux?plantAux+r:nullptr,N);
+        WBC_SYNC();
+        { QPData& q=qpd[r]; ASM_FOR(i,216) q.Jc[i]=stg.Jc[i]; ASM_FOR(i,36) q.Mbb[i]=stg.Mbb[i]; ASM_FOR(i,12) q.biasj[i]=stg.biasj[i]; }
         ASM_FOR(k,3) com[k*N+r]=s.com[k];
         WBC_SYNC();
     }

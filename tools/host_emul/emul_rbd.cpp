@@ -25,6 +25,6 @@ extern "C" void emul_tick(const double* params16,const double* q,const double* q
     quat_to_R(quat,s.Rwb);
     mtv3(s.Rwb,s.twist,s.vbody); mtv3(s.Rwb,s.twist+3,s.vbody+3);
     for(int leg=0;leg<4;leg++) rbd_leg(mc,s,leg,leg);
-    wbc_assemble(mc,P,s,*(CtrlState*)state,*(QPData*)qpdata,0,switching,first,nullptr,1);
+    wbc_assemble(mc,P,s,*(CtrlState*)state,*(QPData*)qpdata,*(QPData*)qpdata,0,switching,first,nullptr,1);
 }
 extern "C" int emul_sizes(int which){ return which==0?CTRLSTATE_DOUBLES:QPDATA_DOUBLES; }
